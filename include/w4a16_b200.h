@@ -1,0 +1,158 @@
+/*
+ * w4a16_b200.h -- C ABI of libw4a16_b200.so: the B200-native (sm_100a) W4A16
+ * quantized-linear forward that replaces vllm-rust's AWQ / AWQ-Marlin / GPTQ
+ * CUDA path behind `trait QuantizedLinear`.
+ *
+ * Every entry point names the reference interface it replaces (file:line under
+ * crates/core/src/quantization/ of vasia123/vllm-rust).  INTEGRATION.md shows the
+ * Rust `extern "C"` block + `impl QuantizedLinear for B200W4A16Linear` that binds
+ * these symbols from crates/core.
+ *
+ * Conventions
+ *   - Plain pointers and sizes only.  No torch / candle types.
+ *   - Every function returns 0 on success, non-zero on failure; the message of
+ *     the last failure on the calling thread is w4a16_last_error()
+ *     (mirrors candle_core::Error::Msg via bail!, marlin_cuda.rs:546-564).
+ *   - All device pointers must live on the handle's device.  x / y / checkpoint
+ *     tensors are caller-owned; the handle owns the repacked weights and a fixed
+ *     workspace.  w4a16_forward_into never allocates and never synchronises, so
+ *     it can be captured in a CUDA graph (replaces OutputPool-backed
+ *     marlin_gemm_pooled, marlin_cuda.rs:1655-1753).
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream).
+ *   - There is no CPU fallback.  If no sm_100 device is present every call that
+ *     needs one fails loudly.
+ */
+#ifndef W4A16_B200_H
+#define W4A16_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define W4A16_ABI_VERSION 1
+
+typedef struct w4a16_linear *w4a16_handle_t;
+typedef void *w4a16_stream_t; /* cudaStream_t */
+typedef void *w4a16_comm_t;   /* ncclComm_t   */
+
+/* Checkpoint formats.  SURVEY.md 8a rows U1/D1 (AWQ), G1 (GPTQ, zeros as stored,
+ * no "+1"), G3 (symmetric q-8, qzeros ignored: marlin_gemm.cu:43-48). */
+enum w4a16_format {
+    W4A16_FORMAT_AWQ = 0,      /* qweight [K,N/8] + qzeros [G,N/8], AWQ nibble interleave (awq.rs:20-49) */
+    W4A16_FORMAT_GPTQ_ZP = 1,  /* qweight [K/8,N] + qzeros [G,N/8], sequential nibbles (gptq_dequant.cu:6-14) */
+    W4A16_FORMAT_GPTQ_SYM = 2  /* qweight [K/8,N], W = (q-8)*s (MarlinScalarType::Uint4b8, marlin.rs:52-56) */
+};
+
+enum w4a16_dtype { W4A16_DTYPE_F16 = 0, W4A16_DTYPE_BF16 = 1, W4A16_DTYPE_F32 = 2 };
+
+/* Tensor-parallel shard of one linear (distributed/parallel_layers.rs:36-324). */
+enum w4a16_tp_mode {
+    W4A16_TP_NONE = 0,
+    W4A16_TP_COLUMN = 1, /* rank r keeps output columns [r*N/tp, (r+1)*N/tp); no collective          */
+    W4A16_TP_ROW = 2     /* rank r keeps input rows    [r*K/tp, (r+1)*K/tp); forward ends in all-reduce */
+};
+
+/* -- errors ---------------------------------------------------------------- */
+const char *w4a16_last_error(void);
+int w4a16_abi_version(void);
+
+/* -- shape gate -------------------------------------------------------------
+ * check_marlin_supports_shape (marlin.rs:308-341): N % 64 == 0, K % 128 == 0,
+ * group_size in {-1, 32, 64, 128} (marlin.rs:48) and K % group_size == 0.     */
+int w4a16_check_shape(int64_t out_features, int64_t in_features, int group_size);
+
+/* -- construction -----------------------------------------------------------
+ * QuantizationConfig::create_linear(in, out, bias, device) (config.rs:125-131);
+ * AwqMarlinLinear::new (awq_marlin.rs:431-446); GptqLinear::new (gptq.rs:254-).
+ * in_features / out_features are the FULL (unsharded) sizes; w4a16_create is
+ * w4a16_create_shard with W4A16_TP_NONE.                                       */
+int w4a16_create(w4a16_handle_t *out, int64_t in_features, int64_t out_features, int group_size,
+                 int format, int has_bias, int device);
+int w4a16_create_shard(w4a16_handle_t *out, int64_t in_features, int64_t out_features,
+                       int group_size, int format, int has_bias, int device, int tp_mode,
+                       int tp_rank, int tp_size);
+int w4a16_destroy(w4a16_handle_t h);
+
+/* -- load-time repack -------------------------------------------------------
+ * QuantizedLinear::load_weights(&HashMap) with keys "qweight","qzeros","scales",
+ * "bias","g_idx" in CHECKPOINT layout; the repack happens inside
+ * (AwqMarlinLinear::load_weights awq_marlin.rs:580-667 = R2+R3+R1+S1;
+ *  GptqLinear::load_weights gptq.rs:435-454).
+ * All pointers are DEVICE pointers to the full (unsharded) checkpoint tensors;
+ * a sharded handle reads only its slice.  scales may be F16/BF16/F32 and are
+ * stored as BF16 (round-to-nearest-even, awq_marlin.rs:649-656).  bias may be
+ * NULL when has_bias == 0.  The call is asynchronous on `stream`; the
+ * checkpoint tensors may be freed once the stream has passed it.              */
+int w4a16_load_awq(w4a16_handle_t h, const uint32_t *qweight /*[K,N/8]*/,
+                   const uint32_t *qzeros /*[G,N/8]*/, const void *scales /*[G,N]*/,
+                   int scales_dtype, const void *bias /*[N] or NULL*/, int bias_dtype,
+                   w4a16_stream_t stream);
+/* g_idx: int32 [K] or NULL.  With g_idx the canonical act-order semantics
+ * W[k,n] = (q[k,n] - z[g_idx[k],n]) * s[g_idx[k],n] are implemented by a K
+ * permutation at load plus an activation gather at forward.  (The reference loads
+ * g_idx and never uses it: gptq.rs:349-366, marlin_gemm.cu:79-83.)  g_idx must
+ * assign exactly group_size rows to every group.  g_idx is read on the HOST side
+ * of the call (it synchronises `stream` once, at load).                       */
+int w4a16_load_gptq(w4a16_handle_t h, const uint32_t *qweight /*[K/8,N]*/,
+                    const uint32_t *qzeros /*[G,N/8] or NULL for GPTQ_SYM*/,
+                    const void *scales /*[G,N]*/, int scales_dtype,
+                    const int32_t *g_idx /*[K] device, or NULL*/, const void *bias, int bias_dtype,
+                    w4a16_stream_t stream);
+
+/* -- forward ----------------------------------------------------------------
+ * QuantizedLinear::forward(&Tensor) (config.rs:149) as it is executed by
+ * MarlinLinear::forward -> marlin_gemm_pooled / marlin_gemm (marlin.rs:741-754,
+ * marlin_cuda.rs:843-953, 1655-1753) and GptqLinear::forward -> gptq_gemm
+ * (gptq.rs:413-433, gptq_cuda.rs:322).
+ * x: [M, K_local] bf16, contiguous, 16-byte aligned.  y: [M, N_local] bf16; every
+ * element is written, no zero-init needed (marlin_cuda.rs:431-440).  Leading
+ * dims are flattened by the caller (awq_marlin.rs:545-571).  M >= 1.
+ * For a ROW shard y is the rank's partial sum WITHOUT bias.                   */
+int w4a16_forward_into(w4a16_handle_t h, const void *x_bf16, void *y_bf16, int64_t M,
+                       w4a16_stream_t stream);
+
+/* Same call with HOST buffers: H2D copy of x, forward, D2H copy of y, stream
+ * synchronise.  Staging buffers are owned by the handle and grown on demand
+ * (so this entry point may allocate; it is the end-to-end path bench.py times). */
+int w4a16_forward_host(w4a16_handle_t h, const void *x_bf16_host, void *y_bf16_host, int64_t M,
+                       w4a16_stream_t stream);
+
+/* RowParallelLinear::forward (parallel_layers.rs:275-313): local GEMM, then
+ * all_reduce(Sum) (nccl.rs:1338-1364), then + bias.  `comm` is the caller's
+ * ncclComm_t.  tp_size == 1 short-circuits the collective (nccl.rs:1339-1341). */
+int w4a16_forward_row_allreduce(w4a16_handle_t h, const void *x_bf16, void *y_bf16, int64_t M,
+                                w4a16_comm_t comm, w4a16_stream_t stream);
+
+/* Reserve per-handle scratch for up to max_tokens rows (act-order gather buffer,
+ * host staging).  Call before CUDA-graph capture.                             */
+int w4a16_reserve(w4a16_handle_t h, int64_t max_tokens);
+
+/* -- parity hooks (bit-exact checks against the oracle) ----------------------
+ * dequant: gptq_dequant_int4_bf16 / awq_marlin_dequant_int4_bf16 semantics,
+ * out[k,n] = bf16_rn(f32(q - z) * f32(bf16 scale)), dense [K_local, N_local]
+ * row-major, in ORIGINAL k order (act-order un-permuted).
+ * unpack: q as one byte per nibble [K_local, N_local], z [G_local, N_local].
+ * scales: the resident bf16 scales [G_local, N_local].                        */
+int w4a16_dequant_into(w4a16_handle_t h, void *w_bf16, w4a16_stream_t stream);
+int w4a16_unpack_into(w4a16_handle_t h, uint8_t *q, uint8_t *z, w4a16_stream_t stream);
+int w4a16_scales_into(w4a16_handle_t h, void *scales_bf16, w4a16_stream_t stream);
+
+/* -- introspection ----------------------------------------------------------- */
+int64_t w4a16_in_features(w4a16_handle_t h);   /* local K */
+int64_t w4a16_out_features(w4a16_handle_t h);  /* local N */
+int w4a16_has_bias(w4a16_handle_t h);
+int64_t w4a16_weight_bytes(w4a16_handle_t h);  /* resident bytes of the repacked layout */
+/* Kernels launched by this library in this process so far (bench.py's gpu_launches). */
+uint64_t w4a16_kernel_launches(void);
+/* Name of the kernel the dispatcher picks for M tokens ("decode_nt1", "prefill_umma", ...). */
+const char *w4a16_kernel_for(w4a16_handle_t h, int64_t M);
+/* Override dispatch for experiments: "auto" | "decode" | "prefill".  Returns non-zero if unknown. */
+int w4a16_set_dispatch(const char *mode);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* W4A16_B200_H */

@@ -1,0 +1,100 @@
+// w4a16_internal.cuh -- handle layout, error plumbing and kernel launch entry points
+// shared by the translation units of libw4a16_b200.so.  Not part of the ABI.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <string>
+
+#include "w4a16_layout.cuh"
+
+namespace w4 {
+
+// ---- errors ----------------------------------------------------------------
+void set_error(const std::string &msg);
+int fail(const std::string &msg);  // sets the error, returns 1
+#define W4_CUDA_OK(expr)                                                                          \
+    do {                                                                                          \
+        cudaError_t _e = (expr);                                                                  \
+        if (_e != cudaSuccess)                                                                    \
+            return ::w4::fail(std::string(#expr) + ": " + cudaGetErrorString(_e));                \
+    } while (0)
+
+extern std::atomic<uint64_t> g_kernel_launches;
+inline void count_launch() { g_kernel_launches.fetch_add(1, std::memory_order_relaxed); }
+
+// ---- per-device shared scratch (split-K partial sums) ------------------------
+// Forwards on one device are stream-ordered by the single engine task in the
+// reference (engine/output_pool.rs:40-43); the partial-sum scratch is therefore
+// per device, not per handle.  Tile tickets are per handle.
+struct DeviceScratch {
+    float *partials = nullptr;
+    size_t partial_bytes = 0;
+    int sm_count = 0;
+    int cc_major = 0, cc_minor = 0;
+};
+int get_device_scratch(int device, DeviceScratch **out);
+
+// ---- the handle ---------------------------------------------------------------
+struct Linear {
+    // full (checkpoint) geometry
+    int64_t K_full = 0, N_full = 0;
+    int group_size_cfg = 0;  // as given: -1 or 32/64/128
+    int format = 0;
+    bool has_bias = false;
+    int device = 0;
+    int tp_mode = 0, tp_rank = 0, tp_size = 1;
+    // local shard geometry
+    int64_t k_off = 0, n_off = 0;
+    Dims d{};
+    // resident tensors
+    uint32_t *qw = nullptr;        // [NR][KB][128]
+    uint8_t *meta = nullptr;       // [NR][G][48]
+    __nv_bfloat16 *bias = nullptr; // [N] or null
+    int32_t *perm = nullptr;       // act-order: tiled row i holds checkpoint row perm[i]; null otherwise
+    int32_t *tickets = nullptr;    // [NR] split-K arrival counters (self-resetting)
+    bool loaded = false;
+    // scratch that scales with M
+    __nv_bfloat16 *x_gather = nullptr;  // act-order gathered activations [cap, K]
+    int64_t x_gather_cap = 0;
+    __nv_bfloat16 *stage_x = nullptr, *stage_y = nullptr;  // forward_host staging
+    int64_t stage_cap = 0;
+    float *rowpar_f32 = nullptr;  // unused for now (fp32 all-reduce staging)
+    DeviceScratch *scratch = nullptr;
+};
+
+// ---- kernels (defined in the .cu files) ----------------------------------------
+struct RepackSrc {
+    const uint32_t *qweight;  // AWQ [K_full, N_full/8]  or GPTQ [K_full/8, N_full]
+    const uint32_t *qzeros;   // [G_full, N_full/8] or null (sym)
+    const void *scales;       // [G_full, N_full]
+    int scales_dtype;
+    int format;
+    int64_t K_full, N_full, G_full;
+    int64_t k_off, n_off;     // shard offsets (rows / columns of the checkpoint)
+    int gs;                   // effective group size
+    const int32_t *perm;      // device, local row i -> checkpoint row (already includes k_off) or null
+    const int32_t *row_group; // device, local row i -> checkpoint group index (act-order) or null
+};
+int launch_repack(const Linear &L, const RepackSrc &src, cudaStream_t stream);
+int launch_unpack(const Linear &L, uint8_t *q, uint8_t *z, cudaStream_t stream);
+int launch_dequant(const Linear &L, __nv_bfloat16 *w, cudaStream_t stream);
+int launch_scales_out(const Linear &L, __nv_bfloat16 *s, cudaStream_t stream);
+int launch_convert_bias(const void *src, int dtype, __nv_bfloat16 *dst, int64_t n, cudaStream_t stream);
+int launch_gather_x(const __nv_bfloat16 *x, const int32_t *perm, __nv_bfloat16 *xg, int64_t M, int64_t K,
+                    cudaStream_t stream);
+int launch_add_bias(__nv_bfloat16 *y, const __nv_bfloat16 *bias, int64_t M, int64_t N, cudaStream_t stream);
+
+// decode: M <= 32 tokens per launch
+int launch_decode(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
+                  cudaStream_t stream);
+const char *decode_kernel_name(int64_t M);
+// prefill (tcgen05): any M
+int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
+                   cudaStream_t stream);
+bool prefill_available();
+
+}  // namespace w4

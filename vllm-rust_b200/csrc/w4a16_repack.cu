@@ -1,0 +1,287 @@
+// w4a16_repack.cu -- load-time repack of AWQ / GPTQ checkpoints into the W4T layout,
+// plus the bit-exact parity hooks (unpack, dequant, scales) that read it back.
+//
+// Replaces, in one pass each:
+//   awq_to_gptq_qweight_int4 + .t().contiguous()   (marlin_gemm.cu:491-517, awq_marlin.rs:621-635)
+//   awq_marlin_repack_int4 on qzeros               (marlin_gemm.cu:431-459, awq_marlin.rs:638-644)
+//   scales F16 -> BF16                             (awq_marlin.rs:649-656)
+//   awq_to_marlin_tile_repack_cpu                  (awq_marlin.rs:276-366; the opt-in tile_b copy)
+// Integer work, bit-exact; tests/test_parity_gpu.py round-trips it through
+// w4a16_unpack_into against the oracle's unpack of the checkpoint tensors.
+#include "w4a16_internal.cuh"
+#include "w4a16_dequant.cuh"
+
+namespace w4 {
+
+__device__ __constant__ int kAwqShift[8] = {0, 16, 4, 20, 8, 24, 12, 28};  // awq_marlin.rs:372
+
+struct RepackParams {
+    const uint32_t *qweight;
+    const uint32_t *qzeros;
+    const void *scales;
+    int scales_dtype, format;
+    int64_t K_full, N_full;
+    int64_t k_off, n_off;
+    int gs;       // local effective group size
+    int gs_ckpt;  // checkpoint group size (K_full for per-channel)
+    const int32_t *perm;       // local tiled row -> local checkpoint row (null = identity)
+    const int32_t *grp_map;    // local group -> checkpoint group (null = (k_off + grp*gs)/gs_ckpt)
+    Dims d;
+    uint32_t *qw;
+    uint8_t *meta;
+};
+
+__device__ __forceinline__ uint32_t src_nibble(const RepackParams &p, int64_t k_local, int64_t n_local) {
+    int64_t row = p.k_off + (p.perm ? (int64_t)p.perm[k_local] : k_local);
+    int64_t col = p.n_off + n_local;
+    if (p.format == 0) {  // AWQ [K, N/8], interleaved along N (awq.rs:38)
+        uint32_t w = p.qweight[row * (p.N_full >> 3) + (col >> 3)];
+        return (w >> kAwqShift[col & 7]) & 0xFu;
+    }
+    uint32_t w = p.qweight[(row >> 3) * p.N_full + col];  // GPTQ [K/8, N], sequential along K
+    return (w >> (4 * (int)(row & 7))) & 0xFu;
+}
+
+__global__ void repack_qweight_kernel(RepackParams p) {
+    int64_t total = p.d.NR * p.d.KB * CHUNK_WORDS;
+    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        int64_t chunk = idx >> 7;
+        int wi = (int)(idx & 127);
+        int lane = wi >> 2, j = wi & 3;
+        int64_t R = chunk / p.d.KB, kb = chunk - R * p.d.KB;
+        uint32_t out = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            int kk, nn;
+            nibble_coord(lane, j, i, kk, nn);
+            out |= src_nibble(p, kb * CHUNK_K + kk, R * CHUNK_N + nn) << (4 * i);
+        }
+        p.qw[idx] = out;
+    }
+}
+
+__device__ __forceinline__ uint16_t load_scale_bf16(const void *s, int dtype, int64_t idx) {
+    float f;
+    if (dtype == 1) return reinterpret_cast<const uint16_t *>(s)[idx];
+    if (dtype == 0) f = __half2float(reinterpret_cast<const __half *>(s)[idx]);
+    else f = reinterpret_cast<const float *>(s)[idx];
+    return __bfloat16_as_ushort(__float2bfloat16_rn(f));
+}
+
+__global__ void repack_meta_kernel(RepackParams p) {
+    int64_t total = p.d.NR * p.d.G * 8;
+    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        int g = (int)(idx & 7);
+        int64_t blk = idx >> 3;
+        int64_t R = blk / p.d.G, grp = blk - R * p.d.G;
+        int64_t cg = p.grp_map ? (int64_t)p.grp_map[grp] : (p.k_off + grp * p.gs) / p.gs_ckpt;
+        uint8_t *m = p.meta + blk * META_BYTES;
+        uint32_t zz[2];
+        uint16_t ss[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            int64_t col = p.n_off + R * CHUNK_N + g + 8 * h;
+            ss[h] = load_scale_bf16(p.scales, p.scales_dtype, cg * p.N_full + col);
+            if (p.format == 2) {
+                zz[h] = 8u;  // symmetric: W = (q - 8) * s  (marlin_gemm.cu:43-48)
+            } else {
+                uint32_t w = p.qzeros[cg * (p.N_full >> 3) + (col >> 3)];
+                int sh = p.format == 0 ? kAwqShift[col & 7] : 4 * (int)(col & 7);
+                zz[h] = (w >> sh) & 0xFu;
+            }
+        }
+        reinterpret_cast<uint32_t *>(m)[g] = (uint32_t)ss[0] | ((uint32_t)ss[1] << 16);
+        m[META_ZERO_OFF + g] = (uint8_t)(zz[0] | (zz[1] << 4));
+        if (g == 0) reinterpret_cast<uint64_t *>(m)[5] = 0ull;  // pad bytes 40..47
+    }
+}
+
+int launch_repack(const Linear &L, const RepackSrc &src, cudaStream_t stream) {
+    RepackParams p;
+    p.qweight = src.qweight; p.qzeros = src.qzeros; p.scales = src.scales;
+    p.scales_dtype = src.scales_dtype; p.format = src.format;
+    p.K_full = src.K_full; p.N_full = src.N_full; p.k_off = src.k_off; p.n_off = src.n_off;
+    p.gs = L.d.gs; p.gs_ckpt = src.gs;
+    p.perm = src.perm; p.grp_map = src.row_group;
+    p.d = L.d; p.qw = L.qw; p.meta = L.meta;
+    int64_t words = L.d.NR * L.d.KB * CHUNK_WORDS;
+    int blocks = (int)((words + 255) / 256 < 148 * 16 ? (words + 255) / 256 : 148 * 16);
+    repack_qweight_kernel<<<blocks, 256, 0, stream>>>(p);
+    count_launch();
+    int64_t metas = L.d.NR * L.d.G * 8;
+    int mblocks = (int)((metas + 255) / 256 < 148 * 8 ? (metas + 255) / 256 : 148 * 8);
+    repack_meta_kernel<<<mblocks, 256, 0, stream>>>(p);
+    count_launch();
+    W4_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// parity hooks
+// ---------------------------------------------------------------------------
+struct HookParams {
+    Dims d;
+    const uint32_t *qw;
+    const uint8_t *meta;
+    const int32_t *perm;     // local tiled row -> local checkpoint row, or null
+    const int32_t *grp_map;  // local group -> output group row, or null (identity)
+};
+
+__global__ void unpack_q_kernel(HookParams p, uint8_t *q) {
+    int64_t total = p.d.K * p.d.N;
+    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        int64_t k = idx / p.d.N, n = idx - k * p.d.N;
+        NibblePos np = nibble_pos(p.d, k, n);
+        int64_t ko = p.perm ? (int64_t)p.perm[k] : k;
+        q[ko * p.d.N + n] = (uint8_t)((p.qw[np.word] >> np.shift) & 0xFu);
+    }
+}
+
+__global__ void unpack_z_kernel(HookParams p, uint8_t *z, __nv_bfloat16 *s) {
+    int64_t total = p.d.G * p.d.N;
+    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        int64_t grp = idx / p.d.N, n = idx - grp * p.d.N;
+        int64_t R = n >> 4;
+        int r = (int)(n & 15), g = r & 7, h = r >> 3;
+        const uint8_t *m = p.meta + meta_offset(p.d, R, grp);
+        int64_t go = p.grp_map ? (int64_t)p.grp_map[grp] : grp;
+        if (z) z[go * p.d.N + n] = (uint8_t)((m[META_ZERO_OFF + g] >> (4 * h)) & 0xF);
+        if (s) {
+            uint32_t pr = reinterpret_cast<const uint32_t *>(m)[g];
+            s[go * p.d.N + n] = __ushort_as_bfloat16((unsigned short)(h ? (pr >> 16) : (pr & 0xFFFFu)));
+        }
+    }
+}
+
+// Dense [K, N] bf16 through the SAME word-level primitive the prefill kernel uses
+// (w4a16_dequant.cuh): (128+q) - (128+z) in bf16 is exact, times the bf16 scale with
+// one rounding == bf16_rn(f32(q - z) * f32(scale)) of awq_marlin_dequant.cu:66-67.
+__global__ void dequant_dense_kernel(HookParams p, __nv_bfloat16 *w) {
+    int64_t total = p.d.NR * p.d.KB * CHUNK_WORDS;
+    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        int64_t chunk = idx >> 7;
+        int wi = (int)(idx & 127);
+        int lane = wi >> 2, j = wi & 3, g = lane >> 2;
+        int64_t R = chunk / p.d.KB, kb = chunk - R * p.d.KB;
+        uint32_t word = p.qw[idx];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            int kk, nn;
+            nibble_coord(lane, j, r, kk, nn);  // low half of pair r; the high half is k+1
+            int64_t k = kb * CHUNK_K + kk;
+            int64_t grp = k / p.d.gs;
+            const uint8_t *m = p.meta + meta_offset(p.d, R, grp);
+            int h = r & 1;
+            uint32_t pr = reinterpret_cast<const uint32_t *>(m)[g];
+            uint32_t s16 = h ? (pr >> 16) : (pr & 0xFFFFu);
+            uint32_t z4 = (m[META_ZERO_OFF + g] >> (4 * h)) & 0xFu;
+            uint32_t v = dequant_pair(word >> (4 * r), zero_magic(z4), s16 | (s16 << 16));
+            int64_t n = R * CHUNK_N + nn;
+            int64_t k0 = p.perm ? (int64_t)p.perm[k] : k;
+            int64_t k1 = p.perm ? (int64_t)p.perm[k + 1] : k + 1;
+            w[k0 * p.d.N + n] = __ushort_as_bfloat16((unsigned short)(v & 0xFFFFu));
+            w[k1 * p.d.N + n] = __ushort_as_bfloat16((unsigned short)(v >> 16));
+        }
+    }
+}
+
+static int grid_for(int64_t n) {
+    int64_t b = (n + 255) / 256;
+    return (int)(b < 148 * 16 ? (b > 0 ? b : 1) : 148 * 16);
+}
+
+// grp_map for the hooks lives next to perm on the handle (Linear::perm + K entries).
+static HookParams hook_params(const Linear &L) {
+    HookParams p;
+    p.d = L.d; p.qw = L.qw; p.meta = L.meta; p.perm = L.perm;
+    p.grp_map = L.perm ? L.perm + L.d.K : nullptr;
+    return p;
+}
+
+int launch_unpack(const Linear &L, uint8_t *q, uint8_t *z, cudaStream_t stream) {
+    HookParams p = hook_params(L);
+    if (q) { unpack_q_kernel<<<grid_for(L.d.K * L.d.N), 256, 0, stream>>>(p, q); count_launch(); }
+    if (z) { unpack_z_kernel<<<grid_for(L.d.G * L.d.N), 256, 0, stream>>>(p, z, nullptr); count_launch(); }
+    W4_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+int launch_scales_out(const Linear &L, __nv_bfloat16 *s, cudaStream_t stream) {
+    HookParams p = hook_params(L);
+    unpack_z_kernel<<<grid_for(L.d.G * L.d.N), 256, 0, stream>>>(p, nullptr, s);
+    count_launch();
+    W4_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+int launch_dequant(const Linear &L, __nv_bfloat16 *w, cudaStream_t stream) {
+    HookParams p = hook_params(L);
+    dequant_dense_kernel<<<grid_for(L.d.NR * L.d.KB * CHUNK_WORDS), 256, 0, stream>>>(p, w);
+    count_launch();
+    W4_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// small helpers around the forward
+// ---------------------------------------------------------------------------
+__global__ void convert_bias_kernel(const void *src, int dtype, __nv_bfloat16 *dst, int64_t n) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    dst[i] = __ushort_as_bfloat16(load_scale_bf16(src, dtype, i));
+}
+
+int launch_convert_bias(const void *src, int dtype, __nv_bfloat16 *dst, int64_t n, cudaStream_t stream) {
+    convert_bias_kernel<<<(int)((n + 255) / 256), 256, 0, stream>>>(src, dtype, dst, n);
+    count_launch();
+    W4_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+// act-order: xg[m][i] = x[m][perm[i]]  (8 tiled rows = one 16-byte store per thread)
+__global__ void gather_x_kernel(const __nv_bfloat16 *__restrict__ x, const int32_t *__restrict__ perm,
+                                __nv_bfloat16 *__restrict__ xg, int64_t M, int64_t K) {
+    int64_t per_row = K >> 3;
+    int64_t total = M * per_row;
+    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        int64_t m = idx / per_row, c = idx - m * per_row;
+        const __nv_bfloat16 *xr = x + m * K;
+        __align__(16) __nv_bfloat16 v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = xr[perm[c * 8 + e]];
+        *reinterpret_cast<uint4 *>(xg + m * K + c * 8) = *reinterpret_cast<const uint4 *>(v);
+    }
+}
+
+int launch_gather_x(const __nv_bfloat16 *x, const int32_t *perm, __nv_bfloat16 *xg, int64_t M, int64_t K,
+                    cudaStream_t stream) {
+    gather_x_kernel<<<grid_for(M * (K >> 3)), 256, 0, stream>>>(x, perm, xg, M, K);
+    count_launch();
+    W4_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+// y += bias (after the all-reduce of a row-parallel shard, parallel_layers.rs:301-304)
+__global__ void add_bias_kernel(__nv_bfloat16 *y, const __nv_bfloat16 *bias, int64_t M, int64_t N) {
+    int64_t total = M * N;
+    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        int64_t n = idx % N;
+        y[idx] = __float2bfloat16_rn(__bfloat162float(y[idx]) + __bfloat162float(bias[n]));
+    }
+}
+
+int launch_add_bias(__nv_bfloat16 *y, const __nv_bfloat16 *bias, int64_t M, int64_t N, cudaStream_t stream) {
+    add_bias_kernel<<<grid_for(M * N), 256, 0, stream>>>(y, bias, M, N);
+    count_launch();
+    W4_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace w4
