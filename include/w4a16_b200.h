@@ -126,6 +126,15 @@ int w4a16_forward_host(w4a16_handle_t h, const void *x_bf16_host, void *y_bf16_h
 int w4a16_forward_row_allreduce(w4a16_handle_t h, const void *x_bf16, void *y_bf16, int64_t M,
                                 w4a16_comm_t comm, w4a16_stream_t stream);
 
+/* Communicator bootstrap for callers that do not already hold an ncclComm_t
+ * (distributed/launcher.rs:132-262: ncclGetUniqueId on rank 0, out-of-band
+ * broadcast of the 128-byte id, ncclCommInitRank).  NCCL is dlopen'ed as
+ * libnccl.so.2, like nccl.rs:479-485.  unique_id is a 128-byte HOST buffer. */
+#define W4A16_NCCL_UNIQUE_ID_BYTES 128
+int w4a16_nccl_unique_id(void *unique_id_out);
+int w4a16_nccl_comm_init(w4a16_comm_t *comm_out, int world_size, const void *unique_id, int rank);
+int w4a16_nccl_comm_destroy(w4a16_comm_t comm);
+
 /* Reserve per-handle scratch for up to max_tokens rows (act-order gather buffer,
  * host staging).  Call before CUDA-graph capture.                             */
 int w4a16_reserve(w4a16_handle_t h, int64_t max_tokens);

@@ -126,7 +126,7 @@ def test_k6_lcg_case_oracle_consistency(seed, M, K, N):
     qw, qz, sc, x = C.lcg_gemm_case(seed, M, K, N, g)
     # generator sanity: bf16-rounded, in the documented ranges
     assert (O.np_bf16_round(sc) == sc).all() and (O.np_bf16_round(x) == x).all()
-    assert np.abs(sc).max() <= 0.1 + 1e-6 and np.abs(x).max() <= 1.0 + 1e-6
+    assert np.abs(sc).max() <= 0.1 * (1 + 2**-8) and np.abs(x).max() <= 1.0 * (1 + 2**-8)  # bf16 rounding of the range ends
     q, z = C.gptq_unpack_qweight(qw, K, N), C.seq_unpack(qz, N)
     y_c = C.gemm_f32(x, q, z, sc, None, None, g, K, N)
     # pure-Python transcription of marlin_cuda.rs:2091-2112 on a few entries
@@ -162,7 +162,7 @@ def test_k9_marlin_shape_gate(product):
         with pytest.raises(ValueError):
             ok(n, k, 128)
     with pytest.raises(ValueError):
-        ok(4096, 4096 + 128, 256 + 128)  # group does not divide K
+        ok(4096, 4096, 96)  # group does not divide K (marlin.rs:332-338)
     assert product.MARLIN_SUPPORTED_GROUP_SIZES == (-1, 32, 64, 128)
 
 

@@ -1,0 +1,296 @@
+"""GPU parity: the CUDA path, called through the C ABI, against the CPU oracle.
+
+Integer work (unpack, repack round trip, bf16 scales) and the dequantised weights
+are checked BIT-EXACT.  The GEMM is checked with the reference's own tolerance
+max(0.01*max|y|, 5e-2) (marlin_cuda.rs:2168-2183) and the north-star bound
+max|err| <= 1e-2*max|y| against the fp32 dequant-matmul on bf16-rounded operands."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O
+from helpers import (assert_close_ref, awq_unpacked, bits_of, gptq_unpacked, oracle_forward, t_bf16_from_bits, t_i32)
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def make_awq_layer(P, K, N, g, seed, bias=False, **tp):
+    qweight, qzeros, scales, b = O.make_awq_checkpoint(K, N, g if g > 0 else K, seed=seed, bias=bias)
+    cfg = P.AwqConfig.int4(g)
+    lin = cfg.create_linear(K, N, bias, DEV, **tp)
+    w = {"qweight": t_i32(qweight), "qzeros": t_i32(qzeros), "scales": torch.from_numpy(scales)}
+    if bias:
+        w["bias"] = torch.from_numpy(b).to(torch.bfloat16)
+    lin.load_weights(w)
+    bias_r = None if not bias else O.np_bf16_round(b)
+    return lin, (qweight, qzeros, scales, bias_r)
+
+
+def run_forward(lin, x_bits):
+    x = t_bf16_from_bits(x_bits).to(DEV)
+    y = lin.forward(x)
+    torch.cuda.synchronize()
+    return bits_of(y)
+
+
+# ---- integer / dequant: bit exact ---------------------------------------------------
+@pytest.mark.parametrize("K,N,g", [(128, 64, 128), (256, 128, 128), (512, 192, 64), (256, 64, 32), (384, 128, -1),
+                                   (1024, 6144, 128)])
+def test_awq_unpack_scales_dequant_bit_exact(product, K, N, g):
+    lin, (qweight, qzeros, scales, _) = make_awq_layer(product, K, N, g, seed=K + N)
+    q, z, sb = awq_unpacked(qweight, qzeros, scales)
+    gq, gz = lin.unpack()
+    assert (gq.cpu().numpy() == q).all(), "qweight nibbles differ"
+    assert (gz.cpu().numpy() == z).all(), "zero points differ"
+    assert (bits_of(lin.scales()) == sb).all(), "bf16 scales differ"
+    want = O.np_dequant_bf16(q, z, sb, g if g > 0 else K)
+    assert (bits_of(lin.dequantize()) == want).all(), "dequantised weights differ (D2 grid)"
+    if K * N <= 256 * 128:  # and against the scalar C restatement of awq_marlin_dequant.cu
+        assert (want == O.C.dequant_bf16(q, z, sb, None, g if g > 0 else K, K, N)).all()
+
+
+@pytest.mark.parametrize("sym", [False, True])
+@pytest.mark.parametrize("act_order", [False, True])
+def test_gptq_unpack_dequant_bit_exact(product, sym, act_order):
+    K, N, g = 512, 128, 128
+    qweight, qzeros, scales, g_idx = O.make_gptq_checkpoint(K, N, g, seed=3, act_order=act_order)
+    cfg = product.GptqConfig(4, g, desc_act=act_order, use_stored_zeros=not sym)
+    lin = cfg.create_linear(K, N, False, DEV)
+    w = {"qweight": t_i32(qweight), "scales": torch.from_numpy(scales), "qzeros": t_i32(qzeros)}
+    if act_order:
+        w["g_idx"] = torch.from_numpy(g_idx)
+    lin.load_weights(w)
+    q, z, sb = gptq_unpacked(qweight, qzeros, scales)
+    gq, gz = lin.unpack()
+    assert (gq.cpu().numpy() == q).all()
+    if not sym:
+        assert (gz.cpu().numpy() == z).all()
+    else:
+        assert (gz.cpu().numpy() == 8).all()
+    want = O.np_dequant_bf16(q, z, sb, g, g_idx=g_idx, zero_mode=1 if sym else 0)
+    assert (bits_of(lin.dequantize()) == want).all()
+
+
+# ---- reference KATs through the CUDA path ----------------------------------------------
+def test_k5_gemv_smoke_known_values(product):
+    """marlin_cuda.rs:1941-2024 restated at the smallest shape the gate admits: every word
+    0x76543210 along K, z = 0, s = 1, x = 1 -> each group of 8 k sums to 28."""
+    K, N, g = 128, 64, 128
+    qweight = np.full((K // 8, N), 0x76543210, np.uint32)
+    qzeros = np.zeros((1, N // 8), np.uint32)
+    lin = product.GptqConfig(4, g).create_linear(K, N, False, DEV)
+    lin.load_weights({"qweight": t_i32(qweight), "qzeros": t_i32(qzeros), "scales": torch.ones((1, N), dtype=torch.float16)})
+    y = lin.forward(torch.ones((1, K), dtype=torch.bfloat16, device=DEV))
+    assert (y.float().cpu().numpy() == 28.0 * (K // 8)).all()
+
+
+K6_CASES = [(0x9E3779B9, 1, 256, 128), (0xCAFEBABE, 4, 256, 64), (0xCAFEBABE ^ 8, 8, 256, 64),
+            (0xCAFEBABE ^ 12, 12, 256, 64), (0xCAFEBABE ^ 16, 16, 256, 64), (0xDEADBEEF, 32, 256, 64)]
+
+
+@pytest.mark.parametrize("seed,M,K,N", K6_CASES)
+def test_k6_lcg_cases_match_scalar_oracle(product, seed, M, K, N):
+    """test_awq_gemv_matches_cpu_reference_m{1,4,8,12,16} / ..._m32 (marlin_cuda.rs:2032-2612):
+    same LCG data, same scalar fp32 oracle, same tolerance."""
+    g = 128
+    qw, qz, sc, x = O.C.lcg_gemm_case(seed, M, K, N, g)
+    lin = product.GptqConfig(4, g).create_linear(K, N, False, DEV)
+    lin.load_weights({"qweight": t_i32(qw), "qzeros": t_i32(qz), "scales": torch.from_numpy(sc)})
+    q, z = O.C.gptq_unpack_qweight(qw, K, N), O.C.seq_unpack(qz, N)
+    want = O.C.gemm_f32(x, q, z, sc, None, None, g, K, N)
+    got = run_forward(lin, O.np_f32_to_bf16_bits(x))
+    err = np.abs(O.np_bf16_bits_to_f32(got) - want).max()
+    assert err <= O.reference_tolerance(want), err
+    assert err <= 1e-2 * np.abs(want).max() + 1e-6
+
+
+def test_k7_tile_mma_lockdown_data(product):
+    """marlin_tile_cuda.rs:594-726 data: a=((i*0.137)%2)-1, nib=(113k+29n+7)%16, zp=(17g+11n+3)%16,
+    s=0.05+0.01g+0.0025n, tightest tolerance of the nine shapes (5e-2 abs is for K=16; scaled by max|y|)."""
+    for M, K, N in [(4, 128, 64), (16, 256, 128), (32, 512, 64)]:
+        g = 128
+        k, n = np.arange(K)[:, None], np.arange(N)[None, :]
+        q = ((113 * k + 29 * n + 7) % 16).astype(np.uint8)
+        gi = np.arange(K // g)[:, None]
+        z = ((17 * gi + 11 * n + 3) % 16).astype(np.uint8)
+        s = (0.05 + 0.01 * gi + 0.0025 * n).astype(np.float32)
+        a = (((np.arange(M * K) * 0.137) % 2) - 1).astype(np.float32).reshape(M, K)
+        xb = O.np_f32_to_bf16_bits(a)
+        lin = product.GptqConfig(4, g).create_linear(K, N, False, DEV)
+        lin.load_weights({"qweight": t_i32(O.np_gptq_pack_qweight(q)), "qzeros": t_i32(O.np_seq_pack(z)),
+                          "scales": torch.from_numpy(s)})
+        sb = O.np_f32_to_bf16_bits(s)
+        want = oracle_forward(xb, q, z, sb, g)
+        assert_close_ref(run_forward(lin, xb), want, f"K-7 {M}x{K}x{N}")
+
+
+# ---- GEMM parity across M, group sizes, bias ----------------------------------------------
+@pytest.mark.parametrize("M", [1, 2, 3, 7, 8, 9, 15, 16, 17, 31, 32, 33, 64, 100])
+def test_awq_forward_all_m(product, M):
+    K, N, g = 1024, 256, 128
+    lin, (qweight, qzeros, scales, _) = make_awq_layer(product, K, N, g, seed=17)
+    q, z, sb = awq_unpacked(qweight, qzeros, scales)
+    xb = O.make_activations(M, K, seed=M)
+    assert_close_ref(run_forward(lin, xb), oracle_forward(xb, q, z, sb, g), f"M={M}")
+
+
+@pytest.mark.parametrize("g", [32, 64, 128, -1])
+@pytest.mark.parametrize("M", [1, 16, 32])
+def test_awq_forward_group_sizes_and_bias(product, g, M):
+    K, N = 512, 192
+    lin, (qweight, qzeros, scales, bias) = make_awq_layer(product, K, N, g, seed=5 + M, bias=True)
+    q, z, sb = awq_unpacked(qweight, qzeros, scales)
+    xb = O.make_activations(M, K, seed=11)
+    assert_close_ref(run_forward(lin, xb), oracle_forward(xb, q, z, sb, g if g > 0 else K, bias_f32=bias), f"g={g}")
+
+
+def test_rank3_input_and_noncontiguous(product):
+    K, N, g = 256, 128, 128
+    lin, (qweight, qzeros, scales, _) = make_awq_layer(product, K, N, g, seed=9)
+    q, z, sb = awq_unpacked(qweight, qzeros, scales)
+    xb = O.make_activations(6, K, seed=2)
+    x = t_bf16_from_bits(xb).to(DEV).view(2, 3, K)
+    y = lin.forward(x)
+    assert tuple(y.shape) == (2, 3, N)
+    assert_close_ref(bits_of(y).reshape(6, N), oracle_forward(xb, q, z, sb, g), "rank3")
+    xt = t_bf16_from_bits(xb).to(DEV).t().contiguous().t()  # non-contiguous view
+    assert not xt.is_contiguous()
+    assert (bits_of(lin.forward(xt)) == bits_of(y).reshape(6, N)).all()
+
+
+def test_determinism_and_every_element_written(product):
+    K, N, g = 2048, 128, 128  # short N: the decode kernel splits K across CTAs (ticket path)
+    lin, _ = make_awq_layer(product, K, N, g, seed=4)
+    x = t_bf16_from_bits(O.make_activations(5, K, seed=3)).to(DEV)
+    y0 = torch.full((5, N), float("nan"), dtype=torch.bfloat16, device=DEV)
+    lin.forward_into(x, y0)
+    assert not torch.isnan(y0.float()).any()
+    for _ in range(5):
+        y1 = torch.full((5, N), float("nan"), dtype=torch.bfloat16, device=DEV)
+        lin.forward_into(x, y1)
+        assert (bits_of(y1) == bits_of(y0)).all()
+
+
+# ---- BASELINE configs at full size (np float64 oracle) ---------------------------------------
+@pytest.mark.parametrize("K,N", [(1024, 6144), (4096, 6144), (4096, 4096), (4096, 24576), (12288, 4096)])
+def test_config_1_2_shapes_m1(product, K, N):
+    g = 128
+    lin, (qweight, qzeros, scales, _) = make_awq_layer(product, K, N, g, seed=K ^ N)
+    q, z, sb = awq_unpacked(qweight, qzeros, scales)
+    xb = O.make_activations(1, K, seed=1)
+    assert_close_ref(run_forward(lin, xb), oracle_forward(xb, q, z, sb, g), f"{K}x{N}")
+
+
+@pytest.mark.parametrize("M", [1, 8, 64, 256])
+@pytest.mark.parametrize("K,N", [(2560, 6144), (4096, 2560), (9728, 2560)])
+def test_config_4_gptq_act_order(product, M, K, N):
+    g = 128
+    qweight, qzeros, scales, g_idx = O.make_gptq_checkpoint(K, N, g, seed=K + M, act_order=True)
+    lin = product.GptqConfig(4, g, desc_act=True).create_linear(K, N, False, DEV)
+    lin.load_weights({"qweight": t_i32(qweight), "qzeros": t_i32(qzeros), "scales": torch.from_numpy(scales),
+                      "g_idx": torch.from_numpy(g_idx)})
+    q, z, sb = gptq_unpacked(qweight, qzeros, scales)
+    xb = O.make_activations(M, K, seed=M)
+    assert_close_ref(run_forward(lin, xb), oracle_forward(xb, q, z, sb, g, g_idx=g_idx), f"act-order {K}x{N} M={M}")
+
+
+def test_gptq_trivial_g_idx_is_the_pinned_subcase(product):
+    K, N, g = 512, 128, 128
+    qweight, qzeros, scales, _ = O.make_gptq_checkpoint(K, N, g, seed=1)
+    triv = torch.arange(K, dtype=torch.int32) // g
+    w = {"qweight": t_i32(qweight), "qzeros": t_i32(qzeros), "scales": torch.from_numpy(scales)}
+    a = product.GptqConfig(4, g).create_linear(K, N, False, DEV)
+    a.load_weights(w)
+    b = product.GptqConfig(4, g, desc_act=True).create_linear(K, N, False, DEV)
+    b.load_weights({**w, "g_idx": triv})
+    x = t_bf16_from_bits(O.make_activations(4, K)).to(DEV)
+    assert (bits_of(a.forward(x)) == bits_of(b.forward(x))).all()
+
+
+# ---- TP composition on one GPU (config 5 semantics) ------------------------------------
+@pytest.mark.parametrize("tp", [2, 4, 8])
+def test_tp_shards_compose(product, tp):
+    K, N, g, M = 2048, 1024, 128, 4
+    qweight, qzeros, scales, b = O.make_awq_checkpoint(K, N, g, seed=tp, bias=True)
+    w = {"qweight": t_i32(qweight), "qzeros": t_i32(qzeros), "scales": torch.from_numpy(scales),
+         "bias": torch.from_numpy(b).to(torch.bfloat16)}
+    q, z, sb = awq_unpacked(qweight, qzeros, scales)
+    xb = O.make_activations(M, K, seed=8)
+    x = t_bf16_from_bits(xb).to(DEV)
+    cfg = product.AwqConfig.int4(g)
+    # column parallel: concatenated shard outputs == the full layer, bit for bit
+    full = cfg.create_linear(K, N, True, DEV)
+    full.load_weights(w)
+    y_full = bits_of(full.forward(x))
+    cols = []
+    for r in range(tp):
+        sh = cfg.create_linear(K, N, True, DEV, tp_mode=1, tp_rank=r, tp_size=tp)
+        sh.load_weights(w)
+        assert sh.out_features() == N // tp and sh.in_features() == K
+        cols.append(bits_of(sh.forward(x)))
+    assert (np.concatenate(cols, axis=1) == y_full).all()
+    # row parallel: sum of partials (no bias) + bias == oracle within tolerance
+    acc = np.zeros((M, N), np.float64)
+    for r in range(tp):
+        sh = cfg.create_linear(K, N, True, DEV, tp_mode=2, tp_rank=r, tp_size=tp)
+        sh.load_weights(w)
+        k0, k1 = product.shard_range(K, r, tp)
+        part = bits_of(sh.forward(x[:, k0:k1]))
+        want_part = oracle_forward(xb[:, k0:k1], q[k0:k1], z[k0 // g:k1 // g], sb[k0 // g:k1 // g], g)
+        assert_close_ref(part, want_part, f"row shard {r}/{tp}")
+        acc += O.np_bf16_bits_to_f32(part)
+    want = oracle_forward(xb, q, z, sb, g, bias_f32=O.np_bf16_round(b))
+    got = acc + O.np_bf16_round(b)[None, :]
+    assert np.abs(got - want).max() <= O.reference_tolerance(want)
+
+
+# ---- error behaviour (marlin_cuda.rs:138-146, 546-564; awq.rs:691-699) ----------------------------
+def test_errors(product):
+    cfg = product.AwqConfig.int4(128)
+    lin = cfg.create_linear(256, 128, False, DEV)
+    x = torch.zeros((1, 256), dtype=torch.bfloat16, device=DEV)
+    with pytest.raises(product.W4A16Error, match="not loaded"):
+        lin.forward(x)
+    qweight, qzeros, scales, _ = O.make_awq_checkpoint(256, 128, 128)
+    with pytest.raises(product.W4A16Error, match="Missing 'scales'"):
+        lin.load_weights({"qweight": t_i32(qweight), "qzeros": t_i32(qzeros)})
+    with pytest.raises(product.W4A16Error, match="shape"):
+        lin.load_weights({"qweight": t_i32(qweight[:, :8]), "qzeros": t_i32(qzeros), "scales": torch.from_numpy(scales)})
+    lin.load_weights({"qweight": t_i32(qweight), "qzeros": t_i32(qzeros), "scales": torch.from_numpy(scales)})
+    with pytest.raises(product.W4A16Error, match="BF16"):
+        lin.forward(x.to(torch.float16))
+    with pytest.raises(product.W4A16Error, match="in_features"):
+        lin.forward(torch.zeros((1, 128), dtype=torch.bfloat16, device=DEV))
+    with pytest.raises(product.W4A16Error):
+        cfg.create_linear(256, 100, False, DEV)  # outside the Marlin gate: no CPU fallback
+
+
+def test_forward_host_matches_forward(product):
+    K, N, g, M = 1024, 256, 128, 3
+    lin, _ = make_awq_layer(product, K, N, g, seed=2)
+    xb = O.make_activations(M, K)
+    xh = t_bf16_from_bits(xb).pin_memory()
+    yh = torch.empty((M, N), dtype=torch.bfloat16).pin_memory()
+    lin.forward_host(xh, yh)
+    assert (bits_of(yh) == run_forward(lin, xb)).all()
+
+
+def test_cuda_graph_capture(product):
+    """forward_into never allocates or synchronises: the OutputPool / graph-capture contract."""
+    K, N, g, M = 1024, 256, 128, 4
+    lin, _ = make_awq_layer(product, K, N, g, seed=6)
+    x = t_bf16_from_bits(O.make_activations(M, K)).to(DEV)
+    y = torch.zeros((M, N), dtype=torch.bfloat16, device=DEV)
+    want = bits_of(lin.forward(x))
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        lin.forward_into(x, y)  # warm-up on the side stream
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=s):
+            lin.forward_into(x, y)
+            lin.forward_into(x, y)
+    y.zero_()
+    graph.replay()
+    torch.cuda.synchronize()
+    assert (bits_of(y) == want).all()

@@ -1,0 +1,452 @@
+// w4a16_api.cu -- the extern "C" surface of libw4a16_b200.so (include/w4a16_b200.h).
+// Handle lifetime, shape gates, load-time repack orchestration, forward dispatch,
+// the row-parallel all-reduce and the parity hooks.  No compute lives here.
+#include "../../include/w4a16_b200.h"
+
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "w4a16_internal.cuh"
+
+namespace w4 {
+
+static thread_local std::string t_last_error;
+std::atomic<uint64_t> g_kernel_launches{0};
+
+void set_error(const std::string &msg) { t_last_error = msg; }
+int fail(const std::string &msg) {
+    t_last_error = msg;
+    return 1;
+}
+
+static std::mutex g_dev_mu;
+static DeviceScratch g_dev[64];
+static bool g_dev_init[64] = {};
+
+int get_device_scratch(int device, DeviceScratch **out) {
+    if (device < 0 || device >= 64) return fail("device index out of range");
+    std::lock_guard<std::mutex> lk(g_dev_mu);
+    if (!g_dev_init[device]) {
+        int count = 0;
+        cudaError_t e = cudaGetDeviceCount(&count);
+        if (e != cudaSuccess || count == 0)
+            return fail(std::string("no CUDA device available (libw4a16_b200 has no CPU fallback): ") +
+                        cudaGetErrorString(e));
+        if (device >= count) return fail("device index >= device count");
+        cudaDeviceProp prop;
+        W4_CUDA_OK(cudaGetDeviceProperties(&prop, device));
+        if (prop.major != 10)
+            return fail("libw4a16_b200 is built for sm_100a only; device " + std::to_string(device) + " is sm_" +
+                        std::to_string(prop.major) + std::to_string(prop.minor));
+        g_dev[device].sm_count = prop.multiProcessorCount;
+        g_dev[device].cc_major = prop.major;
+        g_dev[device].cc_minor = prop.minor;
+        g_dev_init[device] = true;
+    }
+    *out = &g_dev[device];
+    return 0;
+}
+
+static std::string g_dispatch = "auto";
+constexpr int64_t DECODE_MAX_M = 32;
+
+// marlin.rs:48, 308-341
+static int check_shape(int64_t N, int64_t K, int gs) {
+    if (gs != -1 && gs != 32 && gs != 64 && gs != 128)
+        return fail("Marlin requires group_size in [-1, 32, 64, 128], got " + std::to_string(gs));
+    if (N <= 0 || K <= 0) return fail("in_features and out_features must be positive");
+    if (N % 64 != 0) return fail("out_features (" + std::to_string(N) + ") must be divisible by 64 for Marlin");
+    if (K % 128 != 0) return fail("in_features (" + std::to_string(K) + ") must be divisible by 128 for Marlin");
+    if (gs > 0 && K % gs != 0)
+        return fail("in_features (" + std::to_string(K) + ") must be divisible by group_size (" + std::to_string(gs) + ")");
+    return 0;
+}
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+        else prev = -1;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+static void free_linear(Linear *L) {
+    if (!L) return;
+    DeviceGuard g(L->device);
+    cudaFree(L->qw); cudaFree(L->meta); cudaFree(L->bias); cudaFree(L->perm); cudaFree(L->tickets);
+    cudaFree(L->splitk_scratch); cudaFree(L->x_gather); cudaFree(L->stage_x); cudaFree(L->stage_y);
+    cudaFree(L->rowpar_f32);
+    delete L;
+}
+
+static int finish_load(Linear *L, const void *bias, int bias_dtype, cudaStream_t stream) {
+    if (L->has_bias) {
+        if (!bias) return fail("load_weights: layer was created with bias but none was given");
+        // bias is per output feature: a COLUMN shard keeps its slice, a ROW shard keeps all of it
+        size_t esz = bias_dtype == W4A16_DTYPE_F32 ? 4 : 2;
+        const char *src = reinterpret_cast<const char *>(bias) + (size_t)L->n_off * esz;
+        if (launch_convert_bias(src, bias_dtype, L->bias, L->d.N, stream)) return 1;
+    }
+    L->loaded = true;
+    return 0;
+}
+
+// ---- NCCL, dlopen'ed (nccl.rs:451-547) ---------------------------------------------
+struct UniqueId { char internal[W4A16_NCCL_UNIQUE_ID_BYTES]; };
+struct Nccl {
+    void *lib = nullptr;
+    int (*GetUniqueId)(void *) = nullptr;
+    int (*CommInitRank)(void **, int, UniqueId, int) = nullptr;
+    int (*CommDestroy)(void *) = nullptr;
+    int (*AllReduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+};
+static Nccl g_nccl;
+static std::once_flag g_nccl_once;
+static std::string g_nccl_err;
+
+static int nccl_load() {
+    std::call_once(g_nccl_once, [] {
+        const char *names[] = {"libnccl.so.2", "libnccl.so"};
+        for (const char *n : names) {
+            g_nccl.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+            if (g_nccl.lib) break;
+        }
+        if (!g_nccl.lib) { g_nccl_err = std::string("dlopen(libnccl.so.2) failed: ") + dlerror(); return; }
+        auto sym = [&](const char *s) { return dlsym(g_nccl.lib, s); };
+        g_nccl.GetUniqueId = reinterpret_cast<int (*)(void *)>(sym("ncclGetUniqueId"));
+        g_nccl.CommInitRank = reinterpret_cast<int (*)(void **, int, UniqueId, int)>(sym("ncclCommInitRank"));
+        g_nccl.CommDestroy = reinterpret_cast<int (*)(void *)>(sym("ncclCommDestroy"));
+        g_nccl.AllReduce = reinterpret_cast<int (*)(const void *, void *, size_t, int, int, void *, cudaStream_t)>(sym("ncclAllReduce"));
+        g_nccl.GetErrorString = reinterpret_cast<const char *(*)(int)>(sym("ncclGetErrorString"));
+        if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.CommDestroy || !g_nccl.AllReduce)
+            g_nccl_err = "libnccl.so.2 is missing a required symbol";
+    });
+    if (!g_nccl_err.empty()) return fail(g_nccl_err);
+    return 0;
+}
+static int nccl_check(int rc, const char *what) {
+    if (rc == 0) return 0;
+    return fail(std::string(what) + ": " + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "NCCL error") +
+                " (" + std::to_string(rc) + ")");
+}
+constexpr int NCCL_BF16 = 9, NCCL_SUM = 0;
+
+static int ensure_stage(Linear *L, int64_t M) {
+    if (M <= L->stage_cap) return 0;
+    cudaFree(L->stage_x); cudaFree(L->stage_y);
+    L->stage_x = L->stage_y = nullptr; L->stage_cap = 0;
+    W4_CUDA_OK(cudaMalloc(&L->stage_x, (size_t)M * L->d.K * 2));
+    W4_CUDA_OK(cudaMalloc(&L->stage_y, (size_t)M * L->d.N * 2));
+    L->stage_cap = M;
+    return 0;
+}
+static int ensure_gather(Linear *L, int64_t M) {
+    if (!L->perm || M <= L->x_gather_cap) return 0;
+    cudaFree(L->x_gather);
+    L->x_gather = nullptr; L->x_gather_cap = 0;
+    W4_CUDA_OK(cudaMalloc(&L->x_gather, (size_t)M * L->d.K * 2));
+    L->x_gather_cap = M;
+    return 0;
+}
+
+static int forward_local(Linear *L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
+                         cudaStream_t stream) {
+    if (!L->loaded) return fail("forward: weights not loaded (call load_weights first)");
+    if (M < 1) return fail("forward: M must be >= 1");
+    if (!x || !y) return fail("forward: null x or y");
+    if ((reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(y) & 15))
+        return fail("forward: x and y must be 16-byte aligned");
+    if (L->perm) {  // act-order: tiled row i multiplies x[:, perm[i]]
+        if (ensure_gather(L, M)) return 1;
+        if (launch_gather_x(x, L->perm, L->x_gather, M, L->d.K, stream)) return 1;
+        x = L->x_gather;
+    }
+    bool want_prefill = g_dispatch == "prefill" || (g_dispatch == "auto" && M > DECODE_MAX_M);
+    if (want_prefill && prefill_available()) return launch_prefill(*L, x, y, M, add_bias, stream);
+    if (g_dispatch == "prefill") return fail("forward: prefill kernel not available in this build");
+    for (int64_t m0 = 0; m0 < M; m0 += DECODE_MAX_M) {
+        int64_t mm = std::min<int64_t>(DECODE_MAX_M, M - m0);
+        if (launch_decode(*L, x + m0 * L->d.K, y + m0 * L->d.N, mm, add_bias, stream)) return 1;
+    }
+    return 0;
+}
+
+}  // namespace w4
+
+using namespace w4;
+
+extern "C" {
+
+const char *w4a16_last_error(void) { return t_last_error.c_str(); }
+int w4a16_abi_version(void) { return W4A16_ABI_VERSION; }
+uint64_t w4a16_kernel_launches(void) { return g_kernel_launches.load(); }
+
+int w4a16_check_shape(int64_t out_features, int64_t in_features, int group_size) {
+    return check_shape(out_features, in_features, group_size);
+}
+
+int w4a16_create_shard(w4a16_handle_t *out, int64_t in_features, int64_t out_features, int group_size,
+                       int format, int has_bias, int device, int tp_mode, int tp_rank, int tp_size) {
+    if (!out) return fail("create: null out pointer");
+    *out = nullptr;
+    if (format < W4A16_FORMAT_AWQ || format > W4A16_FORMAT_GPTQ_SYM) return fail("create: unknown format");
+    if (tp_mode < W4A16_TP_NONE || tp_mode > W4A16_TP_ROW) return fail("create: unknown tp_mode");
+    if (tp_mode == W4A16_TP_NONE) { tp_rank = 0; tp_size = 1; }
+    if (tp_size < 1 || tp_rank < 0 || tp_rank >= tp_size) return fail("create: bad tp_rank / tp_size");
+    if (check_shape(out_features, in_features, group_size)) return 1;
+    int64_t K = in_features, N = out_features, k_off = 0, n_off = 0;
+    if (tp_mode == W4A16_TP_COLUMN) {
+        if (N % tp_size) return fail("create: out_features not divisible by tp_size");
+        N /= tp_size; n_off = tp_rank * N;
+    } else if (tp_mode == W4A16_TP_ROW) {
+        if (K % tp_size) return fail("create: in_features not divisible by tp_size");
+        K /= tp_size; k_off = tp_rank * K;
+        if (group_size > 0 && K % group_size) return fail("create: row shard is not a whole number of groups");
+    }
+    if (check_shape(N, K, group_size)) {  // the shard itself must pass the gate (SURVEY 8d gate check)
+        set_error(std::string("create: shard fails the shape gate: ") + w4a16_last_error());
+        return 1;
+    }
+    DeviceScratch *ds = nullptr;
+    if (get_device_scratch(device, &ds)) return 1;
+    DeviceGuard guard(device);
+    Linear *L = new Linear();
+    L->K_full = in_features; L->N_full = out_features; L->group_size_cfg = group_size;
+    L->format = format; L->has_bias = has_bias != 0; L->device = device;
+    L->tp_mode = tp_mode; L->tp_rank = tp_rank; L->tp_size = tp_size;
+    L->k_off = k_off; L->n_off = n_off; L->scratch = ds;
+    L->d.K = K; L->d.N = N; L->d.gs = group_size > 0 ? group_size : (int)K;
+    L->d.KB = K / CHUNK_K; L->d.NR = N / CHUNK_N; L->d.G = K / L->d.gs;
+    auto bail = [&](const std::string &m) { free_linear(L); return fail(m); };
+#define W4_ALLOC(ptr, bytes)                                                                     \
+    do {                                                                                         \
+        cudaError_t _e = cudaMalloc(reinterpret_cast<void **>(&(ptr)), (bytes));                 \
+        if (_e != cudaSuccess) return bail(std::string("cudaMalloc: ") + cudaGetErrorString(_e)); \
+    } while (0)
+    W4_ALLOC(L->qw, (size_t)qw_bytes(L->d));
+    W4_ALLOC(L->meta, (size_t)meta_bytes(L->d));
+    if (L->has_bias) W4_ALLOC(L->bias, (size_t)N * 2);
+    int64_t sf = 0, nt = 0;
+    decode_scratch_need(*L, ds->sm_count, &sf, &nt);
+    W4_ALLOC(L->tickets, (size_t)nt * 4);
+    if (cudaMemset(L->tickets, 0, (size_t)nt * 4) != cudaSuccess) return bail("cudaMemset(tickets) failed");
+    if (sf > 0) { W4_ALLOC(L->splitk_scratch, (size_t)sf * 4); L->splitk_floats = sf; }
+#undef W4_ALLOC
+    *out = reinterpret_cast<w4a16_handle_t>(L);
+    return 0;
+}
+
+int w4a16_create(w4a16_handle_t *out, int64_t in_features, int64_t out_features, int group_size, int format,
+                 int has_bias, int device) {
+    return w4a16_create_shard(out, in_features, out_features, group_size, format, has_bias, device,
+                              W4A16_TP_NONE, 0, 1);
+}
+
+int w4a16_destroy(w4a16_handle_t h) {
+    free_linear(reinterpret_cast<Linear *>(h));
+    return 0;
+}
+
+static int load_common(Linear *L, int format_expected_min, int format_expected_max, const uint32_t *qweight,
+                       const uint32_t *qzeros, const void *scales, int scales_dtype, const int32_t *perm_dev,
+                       const int32_t *grp_dev, cudaStream_t stream) {
+    if (L->format < format_expected_min || L->format > format_expected_max)
+        return fail("load_weights: handle was created for a different checkpoint format");
+    if (!qweight) return fail("load_weights: missing 'qweight'");
+    if (!scales) return fail("load_weights: missing 'scales'");
+    if (L->format != W4A16_FORMAT_GPTQ_SYM && !qzeros) return fail("load_weights: missing 'qzeros'");
+    if (scales_dtype < W4A16_DTYPE_F16 || scales_dtype > W4A16_DTYPE_F32) return fail("load_weights: bad scales dtype");
+    RepackSrc src;
+    src.qweight = qweight; src.qzeros = qzeros; src.scales = scales; src.scales_dtype = scales_dtype;
+    src.format = L->format; src.K_full = L->K_full; src.N_full = L->N_full;
+    src.gs = L->group_size_cfg > 0 ? L->group_size_cfg : (int)L->K_full;
+    src.G_full = L->K_full / src.gs;
+    src.k_off = L->k_off; src.n_off = L->n_off;
+    src.perm = perm_dev; src.row_group = grp_dev;
+    return launch_repack(*L, src, stream);
+}
+
+int w4a16_load_awq(w4a16_handle_t h, const uint32_t *qweight, const uint32_t *qzeros, const void *scales,
+                   int scales_dtype, const void *bias, int bias_dtype, w4a16_stream_t stream) {
+    Linear *L = reinterpret_cast<Linear *>(h);
+    if (!L) return fail("load_awq: null handle");
+    DeviceGuard g(L->device);
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (load_common(L, W4A16_FORMAT_AWQ, W4A16_FORMAT_AWQ, qweight, qzeros, scales, scales_dtype, nullptr, nullptr, s))
+        return 1;
+    return finish_load(L, bias, bias_dtype, s);
+}
+
+int w4a16_load_gptq(w4a16_handle_t h, const uint32_t *qweight, const uint32_t *qzeros, const void *scales,
+                    int scales_dtype, const int32_t *g_idx, const void *bias, int bias_dtype,
+                    w4a16_stream_t stream) {
+    Linear *L = reinterpret_cast<Linear *>(h);
+    if (!L) return fail("load_gptq: null handle");
+    DeviceGuard g(L->device);
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    const int32_t *perm_dev = nullptr, *grp_dev = nullptr;
+    if (g_idx) {
+        if (L->tp_mode == W4A16_TP_ROW)
+            return fail("load_gptq: act-order (g_idx) with a ROW shard needs a global K permutation before sharding; not supported");
+        const int64_t K = L->d.K;
+        const int gs = L->d.gs;
+        const int64_t G = L->d.G;
+        std::vector<int32_t> gi((size_t)K);
+        W4_CUDA_OK(cudaMemcpyAsync(gi.data(), g_idx, (size_t)K * 4, cudaMemcpyDeviceToHost, s));
+        W4_CUDA_OK(cudaStreamSynchronize(s));
+        bool trivial = true;
+        for (int64_t k = 0; k < K; ++k) {
+            if (gi[k] < 0 || gi[k] >= G) return fail("load_gptq: g_idx entry out of range");
+            if (gi[k] != k / gs) trivial = false;
+        }
+        if (!trivial) {
+            // stable sort of the rows by group: tiled row i <- checkpoint row perm[i]
+            std::vector<int32_t> perm((size_t)K + (size_t)G);
+            std::vector<int64_t> count((size_t)G, 0);
+            for (int64_t k = 0; k < K; ++k) ++count[gi[k]];
+            for (int64_t gg = 0; gg < G; ++gg)
+                if (count[gg] != gs) return fail("load_gptq: g_idx must assign exactly group_size rows to every group");
+            std::vector<int64_t> next((size_t)G);
+            for (int64_t gg = 0; gg < G; ++gg) next[gg] = gg * gs;
+            for (int64_t k = 0; k < K; ++k) perm[next[gi[k]]++] = (int32_t)k;
+            for (int64_t gg = 0; gg < G; ++gg) perm[K + gg] = (int32_t)gg;  // sorted block gg is checkpoint group gg
+            cudaFree(L->perm); L->perm = nullptr;
+            W4_CUDA_OK(cudaMalloc(&L->perm, perm.size() * 4));
+            W4_CUDA_OK(cudaMemcpyAsync(L->perm, perm.data(), perm.size() * 4, cudaMemcpyHostToDevice, s));
+            W4_CUDA_OK(cudaStreamSynchronize(s));  // perm is a local; the copy must finish before it dies
+            perm_dev = L->perm; grp_dev = L->perm + K;
+        }
+    }
+    if (load_common(L, W4A16_FORMAT_GPTQ_ZP, W4A16_FORMAT_GPTQ_SYM, qweight, qzeros, scales, scales_dtype, perm_dev,
+                    grp_dev, s))
+        return 1;
+    return finish_load(L, bias, bias_dtype, s);
+}
+
+int w4a16_forward_into(w4a16_handle_t h, const void *x_bf16, void *y_bf16, int64_t M, w4a16_stream_t stream) {
+    Linear *L = reinterpret_cast<Linear *>(h);
+    if (!L) return fail("forward: null handle");
+    DeviceGuard g(L->device);
+    // a ROW shard returns its partial sum without bias (bias is added after the reduce)
+    bool add_bias = L->tp_mode != W4A16_TP_ROW || L->tp_size == 1;
+    return forward_local(L, reinterpret_cast<const __nv_bfloat16 *>(x_bf16), reinterpret_cast<__nv_bfloat16 *>(y_bf16),
+                         M, add_bias, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int w4a16_forward_host(w4a16_handle_t h, const void *x_host, void *y_host, int64_t M, w4a16_stream_t stream) {
+    Linear *L = reinterpret_cast<Linear *>(h);
+    if (!L) return fail("forward_host: null handle");
+    if (M < 1) return fail("forward_host: M must be >= 1");
+    DeviceGuard g(L->device);
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (ensure_stage(L, M)) return 1;
+    W4_CUDA_OK(cudaMemcpyAsync(L->stage_x, x_host, (size_t)M * L->d.K * 2, cudaMemcpyHostToDevice, s));
+    if (w4a16_forward_into(h, L->stage_x, L->stage_y, M, stream)) return 1;
+    W4_CUDA_OK(cudaMemcpyAsync(y_host, L->stage_y, (size_t)M * L->d.N * 2, cudaMemcpyDeviceToHost, s));
+    W4_CUDA_OK(cudaStreamSynchronize(s));
+    return 0;
+}
+
+int w4a16_forward_row_allreduce(w4a16_handle_t h, const void *x_bf16, void *y_bf16, int64_t M, w4a16_comm_t comm,
+                                w4a16_stream_t stream) {
+    Linear *L = reinterpret_cast<Linear *>(h);
+    if (!L) return fail("forward_row_allreduce: null handle");
+    DeviceGuard g(L->device);
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    const bool single = L->tp_size == 1 || L->tp_mode != W4A16_TP_ROW;
+    if (single)  // world-size-1 short-circuit (nccl.rs:1339-1341)
+        return forward_local(L, reinterpret_cast<const __nv_bfloat16 *>(x_bf16),
+                             reinterpret_cast<__nv_bfloat16 *>(y_bf16), M, true, s);
+    if (!comm) return fail("forward_row_allreduce: null communicator for tp_size > 1");
+    if (nccl_load()) return 1;
+    if (forward_local(L, reinterpret_cast<const __nv_bfloat16 *>(x_bf16), reinterpret_cast<__nv_bfloat16 *>(y_bf16), M,
+                      false, s))
+        return 1;
+    if (nccl_check(g_nccl.AllReduce(y_bf16, y_bf16, (size_t)M * L->d.N, NCCL_BF16, NCCL_SUM, comm, s), "ncclAllReduce"))
+        return 1;
+    if (L->has_bias) return launch_add_bias(reinterpret_cast<__nv_bfloat16 *>(y_bf16), L->bias, M, L->d.N, s);
+    return 0;
+}
+
+int w4a16_nccl_unique_id(void *unique_id_out) {
+    if (!unique_id_out) return fail("nccl_unique_id: null buffer");
+    if (nccl_load()) return 1;
+    return nccl_check(g_nccl.GetUniqueId(unique_id_out), "ncclGetUniqueId");
+}
+int w4a16_nccl_comm_init(w4a16_comm_t *comm_out, int world_size, const void *unique_id, int rank) {
+    if (!comm_out || !unique_id) return fail("nccl_comm_init: null argument");
+    if (nccl_load()) return 1;
+    UniqueId id;
+    memcpy(&id, unique_id, sizeof(id));
+    void *c = nullptr;
+    if (nccl_check(g_nccl.CommInitRank(&c, world_size, id, rank), "ncclCommInitRank")) return 1;
+    *comm_out = c;
+    return 0;
+}
+int w4a16_nccl_comm_destroy(w4a16_comm_t comm) {
+    if (!comm) return 0;
+    if (nccl_load()) return 1;
+    return nccl_check(g_nccl.CommDestroy(comm), "ncclCommDestroy");
+}
+
+int w4a16_reserve(w4a16_handle_t h, int64_t max_tokens) {
+    Linear *L = reinterpret_cast<Linear *>(h);
+    if (!L) return fail("reserve: null handle");
+    if (max_tokens < 1) return fail("reserve: max_tokens must be >= 1");
+    DeviceGuard g(L->device);
+    if (ensure_gather(L, max_tokens)) return 1;
+    return ensure_stage(L, max_tokens);
+}
+
+int w4a16_dequant_into(w4a16_handle_t h, void *w_bf16, w4a16_stream_t stream) {
+    Linear *L = reinterpret_cast<Linear *>(h);
+    if (!L || !L->loaded) return fail("dequant_into: weights not loaded");
+    DeviceGuard g(L->device);
+    return launch_dequant(*L, reinterpret_cast<__nv_bfloat16 *>(w_bf16), reinterpret_cast<cudaStream_t>(stream));
+}
+int w4a16_unpack_into(w4a16_handle_t h, uint8_t *q, uint8_t *z, w4a16_stream_t stream) {
+    Linear *L = reinterpret_cast<Linear *>(h);
+    if (!L || !L->loaded) return fail("unpack_into: weights not loaded");
+    DeviceGuard g(L->device);
+    return launch_unpack(*L, q, z, reinterpret_cast<cudaStream_t>(stream));
+}
+int w4a16_scales_into(w4a16_handle_t h, void *scales_bf16, w4a16_stream_t stream) {
+    Linear *L = reinterpret_cast<Linear *>(h);
+    if (!L || !L->loaded) return fail("scales_into: weights not loaded");
+    DeviceGuard g(L->device);
+    return launch_scales_out(*L, reinterpret_cast<__nv_bfloat16 *>(scales_bf16), reinterpret_cast<cudaStream_t>(stream));
+}
+
+int64_t w4a16_in_features(w4a16_handle_t h) { return h ? reinterpret_cast<Linear *>(h)->d.K : -1; }
+int64_t w4a16_out_features(w4a16_handle_t h) { return h ? reinterpret_cast<Linear *>(h)->d.N : -1; }
+int w4a16_has_bias(w4a16_handle_t h) { return h ? (int)reinterpret_cast<Linear *>(h)->has_bias : 0; }
+int64_t w4a16_weight_bytes(w4a16_handle_t h) {
+    if (!h) return -1;
+    Linear *L = reinterpret_cast<Linear *>(h);
+    return qw_bytes(L->d) + meta_bytes(L->d);
+}
+const char *w4a16_kernel_for(w4a16_handle_t h, int64_t M) {
+    (void)h;
+    bool want_prefill = g_dispatch == "prefill" || (g_dispatch == "auto" && M > DECODE_MAX_M);
+    if (want_prefill && prefill_available()) return "prefill_umma";
+    return decode_kernel_name(std::min<int64_t>(M, DECODE_MAX_M));
+}
+int w4a16_set_dispatch(const char *mode) {
+    if (!mode) return fail("set_dispatch: null mode");
+    std::string m(mode);
+    if (m != "auto" && m != "decode" && m != "prefill") return fail("set_dispatch: unknown mode '" + m + "'");
+    g_dispatch = m;
+    return 0;
+}
+
+}  // extern "C"

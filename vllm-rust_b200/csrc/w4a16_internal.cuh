@@ -26,13 +26,8 @@ int fail(const std::string &msg);  // sets the error, returns 1
 extern std::atomic<uint64_t> g_kernel_launches;
 inline void count_launch() { g_kernel_launches.fetch_add(1, std::memory_order_relaxed); }
 
-// ---- per-device shared scratch (split-K partial sums) ------------------------
-// Forwards on one device are stream-ordered by the single engine task in the
-// reference (engine/output_pool.rs:40-43); the partial-sum scratch is therefore
-// per device, not per handle.  Tile tickets are per handle.
+// ---- per-device facts ----------------------------------------------------------
 struct DeviceScratch {
-    float *partials = nullptr;
-    size_t partial_bytes = 0;
     int sm_count = 0;
     int cc_major = 0, cc_minor = 0;
 };
@@ -56,6 +51,8 @@ struct Linear {
     __nv_bfloat16 *bias = nullptr; // [N] or null
     int32_t *perm = nullptr;       // act-order: tiled row i holds checkpoint row perm[i]; null otherwise
     int32_t *tickets = nullptr;    // [NR] split-K arrival counters (self-resetting)
+    float *splitk_scratch = nullptr;  // [SC][32][N] fp32 partials when the decode kernel splits K over CTAs
+    int64_t splitk_floats = 0;
     bool loaded = false;
     // scratch that scales with M
     __nv_bfloat16 *x_gather = nullptr;  // act-order gathered activations [cap, K]
@@ -92,6 +89,7 @@ int launch_add_bias(__nv_bfloat16 *y, const __nv_bfloat16 *bias, int64_t M, int6
 int launch_decode(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
                   cudaStream_t stream);
 const char *decode_kernel_name(int64_t M);
+int decode_scratch_need(const Linear &L, int sm_count, int64_t *scratch_floats, int64_t *tickets);
 // prefill (tcgen05): any M
 int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
                    cudaStream_t stream);

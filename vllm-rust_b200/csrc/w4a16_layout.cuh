@@ -12,11 +12,14 @@
 //
 // Chunk (R, kb), word (lane = g*4 + t, j), nibble i (bits 4i..4i+3) holds q[k][n] with
 //   n = 16R + g + 8*(i & 1)
-//   k = 64kb + 32*(j >> 1) + 8t + 4*(j & 1) + 2*((i >> 1) & 1) + (i >> 2)
+//   k = 64kb + 16j + 4t + 2*((i >> 1) & 1) + (i >> 2)
 // so that  ((word >> 4r) & 0x000F000F) | 0x43004300  is, for r = 0..3, exactly the
-// bf16x2 A-fragment register a_r of mma.m16n8k16 (value 128+q), with the 64 k of
-// a chunk permuted such that thread t's B-fragment registers for the four MMAs of a
-// chunk are two contiguous 16-byte pieces of the activation row.
+// bf16x2 A-fragment register a_r of mma.m16n8k16 (value 128+q) for the 16 k of word j
+// (k-slot s = 4t+{0,1,2,3} of that MMA is k = 16j + s: thread t's B fragment is one
+// contiguous 8-byte piece of the activation row), and at the same time the register
+// quadruple {r0,r2,r1,r3} of a tcgen05.st.16x256b fragment (row g cols 2t,2t+1; row g+8
+// cols 2t,2t+1), which is how the prefill kernel puts dequantised weights into TMEM
+// as the A operand of tcgen05.mma with NO k permutation of the activations.
 //
 // Meta block (R, grp), 48 bytes:
 //   [ 4g .. 4g+3 ]  bf16 scale of row 16R+g, bf16 scale of row 16R+g+8      (g = 0..7)
@@ -57,8 +60,8 @@ struct NibblePos { int64_t word; int shift; };
 W4_HD NibblePos nibble_pos(const Dims &d, int64_t k, int64_t n) {
     int64_t R = n >> 4; int r = (int)(n & 15); int g = r & 7; int i0 = r >> 3;
     int64_t kb = k >> 6; int kk = (int)(k & 63);
-    int jh = kk >> 5; int t = (kk & 31) >> 3; int jl = (kk & 7) >> 2; int i1 = (kk & 3) >> 1; int i2 = kk & 1;
-    int j = 2 * jh + jl; int i = i0 | (i1 << 1) | (i2 << 2);
+    int j = kk >> 4; int t = (kk & 15) >> 2; int i1 = (kk & 3) >> 1; int i2 = kk & 1;
+    int i = i0 | (i1 << 1) | (i2 << 2);
     int lane = g * 4 + t;
     NibblePos p;
     p.word = chunk_index(d, R, kb) * CHUNK_WORDS + lane * 4 + j;
@@ -70,7 +73,7 @@ W4_HD NibblePos nibble_pos(const Dims &d, int64_t k, int64_t n) {
 W4_HD void nibble_coord(int lane, int j, int i, int &k_in_chunk, int &n_in_chunk) {
     int g = lane >> 2, t = lane & 3;
     n_in_chunk = g + 8 * (i & 1);
-    k_in_chunk = 32 * (j >> 1) + 8 * t + 4 * (j & 1) + 2 * ((i >> 1) & 1) + (i >> 2);
+    k_in_chunk = 16 * j + 4 * t + 2 * ((i >> 1) & 1) + (i >> 2);
 }
 
 W4_HD int64_t meta_offset(const Dims &d, int64_t R, int64_t grp) { return (R * d.G + grp) * META_BYTES; }

@@ -1,0 +1,187 @@
+"""Tensor-parallel W4A16 linears: the composition the reference never executes
+(its Column/RowParallelLinear hold dense weights, distributed/parallel_layers.rs:36-324)
+built with the reference's own sharding and collective semantics:
+
+  column: rank r keeps output columns [r*N/tp, (r+1)*N/tp), no collective
+          (gather_output=false, distributed/attention.rs:76)
+  row   : rank r keeps input rows [r*K/tp, (r+1)*K/tp) and the matching group rows;
+          forward = local GEMM -> all_reduce(Sum) -> + bias   (parallel_layers.rs:275-313)
+
+DeviceCommunicator mirrors distributed/communicator.rs; NcclCommunicator is the
+library's dlopen'ed NCCL (nccl.rs:451-547, 1338-1364), bootstrapped from a 128-byte
+unique id broadcast out of band (distributed/launcher.rs:204-262; here over
+torch.distributed's store instead of raw TCP).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Tuple
+
+import torch
+
+from ._lib import W4A16Error, check, lib
+from .quantization import TP_COLUMN, TP_ROW, B200W4A16Linear, QuantizedLinear
+
+
+def shard_range(total: int, rank: int, world: int) -> Tuple[int, int]:
+    """[start, end) of rank's contiguous shard (parallel_layers.rs:62-70, 205-213)."""
+    if total % world:
+        raise ValueError(f"dimension {total} is not divisible by world size {world}")
+    per = total // world
+    return rank * per, (rank + 1) * per
+
+
+class DeviceCommunicator:
+    """distributed/communicator.rs DeviceCommunicator (the part this path uses)."""
+
+    def rank(self) -> int:
+        raise NotImplementedError
+
+    def world_size(self) -> int:
+        raise NotImplementedError
+
+    def all_reduce(self, t: torch.Tensor) -> torch.Tensor:
+        raise NotImplementedError
+
+    def nccl_comm(self) -> Optional[int]:
+        return None
+
+
+class MockCommunicator(DeviceCommunicator):
+    """communicator.rs:100-236: all_reduce is the identity."""
+
+    def __init__(self, rank: int = 0, world_size: int = 1):
+        self._r, self._w = rank, world_size
+
+    def rank(self):
+        return self._r
+
+    def world_size(self):
+        return self._w
+
+    def all_reduce(self, t):
+        return t
+
+
+class TorchDistCommunicator(DeviceCommunicator):
+    """all_reduce(Sum) through torch.distributed (gloo on CPU for the host-logic tests)."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+        self._dist, self._group = dist, group
+
+    def rank(self):
+        return self._dist.get_rank(self._group)
+
+    def world_size(self):
+        return self._dist.get_world_size(self._group)
+
+    def all_reduce(self, t):
+        self._dist.all_reduce(t, op=self._dist.ReduceOp.SUM, group=self._group)
+        return t
+
+
+class NcclCommunicator(DeviceCommunicator):
+    """ncclComm_t owned by libw4a16_b200.so; the id travels over torch.distributed."""
+
+    def __init__(self, rank: int, world_size: int, device: int, unique_id: Optional[bytes] = None):
+        self._r, self._w = rank, world_size
+        self._comm = ctypes.c_void_p()
+        if unique_id is None:
+            import torch.distributed as dist
+            buf = torch.zeros(128, dtype=torch.uint8)
+            if rank == 0:
+                raw = (ctypes.c_char * 128)()
+                check(lib().w4a16_nccl_unique_id(ctypes.cast(raw, ctypes.c_void_p)))
+                buf = torch.frombuffer(bytearray(raw.raw), dtype=torch.uint8).clone()
+            if dist.get_backend() == "nccl":
+                buf = buf.cuda(device)
+            dist.broadcast(buf, src=0)
+            unique_id = bytes(buf.cpu().tolist())
+        raw = (ctypes.c_char * 128).from_buffer_copy(unique_id)
+        with torch.cuda.device(device):
+            check(lib().w4a16_nccl_comm_init(ctypes.byref(self._comm), world_size, ctypes.cast(raw, ctypes.c_void_p), rank))
+
+    def rank(self):
+        return self._r
+
+    def world_size(self):
+        return self._w
+
+    def nccl_comm(self):
+        return self._comm.value
+
+    def all_reduce(self, t):
+        raise W4A16Error("NcclCommunicator reduces inside w4a16_forward_row_allreduce; use RowParallelW4A16Linear")
+
+    def destroy(self):
+        if self._comm:
+            lib().w4a16_nccl_comm_destroy(self._comm)
+            self._comm = ctypes.c_void_p()
+
+
+class ColumnParallelW4A16Linear(QuantizedLinear):
+    """ColumnParallelLinear (parallel_layers.rs:36-170) over a W4A16 shard; gather_output=false."""
+
+    def __init__(self, config, in_features: int, out_features: int, bias: bool, comm: DeviceCommunicator, device):
+        self.comm = comm
+        self.inner: B200W4A16Linear = config.create_linear(
+            in_features, out_features, bias, device, tp_mode=TP_COLUMN, tp_rank=comm.rank(), tp_size=comm.world_size())
+
+    def load_weights(self, weights):
+        self.inner.load_weights(weights)  # FULL checkpoint tensors; the shard reads its slice
+
+    def forward(self, x):
+        return self.inner.forward(x)
+
+    def forward_into(self, x2, y):
+        self.inner.forward_into(x2, y)
+
+    def in_features(self):
+        return self.inner.in_features()
+
+    def out_features(self):
+        return self.inner.out_features()
+
+    def has_bias(self):
+        return self.inner.has_bias()
+
+    def weight_dtype(self):
+        return self.inner.weight_dtype()
+
+
+class RowParallelW4A16Linear(QuantizedLinear):
+    """RowParallelLinear (parallel_layers.rs:181-324): local GEMM, all_reduce(Sum), + bias."""
+
+    def __init__(self, config, in_features: int, out_features: int, bias: bool, comm: DeviceCommunicator, device):
+        self.comm = comm
+        self.inner: B200W4A16Linear = config.create_linear(
+            in_features, out_features, bias, device, tp_mode=TP_ROW, tp_rank=comm.rank(), tp_size=comm.world_size())
+
+    def load_weights(self, weights):
+        self.inner.load_weights(weights)
+
+    def forward(self, x):
+        self.inner._check_x(x)
+        lead = x.shape[:-1]
+        x2 = x.contiguous().view(-1, x.shape[-1])
+        y = torch.empty((x2.shape[0], self.out_features()), dtype=torch.bfloat16, device=x.device)
+        self.forward_into(x2, y)
+        return y.view(*lead, self.out_features())
+
+    def forward_into(self, x2, y):
+        if self.comm.world_size() > 1 and self.comm.nccl_comm() is None:
+            raise W4A16Error("RowParallelW4A16Linear needs an NcclCommunicator for world_size > 1")
+        self.inner.forward_row_allreduce(x2, y, self.comm.nccl_comm())
+
+    def in_features(self):
+        return self.inner.in_features()
+
+    def out_features(self):
+        return self.inner.out_features()
+
+    def has_bias(self):
+        return self.inner.has_bias()
+
+    def weight_dtype(self):
+        return self.inner.weight_dtype()

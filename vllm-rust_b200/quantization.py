@@ -1,0 +1,540 @@
+"""Host-side mirror of vllm-rust's W4A16 quantization API over libw4a16_b200.so.
+
+Reference interfaces mirrored (paths under crates/core/src/quantization/):
+  trait QuantizationConfig          config.rs:110-135
+  trait QuantizedLinear             config.rs:147-190
+  AwqConfig / AwqVersion            awq.rs:170-393
+  AwqMarlinConfig                   awq_marlin.rs:38-114
+  MarlinConfig / MarlinScalarType   marlin.rs:52-266
+  GptqConfig                        gptq.rs:28-246
+  check_marlin_supports_shape       marlin.rs:308-341
+  AwqWeightLoader / GptqWeightLoader / create_weight_loader_with_params
+                                    weight_loader.rs:253-317, 596-714, 1596-1706
+  detect_from_json                  detection.rs:240-262
+
+Same names, argument meaning and error behaviour; the tensors are torch CUDA
+tensors (device memory + streams only -- every computation is a kernel of the
+library).  There is no CPU fallback: shapes outside the Marlin gate, which the
+reference routes to its CPU-dequant AwqLinear (awq.rs:384-393), raise here.
+"""
+from __future__ import annotations
+
+import ctypes
+import enum
+from dataclasses import dataclass, field
+from typing import Dict, Mapping, Optional, Sequence
+
+import torch
+
+from ._lib import W4A16Error, check, lib
+
+GPTQ_MARLIN_MIN_THREAD_N = 64   # marlin.rs:41
+GPTQ_MARLIN_MIN_THREAD_K = 128  # marlin.rs:43
+MARLIN_SUPPORTED_GROUP_SIZES = (-1, 32, 64, 128)  # marlin.rs:48
+
+FORMAT_AWQ, FORMAT_GPTQ_ZP, FORMAT_GPTQ_SYM = 0, 1, 2
+DTYPE_CODE = {torch.float16: 0, torch.bfloat16: 1, torch.float32: 2}
+TP_NONE, TP_COLUMN, TP_ROW = 0, 1, 2
+
+
+class QuantizationMethod(enum.Enum):  # quantization/config.rs QuantizationMethod (the W4A16 members)
+    NONE = "none"
+    AWQ = "awq"
+    AWQ_MARLIN = "awq_marlin"
+    GPTQ = "gptq"
+    MARLIN = "marlin"  # "gptq_marlin" routes here (detection.rs:258)
+
+
+class MarlinScalarType(enum.Enum):  # marlin.rs:52-84
+    UINT4B8 = "uint4b8"  # symmetric, W = (q - 8) * s
+    UINT4 = "uint4"      # runtime zero point (AWQ)
+
+    def bits(self) -> int:
+        return 4
+
+    def has_zero_point(self) -> bool:
+        return self is MarlinScalarType.UINT4
+
+    def pack_factor(self) -> int:
+        return 8
+
+
+def check_marlin_supports_shape(output_size: int, input_size: int, group_size: int) -> None:
+    """marlin.rs:308-341.  Raises ValueError with the reference's wording."""
+    if output_size % GPTQ_MARLIN_MIN_THREAD_N:
+        raise ValueError(f"Marlin requires output_size ({output_size}) to be divisible by "
+                         f"{GPTQ_MARLIN_MIN_THREAD_N} (GPTQ_MARLIN_MIN_THREAD_N)")
+    if input_size % GPTQ_MARLIN_MIN_THREAD_K:
+        raise ValueError(f"Marlin requires input_size ({input_size}) to be divisible by "
+                         f"{GPTQ_MARLIN_MIN_THREAD_K} (GPTQ_MARLIN_MIN_THREAD_K)")
+    if group_size > 0 and input_size % group_size:
+        raise ValueError(f"Marlin requires input_size ({input_size}) to be divisible by group_size ({group_size})")
+
+
+class QuantizedLinear:
+    """config.rs:147-190."""
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        raise NotImplementedError
+
+    def load_weights(self, weights: Mapping[str, torch.Tensor]) -> None:
+        raise NotImplementedError
+
+    def weight_dtype(self) -> torch.dtype:
+        raise NotImplementedError
+
+    def in_features(self) -> int:
+        raise NotImplementedError
+
+    def out_features(self) -> int:
+        raise NotImplementedError
+
+    def has_bias(self) -> bool:
+        raise NotImplementedError
+
+
+class QuantizationConfig:
+    """config.rs:110-135."""
+
+    def method(self) -> QuantizationMethod:
+        raise NotImplementedError
+
+    def supported_act_dtypes(self) -> Sequence[torch.dtype]:
+        return (torch.bfloat16,)
+
+    def min_capability(self) -> int:
+        return 100  # sm_100a only
+
+    def is_layer_skipped(self, layer_name: str) -> bool:
+        return False
+
+    def create_linear(self, in_features: int, out_features: int, bias: bool, device) -> QuantizedLinear:
+        raise NotImplementedError
+
+
+def _stream_ptr(x: Optional[torch.Tensor] = None) -> int:
+    return torch.cuda.current_stream(x.device if x is not None else None).cuda_stream
+
+
+def _device_index(device) -> int:
+    d = torch.device(device)
+    if d.type != "cuda":
+        raise W4A16Error(f"B200W4A16Linear needs a CUDA device, got '{d}' (there is no CPU fallback)")
+    return d.index if d.index is not None else torch.cuda.current_device()
+
+
+class B200W4A16Linear(QuantizedLinear):
+    """The drop-in for AwqMarlinLinear (awq_marlin.rs:431-667), MarlinLinear
+    (marlin.rs:586-778) and GptqLinear (gptq.rs:254-471) on sm_100a."""
+
+    def __init__(self, in_features: int, out_features: int, bias: bool, group_size: int, fmt: int, device,
+                 tp_mode: int = TP_NONE, tp_rank: int = 0, tp_size: int = 1):
+        self._h = ctypes.c_void_p()
+        self._device = torch.device("cuda", _device_index(device))
+        check(lib().w4a16_create_shard(ctypes.byref(self._h), in_features, out_features, group_size, fmt,
+                                       int(bias), self._device.index, tp_mode, tp_rank, tp_size))
+        self._full = (in_features, out_features)
+        self._fmt = fmt
+        self._loaded = False
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            try:
+                lib().w4a16_destroy(h)
+            except Exception:
+                pass
+            self._h = None
+
+    # -- trait surface ---------------------------------------------------------------
+    def in_features(self) -> int:
+        return int(lib().w4a16_in_features(self._h))
+
+    def out_features(self) -> int:
+        return int(lib().w4a16_out_features(self._h))
+
+    def has_bias(self) -> bool:
+        return bool(lib().w4a16_has_bias(self._h))
+
+    def weight_dtype(self) -> torch.dtype:
+        return torch.int32  # DType::U32 in the reference (awq_marlin.rs weight_dtype); torch has no stable u32
+
+    def weight_bytes(self) -> int:
+        return int(lib().w4a16_weight_bytes(self._h))
+
+    def kernel_for(self, m: int) -> str:
+        return lib().w4a16_kernel_for(self._h, m).decode()
+
+    def load_weights(self, weights: Mapping[str, torch.Tensor]) -> None:
+        """Keys "qweight", "qzeros", "scales", "bias", "g_idx" in CHECKPOINT layout
+        (awq_marlin.rs:592-664, gptq.rs:435-454); the repack runs inside."""
+        def need(key):
+            t = weights.get(key)
+            if t is None:
+                raise W4A16Error(f"Missing '{key}' in weights")  # awq_marlin.rs:593-598 wording
+            return t
+
+        def dev(t, dtype=None):
+            if t is None:
+                return None
+            if dtype is not None and t.dtype != dtype:
+                if t.dtype.itemsize != 4 or t.dtype.is_floating_point:
+                    raise W4A16Error(f"packed tensor must be a 32-bit integer type, got {t.dtype}")
+                t = t.view(dtype)  # checkpoints hold the packed words as I32 / U32: same bits
+            return t.to(self._device).contiguous()
+
+        kf, nf = self._full
+        qweight = dev(need("qweight"), torch.int32)
+        scales = dev(need("scales"))
+        if scales.dtype not in DTYPE_CODE:
+            raise W4A16Error(f"scales dtype {scales.dtype} not supported")
+        qzeros = dev(weights.get("qzeros"), torch.int32)
+        bias = dev(weights.get("bias"))
+        if bias is not None and bias.dtype not in DTYPE_CODE:
+            raise W4A16Error(f"bias dtype {bias.dtype} not supported")
+        g = scales.shape[0]
+        exp_qw = (kf, nf // 8) if self._fmt == FORMAT_AWQ else (kf // 8, nf)
+        if tuple(qweight.shape) != exp_qw:
+            raise W4A16Error(f"qweight shape {tuple(qweight.shape)} != expected {exp_qw}")
+        if tuple(scales.shape) != (g, nf):
+            raise W4A16Error(f"scales shape {tuple(scales.shape)} != expected [{g}, {nf}]")
+        if qzeros is not None and tuple(qzeros.shape) != (g, nf // 8):
+            raise W4A16Error(f"qzeros shape {tuple(qzeros.shape)} != expected [{g}, {nf // 8}]")
+        ptr = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None  # noqa: E731
+        with torch.cuda.device(self._device):
+            s = _stream_ptr(qweight)
+            if self._fmt == FORMAT_AWQ:
+                if qzeros is None:
+                    raise W4A16Error("Missing 'qzeros' in weights")
+                check(lib().w4a16_load_awq(self._h, ptr(qweight), ptr(qzeros), ptr(scales), DTYPE_CODE[scales.dtype],
+                                           ptr(bias), DTYPE_CODE[bias.dtype] if bias is not None else 1, s))
+            else:
+                g_idx = dev(weights.get("g_idx"), torch.int32)
+                check(lib().w4a16_load_gptq(self._h, ptr(qweight), ptr(qzeros), ptr(scales),
+                                            DTYPE_CODE[scales.dtype], ptr(g_idx), ptr(bias),
+                                            DTYPE_CODE[bias.dtype] if bias is not None else 1, s))
+            # the checkpoint tensors are locals: keep them alive until the repack has run
+            torch.cuda.current_stream().synchronize()
+        self._loaded = True
+
+    def _check_x(self, x: torch.Tensor):
+        if not x.is_cuda:
+            raise W4A16Error("forward: input must be a CUDA tensor (there is no CPU fallback)")
+        if x.dtype != torch.bfloat16:
+            # marlin_cuda.rs:138-146, 492-495: the GPU path takes BF16 only
+            raise W4A16Error(f"forward: input dtype must be BF16, got {x.dtype}")
+        if x.shape[-1] != self.in_features():
+            raise W4A16Error(f"forward: input last dim {x.shape[-1]} != in_features {self.in_features()}")
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        """config.rs:149.  Rank-2 or rank-3 input, leading dims flattened and restored
+        (awq_marlin.rs:545-571); x made contiguous first (marlin_cuda.rs:858-869)."""
+        self._check_x(x)
+        lead = x.shape[:-1]
+        x2 = x.contiguous().view(-1, x.shape[-1])
+        y = torch.empty((x2.shape[0], self.out_features()), dtype=torch.bfloat16, device=x.device)
+        self.forward_into(x2, y)
+        return y.view(*lead, self.out_features())
+
+    def forward_into(self, x2: torch.Tensor, y: torch.Tensor) -> None:
+        """Caller-owned output, no allocation, graph-capturable: the OutputPool contract
+        of marlin_gemm_pooled (marlin_cuda.rs:1655-1753) / forward_pooled (config.rs:167-174)."""
+        m = x2.shape[0]
+        if m < 1:
+            raise W4A16Error("forward: M must be >= 1")
+        check(lib().w4a16_forward_into(self._h, ctypes.c_void_p(x2.data_ptr()), ctypes.c_void_p(y.data_ptr()), m,
+                                       _stream_ptr(x2)))
+
+    def forward_host(self, x_host: torch.Tensor, y_host: torch.Tensor) -> None:
+        """End-to-end call with HOST (ideally pinned) buffers: H2D, forward, D2H, sync."""
+        with torch.cuda.device(self._device):
+            check(lib().w4a16_forward_host(self._h, ctypes.c_void_p(x_host.data_ptr()),
+                                           ctypes.c_void_p(y_host.data_ptr()), x_host.shape[0], _stream_ptr()))
+
+    def forward_row_allreduce(self, x2: torch.Tensor, y: torch.Tensor, comm_ptr: Optional[int]) -> None:
+        check(lib().w4a16_forward_row_allreduce(self._h, ctypes.c_void_p(x2.data_ptr()), ctypes.c_void_p(y.data_ptr()),
+                                                x2.shape[0], ctypes.c_void_p(comm_ptr or 0), _stream_ptr(x2)))
+
+    def reserve(self, max_tokens: int) -> None:
+        with torch.cuda.device(self._device):
+            check(lib().w4a16_reserve(self._h, max_tokens))
+
+    # -- parity hooks -------------------------------------------------------------------
+    def dequantize(self) -> torch.Tensor:
+        """Dense [K, N] bf16 on the D2 grid (awq_marlin_dequant.cu:45-68, gptq_dequant.cu:58-86)."""
+        w = torch.empty((self.in_features(), self.out_features()), dtype=torch.bfloat16, device=self._device)
+        with torch.cuda.device(self._device):
+            check(lib().w4a16_dequant_into(self._h, ctypes.c_void_p(w.data_ptr()), _stream_ptr(w)))
+        return w
+
+    def unpack(self):
+        k, n = self.in_features(), self.out_features()
+        g = self.weight_groups()
+        q = torch.empty((k, n), dtype=torch.uint8, device=self._device)
+        z = torch.empty((g, n), dtype=torch.uint8, device=self._device)
+        with torch.cuda.device(self._device):
+            check(lib().w4a16_unpack_into(self._h, ctypes.c_void_p(q.data_ptr()), ctypes.c_void_p(z.data_ptr()),
+                                          _stream_ptr(q)))
+        return q, z
+
+    def scales(self) -> torch.Tensor:
+        s = torch.empty((self.weight_groups(), self.out_features()), dtype=torch.bfloat16, device=self._device)
+        with torch.cuda.device(self._device):
+            check(lib().w4a16_scales_into(self._h, ctypes.c_void_p(s.data_ptr()), _stream_ptr(s)))
+        return s
+
+    def weight_groups(self) -> int:
+        gs = self._group_size
+        return 1 if gs <= 0 else self.in_features() // gs
+
+    _group_size = 128
+
+
+def _make_linear(in_features, out_features, bias, group_size, fmt, device, **tp) -> B200W4A16Linear:
+    lin = B200W4A16Linear(in_features, out_features, bias, group_size, fmt, device, **tp)
+    lin._group_size = group_size
+    return lin
+
+
+@dataclass
+class MarlinConfig(QuantizationConfig):
+    """marlin.rs:88-266."""
+    bits: int = 4
+    group_size: int = 128
+    desc_act: bool = False
+    is_sym: bool = True
+    scalar_type: MarlinScalarType = MarlinScalarType.UINT4B8
+    use_fp32_reduce: bool = True
+
+    @staticmethod
+    def gptq_int4(group_size: int) -> "MarlinConfig":
+        return MarlinConfig(4, group_size, False, True, MarlinScalarType.UINT4B8)
+
+    @staticmethod
+    def awq_int4(group_size: int) -> "MarlinConfig":
+        return MarlinConfig(4, group_size, False, False, MarlinScalarType.UINT4)
+
+    def method(self):
+        return QuantizationMethod.MARLIN
+
+    def create_linear(self, in_features, out_features, bias, device):
+        check_marlin_supports_shape(out_features, in_features, self.group_size)
+        fmt = FORMAT_GPTQ_SYM if self.scalar_type is MarlinScalarType.UINT4B8 else FORMAT_GPTQ_ZP
+        return _make_linear(in_features, out_features, bias, self.group_size, fmt, device)
+
+
+@dataclass
+class AwqConfig(QuantizationConfig):
+    """awq.rs:170-393."""
+    bits: int = 4
+    group_size: int = 128
+    zero_point: bool = True
+    version: str = "GEMM"
+    use_marlin: bool = True
+    modules_to_not_convert: list = field(default_factory=lambda: ["lm_head"])
+
+    @staticmethod
+    def int4(group_size: int) -> "AwqConfig":
+        return AwqConfig(4, group_size)
+
+    @staticmethod
+    def from_detected(bits, group_size, raw_config: Mapping) -> "AwqConfig":
+        bits = 4 if bits is None else bits
+        group_size = 128 if group_size is None else group_size
+        version = "GEMV" if raw_config.get("version") in ("GEMV", "gemv") else "GEMM"
+        mods = raw_config.get("modules_to_not_convert")
+        mods = ["lm_head"] if not isinstance(mods, list) else [m for m in mods if isinstance(m, str)]
+        return AwqConfig(bits, group_size, bool(raw_config.get("zero_point", True)), version,
+                         bool(raw_config.get("is_marlin_format", False)) or bits == 4, mods)
+
+    def method(self):
+        return QuantizationMethod.AWQ
+
+    def num_groups(self, in_features: int) -> int:
+        return 1 if self.group_size <= 0 else -(-in_features // self.group_size)
+
+    def can_use_marlin(self) -> bool:
+        return self.bits == 4 and self.group_size in MARLIN_SUPPORTED_GROUP_SIZES
+
+    def can_use_marlin_for_shape(self, in_features: int, out_features: int) -> bool:
+        if not self.can_use_marlin():
+            return False
+        try:
+            check_marlin_supports_shape(out_features, in_features, self.group_size)
+            return True
+        except ValueError:
+            return False
+
+    def to_marlin_config(self) -> Optional[MarlinConfig]:
+        return MarlinConfig.awq_int4(self.group_size) if self.can_use_marlin() else None
+
+    def is_layer_skipped(self, layer_name: str) -> bool:
+        return any(p in layer_name for p in self.modules_to_not_convert)
+
+    def create_linear(self, in_features, out_features, bias, device, **tp):
+        if self.use_marlin and self.can_use_marlin_for_shape(in_features, out_features):
+            return _make_linear(in_features, out_features, bias, self.group_size, FORMAT_AWQ, device, **tp)
+        raise W4A16Error(
+            f"AWQ layer {in_features}x{out_features} (bits={self.bits}, group_size={self.group_size}) is outside the "
+            "Marlin gate; the reference would fall back to its CPU-dequant AwqLinear (awq.rs:384-393), "
+            "the B200 path has no CPU fallback")
+
+
+@dataclass
+class AwqMarlinConfig(AwqConfig):
+    """awq_marlin.rs:38-114: same gate, method() reports AwqMarlin."""
+
+    def method(self):
+        return QuantizationMethod.AWQ_MARLIN
+
+
+@dataclass
+class GptqConfig(QuantizationConfig):
+    """gptq.rs:28-246."""
+    bits: int = 4
+    group_size: int = 128
+    desc_act: bool = False
+    sym: bool = True
+    damp_percent: float = 0.01
+    use_marlin: bool = True
+    # G1 vs G3 (SURVEY 8a hazard iii): the production loader builds GptqLinear, which uses the stored
+    # zero points (gptq_dequant.cu:58-86); GptqConfig::create_linear's Marlin route uses q-8.
+    use_stored_zeros: bool = True
+
+    @staticmethod
+    def int4(group_size: int) -> "GptqConfig":
+        return GptqConfig(4, group_size)
+
+    @staticmethod
+    def from_detected(bits, group_size, desc_act, raw_config: Mapping) -> "GptqConfig":
+        bits = 4 if bits is None else bits
+        return GptqConfig(bits, 128 if group_size is None else group_size, bool(desc_act),
+                          bool(raw_config.get("sym", True)), float(raw_config.get("damp_percent", 0.01)),
+                          bool(raw_config.get("is_marlin_format", False)) or bits == 4)
+
+    def method(self):
+        return QuantizationMethod.GPTQ
+
+    def create_linear(self, in_features, out_features, bias, device, **tp):
+        if self.bits != 4:
+            raise W4A16Error(f"GPTQ bits={self.bits}: only int4 is on the B200 W4A16 path")
+        check_marlin_supports_shape(out_features, in_features, self.group_size)
+        fmt = FORMAT_GPTQ_ZP if self.use_stored_zeros else FORMAT_GPTQ_SYM
+        return _make_linear(in_features, out_features, bias, self.group_size, fmt, device, **tp)
+
+
+# ---- detection (detection.rs:240-262) ------------------------------------------------
+_METHODS = {"awq": QuantizationMethod.AWQ, "awq_triton": QuantizationMethod.AWQ,
+            "awq_marlin": QuantizationMethod.AWQ_MARLIN, "gptq": QuantizationMethod.GPTQ,
+            "gptq_marlin": QuantizationMethod.MARLIN}
+
+
+@dataclass
+class DetectedQuantConfig:
+    method: QuantizationMethod = QuantizationMethod.NONE
+    bits: Optional[int] = None
+    group_size: Optional[int] = None
+    desc_act: Optional[bool] = None
+    raw_config: Dict = field(default_factory=dict)
+
+
+def detect_from_json(config: Mapping) -> DetectedQuantConfig:
+    qc = config.get("quantization_config")
+    if not isinstance(qc, Mapping):
+        return DetectedQuantConfig()
+    m = _METHODS.get(qc.get("quant_method"), QuantizationMethod.NONE)
+    return DetectedQuantConfig(m, qc.get("bits"), qc.get("group_size"), qc.get("desc_act"), dict(qc))
+
+
+def create_config(detected: DetectedQuantConfig) -> QuantizationConfig:
+    """quantization/mod.rs:135-213 for the W4A16 members."""
+    if detected.method is QuantizationMethod.AWQ:
+        return AwqConfig.from_detected(detected.bits, detected.group_size, detected.raw_config)
+    if detected.method is QuantizationMethod.AWQ_MARLIN:
+        c = AwqConfig.from_detected(detected.bits, detected.group_size, detected.raw_config)
+        return AwqMarlinConfig(c.bits, c.group_size, c.zero_point, c.version, c.use_marlin, c.modules_to_not_convert)
+    if detected.method in (QuantizationMethod.GPTQ, QuantizationMethod.MARLIN):
+        return GptqConfig.from_detected(detected.bits, detected.group_size, detected.desc_act, detected.raw_config)
+    raise W4A16Error(f"quantization method {detected.method} is not on the W4A16 path")
+
+
+# ---- weight loaders (weight_loader.rs) --------------------------------------------------
+class _Loader:
+    """`tensors` plays the VarBuilder: a mapping "prefix.name" -> tensor (any device)."""
+
+    def __init__(self, tensors: Mapping[str, torch.Tensor], config, device):
+        self.tensors, self.config, self._device = tensors, config, torch.device(device)
+
+    def device(self):
+        return self._device
+
+    def dtype(self):
+        return torch.bfloat16
+
+    def _get(self, prefix, name, shape, what):
+        t = self.tensors.get(f"{prefix}.{name}")
+        if t is None:
+            raise W4A16Error(f"{what} {name} load failed for {prefix} with expected shape {list(shape)}: missing tensor")
+        if tuple(t.shape) != tuple(shape):
+            raise W4A16Error(f"{what} {name} load failed for {prefix} with expected shape {list(shape)}: "
+                             f"got {list(t.shape)}")
+        return t
+
+
+class AwqWeightLoader(_Loader):
+    """weight_loader.rs:596-714."""
+
+    def method(self):
+        return QuantizationMethod.AWQ
+
+    def load_linear(self, prefix: str, in_features: int, out_features: int, bias: bool, **tp) -> QuantizedLinear:
+        if self.config.is_layer_skipped(prefix):
+            raise W4A16Error(f"{prefix} is in modules_to_not_convert: it is a dense layer, not on the W4A16 path")
+        packed_out = -(-out_features // 8)
+        g = self.config.num_groups(in_features)
+        w = {"qweight": self._get(prefix, "qweight", (in_features, packed_out), "AWQ"),
+             "scales": self._get(prefix, "scales", (g, out_features), "AWQ"),
+             "qzeros": self._get(prefix, "qzeros", (g, packed_out), "AWQ")}
+        if bias and f"{prefix}.bias" in self.tensors:
+            w["bias"] = self.tensors[f"{prefix}.bias"]
+        has_bias = "bias" in w
+        lin = self.config.create_linear(in_features, out_features, has_bias, self._device, **tp)
+        lin.load_weights(w)
+        return lin
+
+
+class GptqWeightLoader(_Loader):
+    """weight_loader.rs:253-317."""
+
+    def method(self):
+        return QuantizationMethod.GPTQ
+
+    def load_linear(self, prefix: str, in_features: int, out_features: int, bias: bool, **tp) -> QuantizedLinear:
+        gs = self.config.group_size
+        g = 1 if gs <= 0 else -(-in_features // gs)
+        w = {"qweight": self._get(prefix, "qweight", (in_features // 8, out_features), "GPTQ"),
+             "scales": self._get(prefix, "scales", (g, out_features), "GPTQ"),
+             "qzeros": self._get(prefix, "qzeros", (g, out_features // 8), "GPTQ")}
+        if self.config.desc_act and f"{prefix}.g_idx" in self.tensors:  # weight_loader.rs:301-306
+            w["g_idx"] = self.tensors[f"{prefix}.g_idx"]
+        if bias and f"{prefix}.bias" in self.tensors:
+            w["bias"] = self.tensors[f"{prefix}.bias"]
+        lin = self.config.create_linear(in_features, out_features, "bias" in w, self._device, **tp)
+        lin.load_weights(w)
+        return lin
+
+
+def create_weight_loader_with_params(tensors: Mapping[str, torch.Tensor], detected: DetectedQuantConfig, device):
+    """weight_loader.rs:1596-1706 for the W4A16 members."""
+    cfg = create_config(detected)
+    if isinstance(cfg, AwqConfig):
+        return AwqWeightLoader(tensors, cfg, device)
+    return GptqWeightLoader(tensors, cfg, device)
+
+
+def kernel_launches() -> int:
+    return int(lib().w4a16_kernel_launches())
+
+
+def set_dispatch(mode: str) -> None:
+    check(lib().w4a16_set_dispatch(mode.encode()))
