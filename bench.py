@@ -228,9 +228,10 @@ def run_gpu(args):
                        "algorithmic_bytes_per_launch": int(per_launch_bytes)}
     if rank == 0 and world == 1:
         out["per_shape"] = per_shape_decode(P, torch, dev, peaks, args)
-        out["prefill"] = prefill_point(P, torch, dev, peaks, args)
-        out["e2e"] = e2e_host(P, torch, dev, layers, args)
-        out["cpu_baseline"] = cpu_baseline(sample_layers=1, threads=None, reps=1)
+        if not args.quick:
+            out["prefill"] = prefill_point(P, torch, dev, peaks, args)
+            out["e2e"] = e2e_host(P, torch, dev, layers, args)
+            out["cpu_baseline"] = cpu_baseline(sample_layers=1, threads=None, reps=1)
     elif rank == 0:
         out["e2e"] = {"value": None, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
                       "note": "host-buffer path measured at N=1 only"}
@@ -260,21 +261,28 @@ def per_shape_decode(P, torch, dev, peaks, args):
         for M in (1, 8, 16, 32):
             x = torch.randn((M, K), device=dev).to(torch.bfloat16)
             y = torch.empty((M, N), device=dev, dtype=torch.bfloat16)
-            reps = max(1, 200 // copies)
-            for lin in lins:
-                lin.forward_into(x, y)
-            torch.cuda.synchronize()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            for _ in range(reps):
+            st = torch.cuda.Stream(dev)
+            with torch.cuda.stream(st):
                 for lin in lins:
                     lin.forward_into(x, y)
-            e1.record()
-            torch.cuda.synchronize()
+                graph = torch.cuda.CUDAGraph()  # one pass over all copies; replayed: no host launch cost in the timing
+                with torch.cuda.graph(graph, stream=st):
+                    for lin in lins:
+                        lin.forward_into(x, y)
+                reps = max(3, 400 // copies)
+                graph.replay()
+                st.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(st)
+                for _ in range(reps):
+                    graph.replay()
+                e1.record(st)
+                st.synchronize()
             us = e0.elapsed_time(e1) * 1e3 / (reps * copies)
             gbs = algo_bytes(M, K, N) / (us * 1e-6) / 1e9
             res.append({"shape": f"{name} {K}->{N}", "M": M, "us": round(us, 2), "GBps": round(gbs, 1),
-                        "frac_measured_hbm": round(gbs / peaks["hbm_gbs"], 3), "kernel": lins[0].kernel_for(M)})
+                        "frac_measured_hbm": round(gbs / peaks["hbm_gbs"], 3), "kernel": lins[0].kernel_for(M),
+                        "copies": copies})
         del lins
     return res
 
@@ -413,7 +421,8 @@ def main():
     ap.add_argument("--layers", type=int, default=0, help="override the number of decoder layers (debug)")
     ap.add_argument("--no-graph", dest="graph", action="store_false")
     ap.add_argument("--prefill-m", type=int, nargs="*", default=[64, 256, 1024, 4096])
-    ap.add_argument("--quick", action="store_true", help="skip per-shape / prefill / e2e / cpu legs")
+    ap.add_argument("--quick", action="store_true", help="skip prefill / e2e / cpu legs")
+    ap.add_argument("--only-shapes", action="store_true", help="per-shape decode sweep only")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3

@@ -28,7 +28,8 @@ namespace w4 {
 
 constexpr int DEC_THREADS = 256;
 constexpr int DEC_WARPS = 8;
-constexpr int DEC_DEPTH = 4;  // chunks per register-ring half
+constexpr int DEC_DEPTH = 2;   // 128-k units per register-ring half (ring = 2 halves = 8 chunks = 4 KB per warp)
+constexpr int UNIT_K = 128;    // the K granule of the decode kernel: 2 chunks; K % 128 == 0 by the shape gate
 
 struct DecodeParams {
     const uint4 *qw;
@@ -36,13 +37,13 @@ struct DecodeParams {
     const __nv_bfloat16 *bias;  // null: no bias add in this launch
     const __nv_bfloat16 *x;
     __nv_bfloat16 *y;
-    float *scratch;    // [SC][M][N] fp32 partials, SC > 1 only
+    float4 *scratch;   // [SC][NR][NT][32] fragment-layout fp32 partials, SC > 1 only
     int32_t *tickets;  // [gridDim.x]
     int M, K, N, KB, G;
-    int chunks_per_group_shift;  // gs >= 64: log2(gs/64); per-channel: 31 (every chunk -> group 0)
-    int wk_shift;                // log2(warps along K inside a CTA)
-    int sc;                      // CTAs along K
-    int cps;                     // chunks per slice
+    int meta_unit_stride;  // bytes of meta per 128-k unit: MPU * 48, or 0 for per-channel scales
+    int wk_shift;          // log2(warps along K inside a CTA)
+    int sc;                // CTAs along K
+    int ups;               // units per slice
 };
 
 __device__ __forceinline__ uint4 ldg_stream(const uint4 *p) {
@@ -61,79 +62,77 @@ __device__ __forceinline__ uint32_t ldg_stream_u8(const void *p) {
     asm volatile("ld.global.nc.L1::no_allocate.u8 %0, [%1];" : "=r"(r) : "l"(p));
     return r;
 }
+// D = A*B (+ C).  ZERO_C feeds literal zeros so ptxas uses RZ instead of clearing registers.
+template <bool ZERO_C>
 __device__ __forceinline__ void mma_bf16(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
                                          uint32_t b0, uint32_t b1) {
-    asm volatile(
-        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
-        "{%0,%1,%2,%3};"
-        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+    if (ZERO_C) {
+        asm volatile(
+            "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
+            "{%10,%10,%10,%10};"
+            : "=f"(c[0]), "=f"(c[1]), "=f"(c[2]), "=f"(c[3])
+            : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "f"(0.f));
+    } else {
+        asm volatile(
+            "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
+            "{%0,%1,%2,%3};"
+            : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+            : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+    }
 }
 
-// One prefetched chunk: 4 words of packed nibbles + the scale pair / zero byte of the
-// group(s) it belongs to.  GPC = groups per chunk (2 only for group_size 32).
-template <int GPC>
-struct Slot {
-    uint4 w;
-    uint32_t s2[GPC];
-    uint32_t zb[GPC];
+// One prefetched 128-k unit of one 16-row block: 2 chunks (8 words per lane) + the scale pair /
+// zero byte of each group inside it.  MPU = groups per unit: 1 (g=128 or per-channel), 2 (g=64), 4 (g=32).
+template <int MPU>
+struct Unit {
+    uint4 w[2];
+    uint32_t s2[MPU];
+    uint32_t zb[MPU];
 };
 
-template <int GPC>
-__device__ __forceinline__ void load_slot(Slot<GPC> &s, const DecodeParams &p, const uint4 *wrow,
-                                          const uint8_t *mrow, int kb, int kb_end, int lane) {
-    if (kb < kb_end) {
-        s.w = ldg_stream(wrow + (size_t)kb * 32 + lane);
-        const int g = lane >> 2;
+// wp: this lane's 16 bytes of the unit's first chunk.  ms / mz: this lane's scale pair / zero byte
+// of the unit's first group.  All offsets below are compile-time immediates.
+template <int MPU>
+__device__ __forceinline__ void load_unit(Unit<MPU> &u, const uint4 *wp, const uint8_t *ms, const uint8_t *mz) {
+    u.w[0] = ldg_stream(wp);
+    u.w[1] = ldg_stream(wp + 32);
 #pragma unroll
-        for (int h = 0; h < GPC; ++h) {
-            int grp = GPC == 2 ? kb * 2 + h : (kb >> p.chunks_per_group_shift);
-            const uint8_t *m = mrow + (size_t)grp * META_BYTES;
-            s.s2[h] = ldg_stream_u32(m + 4 * g);
-            s.zb[h] = ldg_stream_u8(m + META_ZERO_OFF + g);
-        }
-    } else {
-        s.w = make_uint4(0, 0, 0, 0);
-#pragma unroll
-        for (int h = 0; h < GPC; ++h) { s.s2[h] = 0; s.zb[h] = 0; }
+    for (int h = 0; h < MPU; ++h) {
+        u.s2[h] = ldg_stream_u32(ms + h * META_BYTES);
+        u.zb[h] = ldg_stream_u8(mz + h * META_BYTES);
     }
 }
 
-template <int NT, int GPC>
-__device__ __forceinline__ void compute_slot(const Slot<GPC> &s, const DecodeParams &p, int kb, int lane,
+template <int NT, int MPU>
+__device__ __forceinline__ void compute_unit(const Unit<MPU> &u, const __nv_bfloat16 *const (&xp)[NT],
                                              float (&yacc)[NT][4]) {
-    const int g = lane >> 2, t = lane & 3;
-    // B fragments: token 8nt+g, k = 64kb + 16j + 4t .. +3  (one 8-byte load through L1)
-    uint2 xb[NT][4];
+    // B fragments: token 8nt+g, k = 16*jm + 4t .. +3 of this unit (8-byte loads through L1)
+    uint2 xb[NT][8];
 #pragma unroll
-    for (int nt = 0; nt < NT; ++nt) {
-        int tok = nt * 8 + g;
-        const __nv_bfloat16 *xr = p.x + (size_t)tok * p.K + (size_t)kb * CHUNK_K + 4 * t;
+    for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-            xb[nt][j] = tok < p.M ? __ldg(reinterpret_cast<const uint2 *>(xr + 16 * j)) : make_uint2(0u, 0u);
-    }
-    const uint32_t wj[4] = {s.w.x, s.w.y, s.w.z, s.w.w};
+        for (int jm = 0; jm < 8; ++jm) xb[nt][jm] = __ldg(reinterpret_cast<const uint2 *>(xp[nt] + 16 * jm));
+    const uint32_t wj[8] = {u.w[0].x, u.w[0].y, u.w[0].z, u.w[0].w, u.w[1].x, u.w[1].y, u.w[1].z, u.w[1].w};
+    constexpr int MMAS_PER_GROUP = 8 / MPU;
 #pragma unroll
-    for (int h = 0; h < GPC; ++h) {
-        const uint32_t zlo = zero_magic(s.zb[h] & 0xFu), zhi = zero_magic(s.zb[h] >> 4);
+    for (int h = 0; h < MPU; ++h) {
+        const uint32_t zlo = zero_magic(u.zb[h] & 0xFu), zhi = zero_magic(u.zb[h] >> 4);
         float acc[NT][4];
 #pragma unroll
-        for (int nt = 0; nt < NT; ++nt)
-#pragma unroll
-            for (int i = 0; i < 4; ++i) acc[nt][i] = 0.f;
-#pragma unroll
-        for (int jj = 0; jj < 4 / GPC; ++jj) {
-            const int j = h * (4 / GPC) + jj;
-            const uint32_t w = wj[j];
+        for (int jj = 0; jj < MMAS_PER_GROUP; ++jj) {
+            const int jm = h * MMAS_PER_GROUP + jj;
+            const uint32_t w = wj[jm];
             const uint32_t a0 = centered_pair(w, zlo);        // row g   , k-slots 4t, 4t+1
             const uint32_t a1 = centered_pair(w >> 4, zhi);   // row g+8 , k-slots 4t, 4t+1
             const uint32_t a2 = centered_pair(w >> 8, zlo);   // row g   , k-slots 4t+2, 4t+3
             const uint32_t a3 = centered_pair(w >> 12, zhi);  // row g+8 , k-slots 4t+2, 4t+3
 #pragma unroll
-            for (int nt = 0; nt < NT; ++nt) mma_bf16(acc[nt], a0, a1, a2, a3, xb[nt][j].x, xb[nt][j].y);
+            for (int nt = 0; nt < NT; ++nt) {
+                if (jj == 0) mma_bf16<true>(acc[nt], a0, a1, a2, a3, xb[nt][jm].x, xb[nt][jm].y);
+                else mma_bf16<false>(acc[nt], a0, a1, a2, a3, xb[nt][jm].x, xb[nt][jm].y);
+            }
         }
-        const float slo = __uint_as_float(s.s2[h] << 16), shi = __uint_as_float(s.s2[h] & 0xFFFF0000u);
+        const float slo = __uint_as_float(u.s2[h] << 16), shi = __uint_as_float(u.s2[h] & 0xFFFF0000u);
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) {
             yacc[nt][0] = fmaf(acc[nt][0], slo, yacc[nt][0]);
@@ -144,22 +143,49 @@ __device__ __forceinline__ void compute_slot(const Slot<GPC> &s, const DecodePar
     }
 }
 
-// NT = token tiles of 8 (M <= 8*NT).  grid = (ceil(NR / WR), SC), WR = 8 >> wk_shift.
-template <int NT, int GPC>
+// Fragment -> y: lane (g,t) holds rows 16R+g and 16R+g+8 for tokens 8nt+2t and 8nt+2t+1.
+template <int NT>
+__device__ __forceinline__ void store_fragment(const DecodeParams &p, int R, int lane, const float4 (&v)[NT]) {
+    const int g = lane >> 2, t = lane & 3;
+    const int n0 = R * 16 + g;
+    const float b0 = p.bias ? __bfloat162float(p.bias[n0]) : 0.f;
+    const float b1 = p.bias ? __bfloat162float(p.bias[n0 + 8]) : 0.f;
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+        const int tok = nt * 8 + 2 * t;
+        if (tok < p.M) {
+            p.y[(size_t)tok * p.N + n0] = __float2bfloat16_rn(v[nt].x + b0);
+            p.y[(size_t)tok * p.N + n0 + 8] = __float2bfloat16_rn(v[nt].z + b1);
+        }
+        if (tok + 1 < p.M) {
+            p.y[(size_t)(tok + 1) * p.N + n0] = __float2bfloat16_rn(v[nt].y + b0);
+            p.y[(size_t)(tok + 1) * p.N + n0 + 8] = __float2bfloat16_rn(v[nt].w + b1);
+        }
+    }
+}
+
+// NT = token tiles of 8 (M <= 8*NT).  grid = (NR / WR, SC), WR = 8 >> wk_shift.
+template <int NT, int MPU>
 __global__ void __launch_bounds__(DEC_THREADS, NT >= 4 ? 1 : 2) decode_kernel(const DecodeParams p) {
-    __shared__ float red[DEC_WARPS][NT][32][4];
+    __shared__ float4 red[DEC_WARPS][NT][32];
     __shared__ int s_last;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int WK = 1 << p.wk_shift, WR = DEC_WARPS >> p.wk_shift;
+    const int g = lane >> 2, t = lane & 3;
+    const int WK = 1 << p.wk_shift;
     const int wr = warp >> p.wk_shift, wkk = warp & (WK - 1);
-    const int NR = p.N >> 4;
-    const int R = blockIdx.x * WR + wr;
+    const int R = blockIdx.x * (DEC_WARPS >> p.wk_shift) + wr;
     const int slice = blockIdx.y * WK + wkk;
-    const int kb0 = slice * p.cps;
-    const int kb_end = R < NR ? min(p.KB, kb0 + p.cps) : kb0;  // out-of-range row block: empty slice
+    const int u0 = slice * p.ups;
+    const int n_units = min(p.K / UNIT_K, u0 + p.ups) - u0;  // may be <= 0 for a trailing slice
 
-    const uint4 *wrow = p.qw + (size_t)(R < NR ? R : 0) * p.KB * 32;
-    const uint8_t *mrow = p.meta + (size_t)(R < NR ? R : 0) * p.G * META_BYTES;
+    const uint4 *wp = p.qw + ((size_t)R * p.KB + 2 * (size_t)u0) * 32 + lane;
+    const uint8_t *ms = p.meta + (size_t)R * p.G * META_BYTES + (size_t)u0 * p.meta_unit_stride + 4 * g;
+    const uint8_t *mz = ms + (META_ZERO_OFF - 3 * g);
+    const __nv_bfloat16 *xp[NT];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)  // token rows beyond M alias row M-1: their columns are never stored
+        xp[nt] = p.x + (size_t)min(nt * 8 + g, p.M - 1) * p.K + (size_t)u0 * UNIT_K + 4 * t;
+    const size_t mstride = (size_t)p.meta_unit_stride;
 
     float yacc[NT][4];
 #pragma unroll
@@ -167,93 +193,96 @@ __global__ void __launch_bounds__(DEC_THREADS, NT >= 4 ? 1 : 2) decode_kernel(co
 #pragma unroll
         for (int i = 0; i < 4; ++i) yacc[nt][i] = 0.f;
 
-    Slot<GPC> cur[DEC_DEPTH], nxt[DEC_DEPTH];
+    Unit<MPU> ring[2 * DEC_DEPTH];
 #pragma unroll
-    for (int d = 0; d < DEC_DEPTH; ++d) load_slot<GPC>(cur[d], p, wrow, mrow, kb0 + d, kb_end, lane);
-#pragma unroll
-    for (int d = 0; d < DEC_DEPTH; ++d) load_slot<GPC>(nxt[d], p, wrow, mrow, kb0 + DEC_DEPTH + d, kb_end, lane);
+    for (int d = 0; d < 2 * DEC_DEPTH; ++d)
+        if (d < n_units) load_unit<MPU>(ring[d], wp + d * 64, ms + d * mstride, mz + d * mstride);
 
     // Weights are immutable: everything above is independent of the previous kernel in the
     // stream.  Let the next kernel start its own prefetch, then wait for our producer.
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
 
-    for (int base = kb0; base < kb_end; base += 2 * DEC_DEPTH) {
+    for (int base = 0; base < n_units; base += 2 * DEC_DEPTH) {
+        const int left = n_units - base;  // units not yet computed, > 0
 #pragma unroll
-        for (int d = 0; d < DEC_DEPTH; ++d)
-            if (base + d < kb_end) compute_slot<NT, GPC>(cur[d], p, base + d, lane, yacc);
+        for (int hlf = 0; hlf < 2; ++hlf) {
 #pragma unroll
-        for (int d = 0; d < DEC_DEPTH; ++d) load_slot<GPC>(cur[d], p, wrow, mrow, base + 2 * DEC_DEPTH + d, kb_end, lane);
+            for (int d = 0; d < DEC_DEPTH; ++d) {
+                const int i = hlf * DEC_DEPTH + d;
+                if (i < left) {
+                    const __nv_bfloat16 *xq[NT];
 #pragma unroll
-        for (int d = 0; d < DEC_DEPTH; ++d)
-            if (base + DEC_DEPTH + d < kb_end) compute_slot<NT, GPC>(nxt[d], p, base + DEC_DEPTH + d, lane, yacc);
+                    for (int nt = 0; nt < NT; ++nt) xq[nt] = xp[nt] + i * UNIT_K;
+                    compute_unit<NT, MPU>(ring[i], xq, yacc);
+                }
+            }
 #pragma unroll
-        for (int d = 0; d < DEC_DEPTH; ++d) load_slot<GPC>(nxt[d], p, wrow, mrow, base + 3 * DEC_DEPTH + d, kb_end, lane);
-    }
-
-    // ---- reduce the K-split warps of this CTA (fixed order) -------------------------
-#pragma unroll
-    for (int nt = 0; nt < NT; ++nt)
-        *reinterpret_cast<float4 *>(&red[warp][nt][lane][0]) = make_float4(yacc[nt][0], yacc[nt][1], yacc[nt][2], yacc[nt][3]);
-    __syncthreads();
-
-    // Output element e of the CTA tile: token-major, n fastest, so stores are contiguous.
-    const int tile_n = WR * 16;
-    const int n_out = tile_n * p.M;
-    const int n_base = blockIdx.x * tile_n;
-    auto tile_value = [&](int e, int &tok, int &n) -> float {
-        tok = e / tile_n;
-        int nl = e - tok * tile_n;
-        n = n_base + nl;
-        int wr_e = nl >> 4, r = nl & 15;
-        int nt = tok >> 3, c = tok & 7;
-        int ln = (r & 7) * 4 + (c >> 1), i = ((r >> 3) << 1) | (c & 1);
-        float v = 0.f;
-        for (int k = 0; k < WK; ++k) v += red[(wr_e << p.wk_shift) + k][nt][ln][i];
-        return v;
-    };
-
-    if (p.sc == 1) {
-        for (int e = threadIdx.x; e < n_out; e += DEC_THREADS) {
-            int tok, n;
-            float v = tile_value(e, tok, n);
-            if (n < p.N) {
-                if (p.bias) v += __bfloat162float(p.bias[n]);
-                p.y[(size_t)tok * p.N + n] = __float2bfloat16_rn(v);
+            for (int d = 0; d < DEC_DEPTH; ++d) {  // refill the half just consumed, one ring turn ahead
+                const int i = hlf * DEC_DEPTH + d + 2 * DEC_DEPTH;
+                if (i < left) load_unit<MPU>(ring[i - 2 * DEC_DEPTH], wp + i * 64, ms + i * mstride, mz + i * mstride);
             }
         }
-        return;
+        wp += 2 * DEC_DEPTH * 64;
+        ms += 2 * DEC_DEPTH * mstride;
+        mz += 2 * DEC_DEPTH * mstride;
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) xp[nt] += 2 * DEC_DEPTH * UNIT_K;
     }
 
-    // ---- cross-CTA split-K: publish the partial, the last CTA of the column sums -----
-    float *part = p.scratch + (size_t)blockIdx.y * p.M * p.N;
-    for (int e = threadIdx.x; e < n_out; e += DEC_THREADS) {
-        int tok, n;
-        float v = tile_value(e, tok, n);
-        if (n < p.N) part[(size_t)tok * p.N + n] = v;
+    // ---- reduce the K-split warps of this CTA: warp (wr, 0) sums its row block in slice order ----
+    if (WK > 1) {
+        if (wkk != 0) {
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt)
+                red[warp][nt][lane] = make_float4(yacc[nt][0], yacc[nt][1], yacc[nt][2], yacc[nt][3]);
+        }
+        __syncthreads();
+        if (wkk != 0 && p.sc == 1) return;
     }
+    float4 v[NT];
+    if (wkk == 0) {
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            v[nt] = make_float4(yacc[nt][0], yacc[nt][1], yacc[nt][2], yacc[nt][3]);
+            for (int k = 1; k < WK; ++k) {
+                const float4 o = red[warp + k][nt][lane];
+                v[nt].x += o.x; v[nt].y += o.y; v[nt].z += o.z; v[nt].w += o.w;
+            }
+        }
+        if (p.sc == 1) {
+            store_fragment<NT>(p, R, lane, v);
+            return;
+        }
+        // cross-CTA split-K: publish this CTA's partial fragment
+        float4 *part = p.scratch + (((size_t)blockIdx.y * (p.N >> 4) + R) * NT) * 32 + lane;
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) __stcg(part + nt * 32, v[nt]);
+    }
+    // ---- the last CTA of this column (ticket) sums the SC partials in slice order: deterministic ----
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
-        int prev = atomicAdd(&p.tickets[blockIdx.x], 1);
+        const int prev = atomicAdd(&p.tickets[blockIdx.x], 1);
         s_last = prev == p.sc - 1;
         if (s_last) p.tickets[blockIdx.x] = 0;  // self-reset for the next launch
     }
     __syncthreads();
-    if (!s_last) return;
+    if (!s_last || wkk != 0) return;
     __threadfence();
-    for (int e = threadIdx.x; e < n_out; e += DEC_THREADS) {
-        int tok = e / tile_n, n = n_base + (e - tok * tile_n);
-        if (n >= p.N) continue;
-        float v = 0.f;
-        for (int s = 0; s < p.sc; ++s) v += __ldcg(p.scratch + ((size_t)s * p.M + tok) * p.N + n);
-        if (p.bias) v += __bfloat162float(p.bias[n]);
-        p.y[(size_t)tok * p.N + n] = __float2bfloat16_rn(v);
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+        v[nt] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int s = 0; s < p.sc; ++s) {
+            const float4 o = __ldcg(p.scratch + (((size_t)s * (p.N >> 4) + R) * NT + nt) * 32 + lane);
+            v[nt].x += o.x; v[nt].y += o.y; v[nt].z += o.z; v[nt].w += o.w;
+        }
     }
+    store_fragment<NT>(p, R, lane, v);
 }
 
 // ---- host side ---------------------------------------------------------------------
-struct DecodeCfg { int wk_shift, sc, cps; };
+struct DecodeCfg { int wk_shift, sc, ups; };
 
 static int env_int(const char *name, int dflt) {
     const char *v = getenv(name);
@@ -263,32 +292,32 @@ static int env_int(const char *name, int dflt) {
 // Heuristic: enough CTAs to cover the chip about twice, at least 4 chunks per warp,
 // and as little K-splitting across CTAs as that allows.
 static DecodeCfg pick_cfg(const Linear &L, int sm_count) {
-    const int NR = (int)L.d.NR, KB = (int)L.d.KB;
+    const int NR = (int)L.d.NR, U = (int)(L.d.K / UNIT_K);
     int wk_shift = 3;  // 8 warps along K, one row block per CTA
-    // Long-N shapes: put 2 or 4 row blocks in a CTA so x is fetched less often.
-    while (wk_shift > 1 && (NR >> (3 - wk_shift + 1)) >= 4 * sm_count && (KB >> (wk_shift - 1)) >= 8) --wk_shift;
+    // Long-N shapes: put 2 or 4 row blocks in a CTA (NR is a multiple of 4 by the N % 64 gate).
+    while (wk_shift > 1 && (NR >> (3 - wk_shift + 1)) >= 4 * sm_count && (U >> (wk_shift - 1)) >= 4) --wk_shift;
     int WR = DEC_WARPS >> wk_shift, WK = 1 << wk_shift;
-    int ctas_x = (NR + WR - 1) / WR;
+    int ctas_x = NR / WR;
     int sc = 1;
-    while (ctas_x * sc < 2 * sm_count && (KB / (WK * sc * 2)) >= 4 && sc < 16) sc *= 2;
+    while (ctas_x * sc < 2 * sm_count && (U / (WK * sc * 2)) >= 2 && sc < 16) sc *= 2;
     int ov_wk = env_int("W4A16_DECODE_WK_SHIFT", -1), ov_sc = env_int("W4A16_DECODE_SC", -1);
-    if (ov_wk >= 0 && ov_wk <= 3) wk_shift = ov_wk;
+    if (ov_wk >= 1 && ov_wk <= 3) wk_shift = ov_wk;
     if (ov_sc >= 1 && ov_sc <= 64) sc = ov_sc;
     WK = 1 << wk_shift;
     int slices = WK * sc;
-    int cps = (KB + slices - 1) / slices;
-    return {wk_shift, sc, cps};
+    int ups = (U + slices - 1) / slices;
+    return {wk_shift, sc, ups};
 }
 
 int decode_scratch_need(const Linear &L, int sm_count, int64_t *scratch_floats, int64_t *tickets) {
     // worst case over the env overrides is bounded by sc <= 64
     DecodeCfg c = pick_cfg(L, sm_count);
-    *scratch_floats = c.sc > 1 ? (int64_t)c.sc * 32 * L.d.N : 0;
+    *scratch_floats = c.sc > 1 ? (int64_t)c.sc * L.d.NR * 4 * 32 * 4 : 0;  // [SC][NR][NT<=4][32] float4
     *tickets = L.d.NR;  // >= gridDim.x for any WR
     return 0;
 }
 
-template <int NT, int GPC>
+template <int NT, int MPU>
 static int launch_t(const DecodeParams &p, dim3 grid, cudaStream_t stream, bool pdl) {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = grid;
@@ -300,7 +329,7 @@ static int launch_t(const DecodeParams &p, dim3 grid, cudaStream_t stream, bool 
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    W4_CUDA_OK(cudaLaunchKernelEx(&cfg, decode_kernel<NT, GPC>, p));
+    W4_CUDA_OK(cudaLaunchKernelEx(&cfg, decode_kernel<NT, MPU>, p));
     count_launch();
     return 0;
 }
@@ -319,26 +348,28 @@ int launch_decode(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int
     p.meta = L.meta;
     p.bias = add_bias && L.has_bias ? L.bias : nullptr;
     p.x = x; p.y = y;
-    p.scratch = L.splitk_scratch; p.tickets = L.tickets;
+    p.scratch = reinterpret_cast<float4 *>(L.splitk_scratch); p.tickets = L.tickets;
     p.M = (int)M; p.K = (int)L.d.K; p.N = (int)L.d.N; p.KB = (int)L.d.KB; p.G = (int)L.d.G;
-    p.chunks_per_group_shift = gs == 64 ? 0 : gs == 128 ? 1 : 31;  // gs == K (per-channel): one group
     if (gs != 32 && gs != 64 && gs != 128 && gs != L.d.K) return fail("launch_decode: unsupported group size");
-    p.wk_shift = c.wk_shift; p.sc = c.sc; p.cps = c.cps;
-    if (c.sc > 1 && (!L.splitk_scratch || (int64_t)c.sc * M * L.d.N > L.splitk_floats))
+    const int mpu = gs == 32 ? 4 : gs == 64 ? 2 : 1;
+    p.meta_unit_stride = gs == L.d.K && gs != 128 ? 0 : mpu * META_BYTES;  // per-channel: one group for all of K
+    p.wk_shift = c.wk_shift; p.sc = c.sc; p.ups = c.ups;
+    const int nt = M <= 8 ? 1 : M <= 16 ? 2 : 4;
+    if (c.sc > 1 && (!L.splitk_scratch || (int64_t)c.sc * L.d.NR * nt * 32 * 4 > L.splitk_floats))
         return fail("launch_decode: split-K scratch too small for this configuration");
     const int WR = DEC_WARPS >> c.wk_shift;
-    dim3 grid((unsigned)((L.d.NR + WR - 1) / WR), (unsigned)c.sc);
+    dim3 grid((unsigned)(L.d.NR / WR), (unsigned)c.sc);
     const bool pdl = env_int("W4A16_NO_PDL", 0) == 0;
-    const int gpc = gs == 32 ? 2 : 1;
-    const int nt = M <= 8 ? 1 : M <= 16 ? 2 : 4;
-    if (gpc == 1) {
-        if (nt == 1) return launch_t<1, 1>(p, grid, stream, pdl);
-        if (nt == 2) return launch_t<2, 1>(p, grid, stream, pdl);
-        return launch_t<4, 1>(p, grid, stream, pdl);
-    }
-    if (nt == 1) return launch_t<1, 2>(p, grid, stream, pdl);
-    if (nt == 2) return launch_t<2, 2>(p, grid, stream, pdl);
-    return launch_t<4, 2>(p, grid, stream, pdl);
+#define W4_DISPATCH(MPU_)                                               \
+    do {                                                                \
+        if (nt == 1) return launch_t<1, MPU_>(p, grid, stream, pdl);    \
+        if (nt == 2) return launch_t<2, MPU_>(p, grid, stream, pdl);    \
+        return launch_t<4, MPU_>(p, grid, stream, pdl);                 \
+    } while (0)
+    if (mpu == 1) W4_DISPATCH(1);
+    if (mpu == 2) W4_DISPATCH(2);
+    W4_DISPATCH(4);
+#undef W4_DISPATCH
 }
 
 }  // namespace w4
