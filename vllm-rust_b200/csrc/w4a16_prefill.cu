@@ -1,8 +1,444 @@
-// w4a16_prefill.cu -- placeholder until the tcgen05 kernel lands (next commit).
+// w4a16_prefill.cu -- the batched / prefill GEMM (M > 32 tokens): tcgen05.mma with TMEM accumulators.
+//
+// Replaces awq_marlin_dequant_int4_bf16 + cuBLAS (awq_marlin_dequant.cu:35-69, marlin_cuda.rs:793-818),
+// gptq_dequant_int4_bf16 + matmul (gptq_dequant.cu:48-87) and marlin_tile_mma (marlin_tile_mma.cu:348-475):
+// the dense bf16 [K,N] weight matrix the reference materialises in HBM on every call never exists here.
+//
+// Arithmetic = the reference's "D2" grid: every weight is bf16_rn(f32(q - z) * f32(bf16 scale))
+// (w4a16_dequant.cuh proves the packed bf16x2 sub+mul is that exact rounding), then a bf16 x bf16
+// contraction with fp32 accumulation, + bias, one rounding to bf16.
+//
+// Mapping onto the SM (one persistent CTA per SM, 16 warps, warp-specialised):
+//   D^T[n, tok] = sum_k W^T[n, k] * X[tok, k]      UMMA M = 128 output features (TMEM lanes),
+//                                                   UMMA N = TM tokens (TMEM columns), UMMA K = 16
+//   A operand (weights)  : TMEM.  8 dequant warps read the W4T chunks straight from global (one coalesced
+//                          16-byte load per lane per 16x64 chunk, 4 stages ahead in registers), turn every
+//                          word into its four bf16x2 fragment registers and write them with ONE
+//                          tcgen05.st.16x256b.x4 per chunk -- the W4T nibble order (w4a16_layout.cuh) IS
+//                          that instruction's register order, so there is no shuffle and no shared-memory
+//                          round trip for weights.
+//   B operand (tokens)   : shared memory, K-major, 128B-swizzled [TM tokens][64 k] tiles loaded by TMA
+//                          (cp.async.bulk.tensor.2d) from the caller's x; rows beyond M are zero-filled.
+//   accumulator          : TMEM columns [0, TM), fp32.
+//   epilogue             : 4 warps, tcgen05.ld.32x32b -> +bias -> bf16 -> shared staging -> 16-byte
+//                          coalesced stores of y rows; TMEM is released as soon as it has been read.
+//   pipeline             : a ring of STAGES {A columns, B tile}; mbarriers full_a / full_b / empty
+//                          (tcgen05.commit), tmem_full / tmem_empty between MMA and epilogue.
+#include <cuda.h>  // CUtensorMap + enums only; the encode entry point is fetched from the runtime, libcuda is not linked
+
+#include <mutex>
+
+#include "w4a16_dequant.cuh"
 #include "w4a16_internal.cuh"
+
 namespace w4 {
-bool prefill_available() { return false; }
-int launch_prefill(const Linear &, const __nv_bfloat16 *, __nv_bfloat16 *, int64_t, bool, cudaStream_t) {
-    return fail("prefill kernel not built");
+
+constexpr int PF_THREADS = 512;
+constexpr int PF_TILE_N = 128;     // output features per CTA tile (UMMA M)
+constexpr int PF_BLOCK_K = 64;     // k per pipeline stage: one W4T chunk column, one 128-byte swizzle row of x
+constexpr int PF_A_COL0 = 256;     // TMEM column where the A ring starts (accumulator owns [0, 256))
+constexpr int PF_A_STAGE_COLS = 32;  // 64 k of bf16 = 32 32-bit columns
+constexpr int PF_WPREF = 4;        // weight chunks each dequant warp keeps in flight
+constexpr uint32_t PF_SPIN_LIMIT = 1u << 26;
+
+struct PrefillParams {
+    const uint4 *qw;
+    const uint8_t *meta;
+    const __nv_bfloat16 *bias;
+    __nv_bfloat16 *y;
+    int M, K, N, KB, G;
+    int gs_shift;      // log2(group size), or 31 for per-channel (every k maps to group 0)
+    int n_tiles, m_tiles;
+};
+
+// ---- PTX wrappers ------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok;
+}
+// A wait that cannot hang the GPU: a lost arrival traps (the launch fails loudly) instead of spinning forever.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t spins = 0;
+    while (!mbar_try_wait(bar, parity))
+        if (++spins > PF_SPIN_LIMIT) __trap();
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem descriptor]
+__device__ __forceinline__ void tc_mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                          uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, int c0, int c1, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+        ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar)
+        : "memory");
+}
+__device__ __forceinline__ void tc_st_16x256b_x4(uint32_t taddr, const uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.16x256b.x4.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+        "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+        : "memory");
+}
+__device__ __forceinline__ void tc_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+    return r;
+}
+__device__ __forceinline__ uint4 ldg_nc_v4(const uint4 *p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
+// start address >> 4 in [0,14), LBO [16,30) unused for swizzled K-major, SBO = 1024 B (8 rows x 128 B)
+// in [32,46), descriptor version 1 in [46,48), layout type SWIZZLE_128B = 2 in [61,64).
+__device__ __forceinline__ uint64_t make_b_desc(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+// kind::f16 instruction descriptor: D = f32 (bit 4), A = B = bf16 (bits 7, 10), both K-major,
+// N >> 3 in [17,23), M >> 4 in [24,29).
+__host__ __device__ constexpr uint32_t make_idesc(int umma_m, int umma_n) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(umma_n >> 3) << 17) | ((uint32_t)(umma_m >> 4) << 24);
+}
+
+template <int TM> struct PfCfg {
+    static constexpr int STAGES = TM == 256 ? 5 : 8;
+    static constexpr int B_STAGE_BYTES = TM * 128;
+    static constexpr int STAGE_BYTES_TOTAL = STAGES * B_STAGE_BYTES;
+    static constexpr int OUT_BYTES = TM * PF_TILE_N * 2;  // bf16 staging tile [TM][128]
+    static constexpr int BAR_BYTES = 1024;
+    static constexpr int SMEM_USED = STAGE_BYTES_TOTAL + OUT_BYTES + BAR_BYTES;
+    // at least ~116 KB so that two CTAs never share an SM: each CTA allocates all 512 TMEM columns
+    static constexpr int SMEM_BYTES = (SMEM_USED < 118 * 1024 ? 118 * 1024 : SMEM_USED) + 1024;
+};
+
+// One prefetched 16x64 chunk of one row block + the scale pair / zero byte of its group(s).
+template <int GPS> struct WEntry {
+    uint4 w;
+    uint32_t s2[GPS];
+    uint32_t zb[GPS];
+};
+
+// TM = tokens per tile (UMMA N): 256, 128 or 64.  GPS = groups per 64-k stage: 1 (g >= 64), 2 (g = 32).
+template <int TM, int GPS>
+__global__ void __launch_bounds__(PF_THREADS, 1)
+prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p) {
+    using C = PfCfg<TM>;
+    constexpr int S = C::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    __nv_bfloat16 *smem_out = reinterpret_cast<__nv_bfloat16 *>(smem + C::STAGE_BYTES_TOTAL);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + C::STAGE_BYTES_TOTAL + C::OUT_BYTES);
+    const uint32_t smem_b = smem_u32(smem);
+    const uint32_t full_b = smem_u32(bars), full_a = full_b + 8 * S, empty = full_a + 8 * S;
+    const uint32_t tmem_full = empty + 8 * S, tmem_empty = tmem_full + 8;
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(bars + 3 * S + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int KBLKS = p.K / PF_BLOCK_K;
+    const int ntiles = p.n_tiles * p.m_tiles;
+
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < S; ++i) {
+            mbar_init(full_b + 8 * i, 1);   // the producer's arrive.expect_tx; TMA completes the bytes
+            mbar_init(full_a + 8 * i, 8);   // one arrival per dequant warp
+            mbar_init(empty + 8 * i, 1);    // tcgen05.commit
+        }
+        mbar_init(tmem_full, 1);            // tcgen05.commit after the last k block of a tile
+        mbar_init(tmem_empty, 4);           // one arrival per epilogue warp
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     ::"r"(smem_u32(const_cast<uint32_t *>(tmem_slot))), "r"(512u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (warp == 0 && lane == 0)
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&x_map) : "memory");
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer: x tiles [TM tokens][64 k] =====
+        if (lane == 0) {
+            int s = 0; uint32_t ph = 0;
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+                const int m_tile = tile / p.n_tiles;
+                for (int kb = 0; kb < KBLKS; ++kb) {
+                    mbar_wait(empty + 8 * s, ph ^ 1);
+                    mbar_arrive_expect_tx(full_b + 8 * s, C::B_STAGE_BYTES);
+                    tma_load_2d(smem_b + s * C::B_STAGE_BYTES, &x_map, kb * PF_BLOCK_K, m_tile * TM, full_b + 8 * s);
+                    if (++s == S) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer: one thread drives the tensor core for the whole CTA =====
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc(PF_TILE_N, TM);
+            int s = 0; uint32_t ph = 0, ti = 0;
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++ti) {
+                mbar_wait(tmem_empty, (ti & 1) ^ 1);   // the epilogue has drained the previous tile
+                tc_fence_after();
+                for (int kb = 0; kb < KBLKS; ++kb) {
+                    mbar_wait(full_b + 8 * s, ph);
+                    mbar_wait(full_a + 8 * s, ph);
+                    tc_fence_after();
+                    const uint64_t bdesc = make_b_desc(smem_b + s * C::B_STAGE_BYTES);
+                    const uint32_t a_tmem = tmem_base + PF_A_COL0 + s * PF_A_STAGE_COLS;
+#pragma unroll
+                    for (int k = 0; k < PF_BLOCK_K / 16; ++k)   // +32 bytes of k inside the swizzle atom = +2 in the address field
+                        tc_mma_ts(tmem_base, a_tmem + k * 8, bdesc + 2 * k, idesc, (uint32_t)((kb | k) != 0));
+                    tc_commit(empty + 8 * s);                   // frees the A columns and the B tile of this stage
+                    if (kb == KBLKS - 1) tc_commit(tmem_full);  // accumulator complete
+                    if (++s == S) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+    } else if (warp >= 4 && warp < 12) {
+        // ===== dequant warps: W4T chunk -> bf16 fragments -> TMEM (A operand) =====
+        const int quarter = warp & 3, half = (warp - 4) >> 2;
+        const int rloc = quarter * 2 + half;
+        const int g = lane >> 2;
+        const uint32_t a_taddr = tmem_base + ((uint32_t)(quarter * 32 + half * 16) << 16) + PF_A_COL0;
+        const int my_tiles = blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+        const int total = my_tiles * KBLKS;
+
+        int pf_tile = blockIdx.x, pf_kb = 0;
+        const uint4 *pf_w = nullptr;
+        const uint8_t *pf_m = nullptr;
+        bool pf_valid = false;   // false for the row blocks of a 64-row tail tile that lie beyond N: they dequantise to 0
+        auto set_tile = [&](int tile) {
+            const size_t R = (size_t)(tile % p.n_tiles) * 8 + rloc;
+            pf_valid = R < (size_t)(p.N >> 4);
+            pf_w = p.qw + R * p.KB * 32 + lane;
+            pf_m = p.meta + R * p.G * META_BYTES + 4 * g;
+        };
+        if (pf_tile < ntiles) set_tile(pf_tile);
+        auto fetch = [&](WEntry<GPS> &e) {
+            if (pf_tile >= ntiles) return;
+            if (pf_valid) {
+                e.w = ldg_nc_v4(pf_w + (size_t)pf_kb * 32);
+#pragma unroll
+                for (int h = 0; h < GPS; ++h) {
+                    const int grp = (pf_kb * PF_BLOCK_K + h * 32) >> p.gs_shift;
+                    const uint8_t *m = pf_m + (size_t)grp * META_BYTES;
+                    e.s2[h] = __ldg(reinterpret_cast<const uint32_t *>(m));
+                    e.zb[h] = __ldg(m + (META_ZERO_OFF - 3 * g));
+                }
+            } else {
+                e.w = make_uint4(0, 0, 0, 0);
+#pragma unroll
+                for (int h = 0; h < GPS; ++h) { e.s2[h] = 0; e.zb[h] = 0; }
+            }
+            if (++pf_kb == KBLKS) {
+                pf_kb = 0;
+                pf_tile += gridDim.x;
+                if (pf_tile < ntiles) set_tile(pf_tile);
+            }
+        };
+        WEntry<GPS> ring[PF_WPREF];
+#pragma unroll
+        for (int u = 0; u < PF_WPREF; ++u) fetch(ring[u]);
+
+        int s = 0; uint32_t ph = 0;
+        for (int it0 = 0; it0 < total; it0 += PF_WPREF) {
+#pragma unroll
+            for (int u = 0; u < PF_WPREF; ++u) {
+                if (it0 + u < total) {
+                    const WEntry<GPS> &e = ring[u];
+                    const uint32_t wj[4] = {e.w.x, e.w.y, e.w.z, e.w.w};
+                    uint32_t r[16];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const int h = GPS == 2 ? (j >> 1) : 0;
+                        const uint32_t zlo = zero_magic(e.zb[h] & 0xFu), zhi = zero_magic(e.zb[h] >> 4);
+                        const uint32_t slo2 = prmt(e.s2[h], 0, 0x1010), shi2 = prmt(e.s2[h], 0, 0x3232);
+                        r[4 * j + 0] = dequant_pair(wj[j], zlo, slo2);        // row g   , k 4t, 4t+1
+                        r[4 * j + 1] = dequant_pair(wj[j] >> 8, zlo, slo2);   // row g   , k 4t+2, 4t+3
+                        r[4 * j + 2] = dequant_pair(wj[j] >> 4, zhi, shi2);   // row g+8 , k 4t, 4t+1
+                        r[4 * j + 3] = dequant_pair(wj[j] >> 12, zhi, shi2);  // row g+8 , k 4t+2, 4t+3
+                    }
+                    fetch(ring[u]);
+                    mbar_wait(empty + 8 * s, ph ^ 1);   // the MMAs that read this stage's columns have retired
+                    tc_fence_after();
+                    tc_st_16x256b_x4(a_taddr + s * PF_A_STAGE_COLS, r);
+                    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                    tc_fence_before();
+                    if (lane == 0) mbar_arrive(full_a + 8 * s);
+                    if (++s == S) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+    } else if (warp >= 12) {
+        // ===== epilogue warps: TMEM -> +bias -> bf16 -> staging -> y =====
+        const int q = warp & 3;
+        const int et = threadIdx.x - 12 * 32;   // 0..127
+        uint32_t ti = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++ti) {
+            const int n_tile = tile % p.n_tiles, m_tile = tile / p.n_tiles;
+            const int n = n_tile * PF_TILE_N + q * 32 + lane;
+            const float bias = p.bias && n < p.N ? __bfloat162float(p.bias[n]) : 0.f;
+            mbar_wait(tmem_full, ti & 1);
+            tc_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < TM / 32; ++c) {
+                uint32_t v[32];
+                tc_ld_32x32b_x32(tmem_base + ((uint32_t)(q * 32) << 16) + c * 32, v);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                    smem_out[(c * 32 + i) * PF_TILE_N + q * 32 + lane] = __float2bfloat16_rn(__uint_as_float(v[i]) + bias);
+            }
+            tc_fence_before();
+            if (lane == 0) mbar_arrive(tmem_empty);   // the next tile's MMAs may overwrite the accumulator
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            const int rows = min(TM, p.M - m_tile * TM);
+            __nv_bfloat16 *ybase = p.y + (size_t)m_tile * TM * p.N + (size_t)n_tile * PF_TILE_N;
+            for (int idx = et; idx < rows * 16; idx += 128) {
+                const int row = idx >> 4, c16 = idx & 15;
+                if (n_tile * PF_TILE_N + c16 * 8 < p.N)
+                    *reinterpret_cast<uint4 *>(ybase + (size_t)row * p.N + c16 * 8) =
+                    *reinterpret_cast<const uint4 *>(smem_out + row * PF_TILE_N + c16 * 8);
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");  // staging is free again
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
+// ---- host side -----------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+static std::once_flag g_encode_once;
+static std::string g_encode_err;
+
+static int get_encode() {
+    std::call_once(g_encode_once, [] {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+        if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn)
+            g_encode_err = std::string("cuTensorMapEncodeTiled entry point not available: ") + cudaGetErrorString(e);
+        else
+            g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+    });
+    if (!g_encode) return fail(g_encode_err);
+    return 0;
+}
+
+bool prefill_available() { return true; }
+
+template <int TM, int GPS>
+static int launch_pf(const CUtensorMap &map, const PrefillParams &p, int grid, cudaStream_t stream) {
+    using C = PfCfg<TM>;
+    static std::once_flag once;
+    static cudaError_t attr_err = cudaSuccess;
+    std::call_once(once, [] {
+        attr_err = cudaFuncSetAttribute(prefill_kernel<TM, GPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
+    });
+    if (attr_err != cudaSuccess)
+        return fail(std::string("cudaFuncSetAttribute(prefill_kernel smem): ") + cudaGetErrorString(attr_err));
+    prefill_kernel<TM, GPS><<<grid, PF_THREADS, C::SMEM_BYTES, stream>>>(map, p);
+    W4_CUDA_OK(cudaGetLastError());
+    count_launch();
+    return 0;
+}
+
+int prefill_token_tile(int64_t M) { return M > 128 ? 256 : M > 64 ? 128 : 64; }
+
+int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
+                   cudaStream_t stream) {
+    if (M < 1) return fail("launch_prefill: M must be >= 1");
+    if (M > (int64_t)1 << 30) return fail("launch_prefill: M too large");
+    if (get_encode()) return 1;
+    const int gs = L.d.gs;
+    if (gs != 32 && gs != 64 && gs != 128 && gs != L.d.K) return fail("launch_prefill: unsupported group size");
+    const int TM = prefill_token_tile(M);
+    PrefillParams p;
+    p.qw = reinterpret_cast<const uint4 *>(L.qw);
+    p.meta = L.meta;
+    p.bias = add_bias && L.has_bias ? L.bias : nullptr;
+    p.y = y;
+    p.M = (int)M; p.K = (int)L.d.K; p.N = (int)L.d.N; p.KB = (int)L.d.KB; p.G = (int)L.d.G;
+    p.gs_shift = gs == L.d.K && gs != 32 && gs != 64 && gs != 128 ? 31 : (gs == 32 ? 5 : gs == 64 ? 6 : 7);
+    p.n_tiles = (int)((L.d.N + PF_TILE_N - 1) / PF_TILE_N);  // N % 64 == 0: the last tile may be half full
+    p.m_tiles = (int)((M + TM - 1) / TM);
+
+    CUtensorMap map;
+    const cuuint64_t gdim[2] = {(cuuint64_t)L.d.K, (cuuint64_t)M};
+    const cuuint64_t gstride[1] = {(cuuint64_t)L.d.K * 2};
+    const cuuint32_t box[2] = {(cuuint32_t)PF_BLOCK_K, (cuuint32_t)TM};
+    const cuuint32_t estride[2] = {1, 1};
+    CUresult r = g_encode(&map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16 *>(x), gdim, gstride, box,
+                          estride, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled(x) failed with CUresult " + std::to_string((int)r));
+
+    const int ntiles = p.n_tiles * p.m_tiles;
+    const int grid = std::min(ntiles, L.scratch->sm_count);
+    const int gps = gs == 32 ? 2 : 1;
+#define W4_PF(TM_)                                                          \
+    do {                                                                    \
+        if (gps == 1) return launch_pf<TM_, 1>(map, p, grid, stream);       \
+        return launch_pf<TM_, 2>(map, p, grid, stream);                     \
+    } while (0)
+    if (TM == 256) W4_PF(256);
+    if (TM == 128) W4_PF(128);
+    W4_PF(64);
+#undef W4_PF
+}
+
 }  // namespace w4
