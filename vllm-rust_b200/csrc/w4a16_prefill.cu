@@ -8,10 +8,10 @@
 // (w4a16_dequant.cuh proves the packed bf16x2 sub+mul is that exact rounding), then a bf16 x bf16
 // contraction with fp32 accumulation, + bias, one rounding to bf16.
 //
-// Mapping onto the SM (one persistent CTA per SM, 16 warps, warp-specialised):
+// Mapping onto the SM (one persistent CTA per SM, 24 warps, warp-specialised):
 //   D^T[n, tok] = sum_k W^T[n, k] * X[tok, k]      UMMA M = 128 output features (TMEM lanes),
 //                                                   UMMA N = TM tokens (TMEM columns), UMMA K = 16
-//   A operand (weights)  : TMEM.  8 dequant warps read the W4T chunks straight from global (one coalesced
+//   A operand (weights)  : TMEM.  16 dequant warps read the W4T chunks straight from global (one coalesced
 //                          16-byte load per lane per 16x64 chunk, 4 stages ahead in registers), turn every
 //                          word into its four bf16x2 fragment registers and write them with ONE
 //                          tcgen05.st.16x256b.x4 per chunk -- the W4T nibble order (w4a16_layout.cuh) IS
@@ -22,10 +22,12 @@
 //   accumulator          : TMEM columns [0, TM), fp32.
 //   epilogue             : 4 warps, tcgen05.ld.32x32b -> +bias -> bf16 -> shared staging -> 16-byte
 //                          coalesced stores of y rows; TMEM is released as soon as it has been read.
-//   pipeline             : a ring of STAGES {A columns, B tile}; mbarriers full_a / full_b / empty
+//   pipeline             : a ring of STAGES {A columns, B tile}; mbarriers full (TMA bytes + 8 dequant warps) / empty
 //                          (tcgen05.commit), tmem_full / tmem_empty between MMA and epilogue.
 #include <cuda.h>  // CUtensorMap + enums only; the encode entry point is fetched from the runtime, libcuda is not linked
 
+#include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 #include "w4a16_dequant.cuh"
@@ -33,7 +35,7 @@
 
 namespace w4 {
 
-constexpr int PF_THREADS = 512;
+constexpr int PF_THREADS = 768;      // 24 warps: TMA, MMA, TMEM-alloc, spare, 16 dequant, 4 epilogue
 constexpr int PF_TILE_N = 128;     // output features per CTA tile (UMMA M)
 constexpr int PF_BLOCK_K = 64;     // k per pipeline stage: one W4T chunk column, one 128-byte swizzle row of x
 constexpr int PF_A_COL0 = 256;     // TMEM column where the A ring starts (accumulator owns [0, 256))
@@ -49,6 +51,8 @@ struct PrefillParams {
     int M, K, N, KB, G;
     int gs_shift;      // log2(group size), or 31 for per-channel (every k maps to group 0)
     int n_tiles, m_tiles;
+    unsigned long long *dbg;   // W4A16_PF_DEBUG & 4: per-CTA {cycles, ns, wait_full_b, wait_full_a, wait_tmem_empty, tiles}
+    int debug;         // timing experiments only (W4A16_PF_DEBUG): 1 = skip x loads after the first k block, 2 = skip dequant
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------
@@ -78,6 +82,17 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity))
         if (++spins > PF_SPIN_LIMIT) __trap();
+}
+// One lane of a converged warp.  Code under `if (elect_one())` is known to run on a single lane, so ptxas keeps
+// descriptor / address operands in uniform registers instead of wrapping every UTCHMMA in a waterfall loop.
+__device__ __forceinline__ uint32_t elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred;
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -171,9 +186,9 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
     __nv_bfloat16 *smem_out = reinterpret_cast<__nv_bfloat16 *>(smem + C::STAGE_BYTES_TOTAL);
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + C::STAGE_BYTES_TOTAL + C::OUT_BYTES);
     const uint32_t smem_b = smem_u32(smem);
-    const uint32_t full_b = smem_u32(bars), full_a = full_b + 8 * S, empty = full_a + 8 * S;
+    const uint32_t full = smem_u32(bars), empty = full + 8 * S;
     const uint32_t tmem_full = empty + 8 * S, tmem_empty = tmem_full + 8;
-    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(bars + 3 * S + 2);
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(bars + 2 * S + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int KBLKS = p.K / PF_BLOCK_K;
@@ -181,8 +196,7 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
 
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < S; ++i) {
-            mbar_init(full_b + 8 * i, 1);   // the producer's arrive.expect_tx; TMA completes the bytes
-            mbar_init(full_a + 8 * i, 8);   // one arrival per dequant warp
+            mbar_init(full + 8 * i, 9);     // the producer's arrive.expect_tx (TMA completes the bytes) + 8 dequant warps
             mbar_init(empty + 8 * i, 1);    // tcgen05.commit
         }
         mbar_init(tmem_full, 1);            // tcgen05.commit after the last k block of a tile
@@ -204,69 +218,99 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
 
     if (warp == 0) {
         // ===== TMA producer: x tiles [TM tokens][64 k] =====
-        if (lane == 0) {
-            int s = 0; uint32_t ph = 0;
-            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-                const int m_tile = tile / p.n_tiles;
-                for (int kb = 0; kb < KBLKS; ++kb) {
-                    mbar_wait(empty + 8 * s, ph ^ 1);
-                    mbar_arrive_expect_tx(full_b + 8 * s, C::B_STAGE_BYTES);
-                    tma_load_2d(smem_b + s * C::B_STAGE_BYTES, &x_map, kb * PF_BLOCK_K, m_tile * TM, full_b + 8 * s);
-                    if (++s == S) { s = 0; ph ^= 1; }
+        int s = 0; uint32_t ph = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            const int m_tile = tile / p.n_tiles;
+            for (int kb = 0; kb < KBLKS; ++kb) {
+                mbar_wait(empty + 8 * s, ph ^ 1);
+                if (elect_one()) {
+                    if ((p.debug & 1) && kb >= S) {
+                        mbar_arrive(full + 8 * s);
+                    } else {
+                        mbar_arrive_expect_tx(full + 8 * s, C::B_STAGE_BYTES);
+                        tma_load_2d(smem_b + s * C::B_STAGE_BYTES, &x_map, kb * PF_BLOCK_K, m_tile * TM, full + 8 * s);
+                    }
                 }
+                __syncwarp();
+                if (++s == S) { s = 0; ph ^= 1; }
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer: one thread drives the tensor core for the whole CTA =====
-        if (lane == 0) {
-            constexpr uint32_t idesc = make_idesc(PF_TILE_N, TM);
-            int s = 0; uint32_t ph = 0, ti = 0;
-            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++ti) {
-                mbar_wait(tmem_empty, (ti & 1) ^ 1);   // the epilogue has drained the previous tile
+        // ===== MMA issuer: the warp stays converged, one elected lane drives the tensor core for the CTA =====
+        constexpr uint32_t idesc = make_idesc(PF_TILE_N, TM);
+        int s = 0; uint32_t ph = 0, ti = 0;
+        const bool prof = p.debug & 4;
+        long long c_start = clock64(), w_f = 0, w_e = 0, w_m = 0, w_c = 0;
+        unsigned long long t_start = 0;
+        if (prof) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++ti) {
+            long long c0 = prof ? clock64() : 0;
+            mbar_wait(tmem_empty, (ti & 1) ^ 1);   // the epilogue has drained the previous tile
+            if (prof) w_e += clock64() - c0;
+            tc_fence_after();
+            for (int kb = 0; kb < KBLKS; ++kb) {
+                if (prof) c0 = clock64();
+                mbar_wait(full + 8 * s, ph);       // x tile landed and all 8 row blocks of A are in TMEM
+                if (prof) { long long c1 = clock64(); w_f += c1 - c0; c0 = c1; }
                 tc_fence_after();
-                for (int kb = 0; kb < KBLKS; ++kb) {
-                    mbar_wait(full_b + 8 * s, ph);
-                    mbar_wait(full_a + 8 * s, ph);
-                    tc_fence_after();
+                if (elect_one()) {
                     const uint64_t bdesc = make_b_desc(smem_b + s * C::B_STAGE_BYTES);
                     const uint32_t a_tmem = tmem_base + PF_A_COL0 + s * PF_A_STAGE_COLS;
 #pragma unroll
                     for (int k = 0; k < PF_BLOCK_K / 16; ++k)   // +32 bytes of k inside the swizzle atom = +2 in the address field
                         tc_mma_ts(tmem_base, a_tmem + k * 8, bdesc + 2 * k, idesc, (uint32_t)((kb | k) != 0));
+                    if (prof) { long long c1 = clock64(); w_m += c1 - c0; c0 = c1; }
                     tc_commit(empty + 8 * s);                   // frees the A columns and the B tile of this stage
                     if (kb == KBLKS - 1) tc_commit(tmem_full);  // accumulator complete
-                    if (++s == S) { s = 0; ph ^= 1; }
+                    if (prof) w_c += clock64() - c0;
                 }
+                __syncwarp();
+                if (++s == S) { s = 0; ph ^= 1; }
             }
         }
-    } else if (warp >= 4 && warp < 12) {
+        if (prof && lane == 0) {
+            unsigned long long t_end;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+            unsigned long long *d = p.dbg + blockIdx.x * 8;
+            d[0] = clock64() - c_start; d[1] = t_end - t_start; d[2] = w_f; d[3] = 0; d[4] = w_e; d[5] = ti;
+        }
+        if (prof && elect_one()) {
+            unsigned long long *d = p.dbg + blockIdx.x * 8;
+            d[6] = w_m; d[7] = w_c;
+        }
+    } else if (warp >= 4 && warp < 20) {
         // ===== dequant warps: W4T chunk -> bf16 fragments -> TMEM (A operand) =====
-        const int quarter = warp & 3, half = (warp - 4) >> 2;
+        // Two sets of 8 warps; set 0 fills the even k blocks, set 1 the odd ones (K % 128 == 0, so the
+        // number of k blocks per tile is even and a set keeps its parity across tiles).  Within a set,
+        // warp (quarter, half) owns the 16 rows at TMEM lanes 32*quarter + 16*half.
+        const int dq = warp - 4;
+        const int quarter = warp & 3, half = (dq >> 2) & 1, set = dq >> 3;
         const int rloc = quarter * 2 + half;
         const int g = lane >> 2;
         const uint32_t a_taddr = tmem_base + ((uint32_t)(quarter * 32 + half * 16) << 16) + PF_A_COL0;
         const int my_tiles = blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
         const int total = my_tiles * KBLKS;
+        const int nr = p.N >> 4;
 
-        int pf_tile = blockIdx.x, pf_kb = 0;
+        int pf_tile = blockIdx.x, pf_kb = set;
         const uint4 *pf_w = nullptr;
         const uint8_t *pf_m = nullptr;
         bool pf_valid = false;   // false for the row blocks of a 64-row tail tile that lie beyond N: they dequantise to 0
         auto set_tile = [&](int tile) {
-            const size_t R = (size_t)(tile % p.n_tiles) * 8 + rloc;
-            pf_valid = R < (size_t)(p.N >> 4);
-            pf_w = p.qw + R * p.KB * 32 + lane;
-            pf_m = p.meta + R * p.G * META_BYTES + 4 * g;
+            const int R = (tile % p.n_tiles) * 8 + rloc;
+            pf_valid = R < nr;
+            pf_w = p.qw + (size_t)R * p.KB * 32 + lane;
+            pf_m = p.meta + (size_t)R * p.G * META_BYTES + 4 * g;
         };
         if (pf_tile < ntiles) set_tile(pf_tile);
         auto fetch = [&](WEntry<GPS> &e) {
             if (pf_tile >= ntiles) return;
             if (pf_valid) {
-                e.w = ldg_nc_v4(pf_w + (size_t)pf_kb * 32);
+                e.w = ldg_nc_v4(pf_w + pf_kb * 32);
 #pragma unroll
                 for (int h = 0; h < GPS; ++h) {
                     const int grp = (pf_kb * PF_BLOCK_K + h * 32) >> p.gs_shift;
-                    const uint8_t *m = pf_m + (size_t)grp * META_BYTES;
+                    const uint8_t *m = pf_m + grp * META_BYTES;
                     e.s2[h] = __ldg(reinterpret_cast<const uint32_t *>(m));
                     e.zb[h] = __ldg(m + (META_ZERO_OFF - 3 * g));
                 }
@@ -275,8 +319,9 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
 #pragma unroll
                 for (int h = 0; h < GPS; ++h) { e.s2[h] = 0; e.zb[h] = 0; }
             }
-            if (++pf_kb == KBLKS) {
-                pf_kb = 0;
+            pf_kb += 2;
+            if (pf_kb >= KBLKS) {
+                pf_kb -= KBLKS;
                 pf_tile += gridDim.x;
                 if (pf_tile < ntiles) set_tile(pf_tile);
             }
@@ -285,11 +330,11 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
 #pragma unroll
         for (int u = 0; u < PF_WPREF; ++u) fetch(ring[u]);
 
-        int s = 0; uint32_t ph = 0;
-        for (int it0 = 0; it0 < total; it0 += PF_WPREF) {
+        int s = set; uint32_t ph = 0;   // stage / phase of global k-block iteration `it` (it = set, set+2, ...)
+        for (int it0 = set; it0 < total; it0 += 2 * PF_WPREF) {
 #pragma unroll
             for (int u = 0; u < PF_WPREF; ++u) {
-                if (it0 + u < total) {
+                if (it0 + 2 * u < total) {
                     const WEntry<GPS> &e = ring[u];
                     const uint32_t wj[4] = {e.w.x, e.w.y, e.w.z, e.w.w};
                     uint32_t r[16];
@@ -306,18 +351,21 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
                     fetch(ring[u]);
                     mbar_wait(empty + 8 * s, ph ^ 1);   // the MMAs that read this stage's columns have retired
                     tc_fence_after();
+                    if (!(p.debug & 2)) {
                     tc_st_16x256b_x4(a_taddr + s * PF_A_STAGE_COLS, r);
                     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                    }
                     tc_fence_before();
-                    if (lane == 0) mbar_arrive(full_a + 8 * s);
-                    if (++s == S) { s = 0; ph ^= 1; }
+                    if (lane == 0) mbar_arrive(full + 8 * s);
+                    s += 2;
+                    if (s >= S) { s -= S; ph ^= 1; }
                 }
             }
         }
-    } else if (warp >= 12) {
+    } else if (warp >= 20) {
         // ===== epilogue warps: TMEM -> +bias -> bf16 -> staging -> y =====
         const int q = warp & 3;
-        const int et = threadIdx.x - 12 * 32;   // 0..127
+        const int et = threadIdx.x - 20 * 32;   // 0..127
         uint32_t ti = 0;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++ti) {
             const int n_tile = tile % p.n_tiles, m_tile = tile / p.n_tiles;
@@ -416,6 +464,14 @@ int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
     p.gs_shift = gs == L.d.K && gs != 32 && gs != 64 && gs != 128 ? 31 : (gs == 32 ? 5 : gs == 64 ? 6 : 7);
     p.n_tiles = (int)((L.d.N + PF_TILE_N - 1) / PF_TILE_N);  // N % 64 == 0: the last tile may be half full
     p.m_tiles = (int)((M + TM - 1) / TM);
+    { const char *dv = getenv("W4A16_PF_DEBUG"); p.debug = dv ? atoi(dv) : 0; }
+    static unsigned long long *dbg_buf = nullptr;
+    p.dbg = nullptr;
+    if (p.debug & 4) {
+        if (!dbg_buf) W4_CUDA_OK(cudaMalloc(&dbg_buf, 256 * 8 * sizeof(unsigned long long)));
+        W4_CUDA_OK(cudaMemsetAsync(dbg_buf, 0, 256 * 8 * sizeof(unsigned long long), stream));
+        p.dbg = dbg_buf;
+    }
 
     CUtensorMap map;
     const cuuint64_t gdim[2] = {(cuuint64_t)L.d.K, (cuuint64_t)M};
@@ -435,10 +491,21 @@ int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
         if (gps == 1) return launch_pf<TM_, 1>(map, p, grid, stream);       \
         return launch_pf<TM_, 2>(map, p, grid, stream);                     \
     } while (0)
-    if (TM == 256) W4_PF(256);
-    if (TM == 128) W4_PF(128);
-    W4_PF(64);
+    int rc;
+    if (TM == 256) rc = [&] { W4_PF(256); }();
+    else if (TM == 128) rc = [&] { W4_PF(128); }();
+    else rc = [&] { W4_PF(64); }();
 #undef W4_PF
+    if (rc == 0 && (p.debug & 4)) {
+        static unsigned long long h[256 * 8];
+        W4_CUDA_OK(cudaStreamSynchronize(stream));
+        W4_CUDA_OK(cudaMemcpy(h, dbg_buf, sizeof(h), cudaMemcpyDeviceToHost));
+        double cyc = 0, ns = 0, wb = 0, wa = 0, we = 0, wm = 0, wc = 0; int n = 0;
+        for (int i = 0; i < grid && i < 256; ++i) { cyc += h[i*8]; ns += h[i*8+1]; wb += h[i*8+2]; wa += h[i*8+3]; we += h[i*8+4]; wm += h[i*8+6]; wc += h[i*8+7]; ++n; }
+        fprintf(stderr, "[pf dbg] grid=%d tiles/cta=%llu cycles=%.0f ns=%.0f clk=%.3f GHz wait_full_b=%.1f%% wait_full_a=%.1f%% wait_tmem_empty=%.1f%% mma_issue=%.1f%% commit=%.1f%%\n",
+                grid, h[5], cyc / n, ns / n, cyc / ns, 100 * wb / cyc, 100 * wa / cyc, 100 * we / cyc, 100 * wm / cyc, 100 * wc / cyc);
+    }
+    return rc;
 }
 
 }  // namespace w4
