@@ -161,6 +161,11 @@ const char *w4a16_kernel_for(w4a16_handle_t h, int64_t M);
 /* Override dispatch for experiments: "auto" | "decode" | "prefill".  Returns non-zero if unknown. */
 int w4a16_set_dispatch(const char *mode);
 
+/* Profiling hook (W4A16_GV_DEBUG=1 in the environment): the decode kernel stamps %globaltimer per CTA
+ * {start, dependency wait passed, activations staged, weights streamed, CTA combined, end, -, -} into a
+ * ring of 4 launches x 1024 CTAs x 8 words; this copies the ring out (synchronises the device). */
+int w4a16_debug_stamps(uint64_t *out, int64_t words, uint64_t *launches);
+
 #ifdef __cplusplus
 }
 #endif

@@ -219,17 +219,22 @@ def test_tp_shards_compose(product, tp):
     xb = O.make_activations(M, K, seed=8)
     x = t_bf16_from_bits(xb).to(DEV)
     cfg = product.AwqConfig.int4(g)
-    # column parallel: concatenated shard outputs == the full layer, bit for bit
+    # column parallel: concatenated shard outputs == the full layer (the fp32 summation order follows
+    # the work partition, which depends on N: equal to within bf16 rounding, each within tolerance)
     full = cfg.create_linear(K, N, True, DEV)
     full.load_weights(w)
     y_full = bits_of(full.forward(x))
+    want_full = oracle_forward(xb, q, z, sb, g, bias_f32=O.np_bf16_round(b))
     cols = []
     for r in range(tp):
         sh = cfg.create_linear(K, N, True, DEV, tp_mode=1, tp_rank=r, tp_size=tp)
         sh.load_weights(w)
         assert sh.out_features() == N // tp and sh.in_features() == K
         cols.append(bits_of(sh.forward(x)))
-    assert (np.concatenate(cols, axis=1) == y_full).all()
+    y_cat = np.concatenate(cols, axis=1)
+    assert_close_ref(y_cat, want_full, f"column shards tp={tp}")
+    diff = np.abs(O.np_bf16_bits_to_f32(y_cat) - O.np_bf16_bits_to_f32(y_full))
+    assert diff.max() <= 2.0 ** -7 * np.abs(want_full).max()
     # row parallel: sum of partials (no bias) + bias == oracle within tolerance
     acc = np.zeros((M, N), np.float64)
     for r in range(tp):

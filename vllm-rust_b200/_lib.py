@@ -62,6 +62,7 @@ SIGNATURES = {
     "w4a16_kernel_launches": (_u64, []),
     "w4a16_kernel_for": (ctypes.c_char_p, [_vp, _i64]),
     "w4a16_set_dispatch": (_i32, [ctypes.c_char_p]),
+    "w4a16_debug_stamps": (_i32, [_vp, _i64, ctypes.POINTER(_u64)]),
 }
 
 _lib = None

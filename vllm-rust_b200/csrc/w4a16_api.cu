@@ -436,10 +436,17 @@ int64_t w4a16_weight_bytes(w4a16_handle_t h) {
     return qw_bytes(L->d) + meta_bytes(L->d);
 }
 const char *w4a16_kernel_for(w4a16_handle_t h, int64_t M) {
-    (void)h;
+    if (!h) return "none";
     bool want_prefill = g_dispatch == "prefill" || (g_dispatch == "auto" && M > DECODE_MAX_M);
     if (want_prefill && prefill_available()) return "prefill_umma";
-    return decode_kernel_name(std::min<int64_t>(M, DECODE_MAX_M));
+    return decode_kernel_name(*reinterpret_cast<Linear *>(h), std::min<int64_t>(M, DECODE_MAX_M));
+}
+int w4a16_debug_stamps(uint64_t *out, int64_t words, uint64_t *launches) {
+    if (!out) return fail("debug_stamps: null buffer");
+    unsigned long long n = 0;
+    if (gemv_debug_read(reinterpret_cast<unsigned long long *>(out), words, &n)) return 1;
+    if (launches) *launches = n;
+    return 0;
 }
 int w4a16_set_dispatch(const char *mode) {
     if (!mode) return fail("set_dispatch: null mode");

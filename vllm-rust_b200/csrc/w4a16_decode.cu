@@ -21,6 +21,8 @@
 // Programmatic dependent launch: the weight prefetch is issued BEFORE griddepcontrol.wait,
 // so in a stream of linears the next layer's weights are already in flight while the
 // previous kernel drains; x / y / scratch are only touched after the wait.
+#include <algorithm>
+
 #include "w4a16_internal.cuh"
 #include "w4a16_dequant.cuh"
 
@@ -313,6 +315,7 @@ int decode_scratch_need(const Linear &L, int sm_count, int64_t *scratch_floats, 
     // worst case over the env overrides is bounded by sc <= 64
     DecodeCfg c = pick_cfg(L, sm_count);
     *scratch_floats = c.sc > 1 ? (int64_t)c.sc * L.d.NR * 4 * 32 * 4 : 0;  // [SC][NR][NT<=4][32] float4
+    *scratch_floats = std::max<int64_t>(*scratch_floats, gemv_scratch_floats(sm_count));
     *tickets = L.d.NR;  // >= gridDim.x for any WR
     return 0;
 }
@@ -334,13 +337,15 @@ static int launch_t(const DecodeParams &p, dim3 grid, cudaStream_t stream, bool 
     return 0;
 }
 
-const char *decode_kernel_name(int64_t M) {
+const char *decode_kernel_name(const Linear &L, int64_t M) {
+    if (gemv_stream_usable(L, M, L.scratch->sm_count)) return M <= 8 ? "gemv_stream_nt1" : "gemv_stream_nt2";
     return M <= 8 ? "decode_mma_nt1" : M <= 16 ? "decode_mma_nt2" : "decode_mma_nt4";
 }
 
 int launch_decode(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
                   cudaStream_t stream) {
     if (M < 1 || M > 32) return fail("launch_decode: M must be in 1..32");
+    if (gemv_stream_usable(L, M, L.scratch->sm_count)) return launch_gemv_stream(L, x, y, M, add_bias, stream);
     const int gs = L.d.gs;
     DecodeCfg c = pick_cfg(L, L.scratch->sm_count);
     DecodeParams p;

@@ -88,8 +88,14 @@ int launch_add_bias(__nv_bfloat16 *y, const __nv_bfloat16 *bias, int64_t M, int6
 // decode: M <= 32 tokens per launch
 int launch_decode(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
                   cudaStream_t stream);
-const char *decode_kernel_name(int64_t M);
+const char *decode_kernel_name(const Linear &L, int64_t M);
 int decode_scratch_need(const Linear &L, int sm_count, int64_t *scratch_floats, int64_t *tickets);
+// decode, M <= 16: the single-wave stream kernel (w4a16_gemv.cu); the register-ring kernel above is its fallback
+bool gemv_stream_usable(const Linear &L, int64_t M, int sm_count);
+int64_t gemv_scratch_floats(int sm_count);
+int launch_gemv_stream(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
+                       cudaStream_t stream);
+int gemv_debug_read(unsigned long long *out, int64_t words, unsigned long long *launches);
 // prefill (tcgen05): any M
 int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
                    cudaStream_t stream);
