@@ -19,60 +19,79 @@
 // B operand from shared memory.  5 ALU + 1 LDS + 1 HMMA issue slots per 8 weights x 8 tokens.
 //
 // Work distribution: the W4T weight array is ONE linear stream of 1 KB units (16 rows x 128 k).  It is
-// cut into gridDim.x equal contiguous ranges (+-1 unit), one CTA each, grid = 2 x SM count = one wave
-// with half of every SM's registers left free, so that under programmatic dependent launch the NEXT
-// linear's CTAs are already resident and have their first weights in flight while this one drains.
-// Inside a CTA the 8 warps take units round-robin; each keeps GV_DEPTH units (4 KB) in flight in
-// registers.  Partial sums of a 16-row block are combined in a fixed order: across the warps of a CTA in
-// shared memory, across the (at most two, for ranges >= one row block) CTAs that share a row block through
-// a per-handle scratch and a self-resetting ticket.  No atomics on data: results are deterministic.
+// cut into gridDim.x contiguous ranges (a per-handle table, equal to +-1 unit), one CTA of 16 warps per SM.
+// A CTA pulls its range through a shared-memory ring of 16 KB stages with cp.async.bulk (TMA bulk copy,
+// mbarrier complete_tx); the copies are issued BEFORE griddepcontrol.wait and a CTA uses at most half of an
+// SM (registers and shared memory), so under programmatic dependent launch the NEXT linear's CTAs are
+// already resident and have up to ~100 KB of weights per SM landed while this one still computes: the HBM
+// stream keeps running across the per-kernel dependency / staging / combine latencies.
+// Inside a stage warp w owns unit w.  Partial sums of a 16-row block are combined in a fixed order: across
+// the warps of a CTA in shared memory, across the CTAs that share a row block through a per-handle scratch
+// and a self-resetting ticket.  No atomics on data: results are deterministic.
+#include <algorithm>
+#include <vector>
+
 #include "w4a16_internal.cuh"
 #include "w4a16_dequant.cuh"
 
 namespace w4 {
 
-constexpr int GV_THREADS = 256;
-constexpr int GV_WARPS = 8;
-constexpr int GV_DEPTH = 4;      // units a warp keeps in flight
-constexpr int GV_UNIT_K = 128;   // 2 chunks = 1 KB of weights
-constexpr int GV_UNIT_V4 = 64;   // uint4 per unit
+constexpr int GV_THREADS = 512;
+constexpr int GV_WARPS = 16;
+constexpr int GV_UNIT_K = 128;        // 2 chunks = 1 KB of weights
+constexpr int GV_UNIT_BYTES = 1024;
+constexpr int GV_STAGE_UNITS = GV_WARPS;
+constexpr int GV_STAGE_W_BYTES = GV_STAGE_UNITS * GV_UNIT_BYTES;
+constexpr int GV_MAX_STAGES = 12;
+constexpr int GV_SMEM_HALF_SM = 112 * 1024;   // two CTAs (this linear + the prefetching next one) per SM
+constexpr int GV_SMEM_FULL_SM = 220 * 1024;
+constexpr uint32_t GV_SPIN_LIMIT = 1u << 26;
 
 struct GemvParams {
-    const uint4 *qw;
+    const uint8_t *qw;
     const uint8_t *meta;
     const __nv_bfloat16 *bias;  // null: no bias add in this launch
     const __nv_bfloat16 *x;
     __nv_bfloat16 *y;
     float4 *scratch;            // [grid][2][P][8] boundary partials
     int32_t *tickets;           // [NR]
+    const int4 *tab;            // [grid][2]: {a, b, first_lo, first_hi}, {last_lo, last_hi, -, -}
     int M, K, N;
     int UPR;                    // units per row block = K / 128
-    int UT;                     // total units
-    int q, r;                   // CTA i owns units [i*q + min(i,r), +q + (i<r))
     int meta_stride;            // bytes of meta per unit (MPU*48), 0 for per-channel scales
-    int G;                      // groups per row block (meta row stride = G*48)
     int P;                      // ceil(M/2): fragment column pairs that hold real tokens
-    int n_slots;                // row blocks a CTA range can touch
+    int n_stages_ring;          // stages in the shared-memory ring
+    int stage_m_bytes;          // meta bytes per ring stage (16-byte multiple)
     // shared-memory carve-up (bytes from the start of dynamic smem)
-    int off_xsum, off_tok, off_part;
+    int off_xs, off_gtab, off_flags, off_part, off_wring, off_mring;
     unsigned long long *dbg;    // W4A16_GV_DEBUG: per-CTA globaltimer stamps {start, after wait, staged, streamed, combined, end}
 };
 
-__device__ __forceinline__ uint4 gv_ldg_stream(const uint4 *p) {
-    uint4 r;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-    return r;
+__device__ __forceinline__ uint32_t gv_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void gv_mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }
-__device__ __forceinline__ uint32_t gv_ldg_u32(const void *p) {
-    uint32_t r;
-    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
-    return r;
+__device__ __forceinline__ void gv_mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ uint32_t gv_ldg_u8(const void *p) {
-    uint32_t r;
-    asm volatile("ld.global.nc.L1::no_allocate.u8 %0, [%1];" : "=r"(r) : "l"(p));
-    return r;
+__device__ __forceinline__ uint32_t gv_mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok;
+}
+// A wait that cannot hang the GPU: a lost completion traps (the launch fails loudly).
+__device__ __forceinline__ void gv_mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t spins = 0;
+    while (!gv_mbar_try_wait(bar, parity))
+        if (++spins > GV_SPIN_LIMIT) __trap();
+}
+__device__ __forceinline__ void gv_bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 __device__ __forceinline__ uint32_t gv_lop3_and_or(uint32_t a, uint32_t b, uint32_t c) {
     uint32_t r;
@@ -97,69 +116,69 @@ __device__ __forceinline__ void gv_mma_f16(float (&c)[4], uint32_t a0, uint32_t 
     }
 }
 
-// One prefetched unit: 2 chunks (8 words per lane) + scale pair / zero byte of each group inside it.
-template <int MPU>
-struct GvUnit {
-    uint4 w[2];
-    uint32_t s2[MPU];
-    uint32_t zb[MPU];
-};
-
-// ms: this lane's scale pair of the unit's first group (meta block + 4g); zoff = META_ZERO_OFF - 3g reaches its zero byte.
-template <int MPU>
-__device__ __forceinline__ void gv_load_unit(GvUnit<MPU> &u, const uint4 *wp, const uint8_t *ms, int zoff) {
-    u.w[0] = gv_ldg_stream(wp);
-    u.w[1] = gv_ldg_stream(wp + 32);
-#pragma unroll
-    for (int h = 0; h < MPU; ++h) {
-        u.s2[h] = gv_ldg_u32(ms + h * META_BYTES);
-        u.zb[h] = gv_ldg_u8(ms + h * META_BYTES + zoff);
-    }
+__device__ __forceinline__ int gv_dp4a_u8s8(uint32_t a_u8x4, uint32_t b_s8x4, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a_u8x4), "r"(b_s8x4), "r"(c));
+    return d;
+}
+__device__ __forceinline__ uint32_t gv_pack4(int b0, int b1, int b2, int b3) {
+    return (uint32_t)(b0 & 0xFF) | ((uint32_t)(b1 & 0xFF) << 8) | ((uint32_t)(b2 & 0xFF) << 16) | ((uint32_t)(b3 & 0xFF) << 24);
 }
 
 // MR = token rows held in shared memory (M rounded up to 1, 2, 4, 8 or 16).  NT = MMA token tiles.
+// MR <= 2 runs on the integer dot-product path (see the header); MR >= 4 on mma.sync.
 template <int MR, int MPU>
-__global__ void __launch_bounds__(GV_THREADS, MR <= 8 ? 3 : 2) gemv_stream_kernel(const GemvParams p) {
+__global__ void __launch_bounds__(GV_THREADS, MR <= 8 ? 2 : 1) gemv_stream_kernel(const GemvParams p) {
+    constexpr bool DP = MR <= 2;
     constexpr int NT = MR <= 8 ? 1 : MR / 8;
     constexpr int PAIRS = MR < 2 ? 1 : MR / 2;     // token pairs per row of the group table
     constexpr int MMAS_PER_GROUP = 8 / MPU;
     constexpr int SUB_K = GV_UNIT_K / MPU;         // k per (sub)group inside a unit
-    extern __shared__ __align__(16) uint8_t gv_smem[];
-    uint2 *xs = reinterpret_cast<uint2 *>(gv_smem);                          // [K/4][MR] 4 x fp16
-    float *gtab = reinterpret_cast<float *>(gv_smem + p.off_xsum);           // [K/SUB_K][PAIRS] {X0, X1, 2^e0, 2^e1}
-    int *flags = reinterpret_cast<int *>(gv_smem + p.off_tok);               // [2]
+    extern __shared__ __align__(128) uint8_t gv_smem[];
+    uint64_t *bars = reinterpret_cast<uint64_t *>(gv_smem);                  // full[GV_MAX_STAGES]
+    uint32_t *consumed = reinterpret_cast<uint32_t *>(gv_smem + 8 * GV_MAX_STAGES);   // [GV_MAX_STAGES] arrival counters
+    uint2 *xs = reinterpret_cast<uint2 *>(gv_smem + p.off_xs);               // [K/4][MR] 4 x fp16
+    float *gtab = reinterpret_cast<float *>(gv_smem + p.off_gtab);           // [K/SUB_K][PAIRS] {X0, X1, 2^e0, 2^e1}
+    int *flags = reinterpret_cast<int *>(gv_smem + p.off_flags);             // [2]
     float4 *part = reinterpret_cast<float4 *>(gv_smem + p.off_part);         // [n_slots][GV_WARPS][P][8]
+    const uint8_t *wring = gv_smem + p.off_wring;
+    const uint8_t *mring = gv_smem + p.off_mring;
+    const uint32_t bar0 = gv_smem_u32(bars);
+    const uint32_t wring_s = gv_smem_u32(wring), mring_s = gv_smem_u32(mring);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t = lane & 3;
     const int cta = blockIdx.x;
-    const int a = cta * p.q + min(cta, p.r);
-    const int n_cta = p.q + (cta < p.r ? 1 : 0);
-    const int b = a + n_cta;
-    const int n_w = warp < n_cta ? (n_cta - warp + GV_WARPS - 1) / GV_WARPS : 0;  // units of this warp
+    const int4 rec0 = __ldg(p.tab + 2 * cta), rec1 = __ldg(p.tab + 2 * cta + 1);
+    const int a = rec0.x, b = rec0.y;
+    const int n_cta = b - a;
+    const int n_stages = (n_cta + GV_STAGE_UNITS - 1) / GV_STAGE_UNITS;
+    const int S = p.n_stages_ring;
     const int R_first = a / p.UPR;
 
-    // ---- prefetch (weights and meta are immutable: independent of the previous kernel) ----
-    const int u0 = a + warp;
-    int R_l = u0 / p.UPR, ku_l = u0 - R_l * p.UPR;   // load cursor (per-channel meta needs R)
-    const uint4 *wp = p.qw + (size_t)u0 * GV_UNIT_V4 + lane;
-    const uint8_t *meta_g = p.meta + 4 * g;
-    const int zoff = META_ZERO_OFF - 3 * g;
-    auto meta_ptr = [&](int R, int ku) -> const uint8_t * {
-        return meta_g + ((size_t)R * p.G) * META_BYTES + (size_t)ku * p.meta_stride;
+    // stage j of this CTA's range -> ring slot j % S
+    auto issue_stage = [&](int j) {
+        const int s = j % S;
+        const int u_lo = a + j * GV_STAGE_UNITS;
+        const int cnt = min(GV_STAGE_UNITS, b - u_lo);
+        const uint32_t wb = (uint32_t)cnt * GV_UNIT_BYTES, mb = (uint32_t)cnt * (uint32_t)p.meta_stride;
+        const uint32_t bar = bar0 + 8 * s;
+        gv_mbar_expect_tx(bar, wb + mb);
+        gv_bulk_g2s(wring_s + s * GV_STAGE_W_BYTES, p.qw + (size_t)u_lo * GV_UNIT_BYTES, wb, bar);
+        if (mb) gv_bulk_g2s(mring_s + s * p.stage_m_bytes, p.meta + (size_t)u_lo * p.meta_stride, mb, bar);
     };
-    GvUnit<MPU> ring[GV_DEPTH];
-#pragma unroll
-    for (int d = 0; d < GV_DEPTH; ++d) {
-        if (d < n_w) {
-            gv_load_unit<MPU>(ring[d], wp + (size_t)d * GV_WARPS * GV_UNIT_V4, meta_ptr(R_l, ku_l), zoff);
-            ku_l += GV_WARPS;
-            while (ku_l >= p.UPR) { ku_l -= p.UPR; ++R_l; }
-        }
+
+    // ---- prefetch (weights and meta are immutable: independent of the previous kernel) ----
+    if (tid == 0) {
+        for (int s = 0; s < S; ++s) { gv_mbar_init(bar0 + 8 * s, 1); consumed[s] = 0; }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        const int first = min(S, n_stages);
+        for (int j = 0; j < first; ++j) issue_stage(j);
     }
-    // zero the partial-sum slots (a warp may never visit some row block of the range)
-    {
-        const int n4 = p.n_slots * GV_WARPS * p.P * 8;
+    {   // zero the partial-sum slots (a warp may never visit some row block of the range)
+        const int R_last0 = n_cta > 0 ? (b - 1) / p.UPR : R_first - 1;
+        const int n4 = (R_last0 - R_first + 1) * GV_WARPS * p.P * 8;
         for (int i = tid; i < n4; i += GV_THREADS) part[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     auto stamp = [&](int i) {
@@ -177,6 +196,54 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 8 ? 3 : 2) gemv_stream_kerne
     // ---- stage the activations: per-(group, token) power-of-two scale, fp16, fragment order, group sums ----
     // One pass: the SUB_K/8 consecutive lanes that hold a (sub)group agree on its max by shuffles.
     const int ppr = p.K >> 3;  // 16-byte pieces per token row
+    if constexpr (DP) {
+        // Integer path: xt rounded to an integer in [-16383, 16383] (exact for every element within 2^6 of the
+        // group's maximum, |error| <= 2^-14 of that maximum below), split into two signed-byte planes
+        // xt = 128*hi + lo, packed per 4-k quad in the byte order (k0,k2,k1,k3) of the weight nibbles.
+        int *gti = reinterpret_cast<int *>(gtab);                    // [K/SUB_K][MR]{sum_t0..3, 2^e, -, -, -}
+        for (int m = 0; m < p.M; ++m) {
+            for (int c0 = tid - lane; c0 < ppr; c0 += GV_THREADS) {
+                const int c = c0 + lane;
+                const bool live = c < ppr;
+                uint4 v = make_uint4(0, 0, 0, 0);
+                if (live) v = __ldg(reinterpret_cast<const uint4 *>(p.x + (size_t)m * p.K) + c);
+                const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+                uint32_t mx = 0;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) mx = max(mx, max(w4[i] & 0x7FFFu, (w4[i] >> 16) & 0x7FFFu));
+#pragma unroll
+                for (int o = SUB_K / 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+                int E = (int)(mx >> 7);
+                E = min(max(E, 14), 254);
+                const float scale = __int_as_float((267 - E) << 23);
+                int xi[8];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    xi[2 * i] = __float2int_rn(__uint_as_float(w4[i] << 16) * scale);
+                    xi[2 * i + 1] = __float2int_rn(__uint_as_float(w4[i] & 0xFFFF0000u) * scale);
+                }
+                int sumA = xi[0] + xi[1] + xi[2] + xi[3], sumB = xi[4] + xi[5] + xi[6] + xi[7];
+#pragma unroll
+                for (int o = SUB_K / 16; o > 1; o >>= 1) {   // pieces of equal parity share the quad positions t
+                    sumA += __shfl_xor_sync(0xffffffffu, sumA, o);
+                    sumB += __shfl_xor_sync(0xffffffffu, sumB, o);
+                }
+                if (live) {
+                    xs[(size_t)(2 * c) * MR + m] = make_uint2(gv_pack4(xi[0] >> 7, xi[2] >> 7, xi[1] >> 7, xi[3] >> 7),
+                                                              gv_pack4(xi[0] & 127, xi[2] & 127, xi[1] & 127, xi[3] & 127));
+                    xs[(size_t)(2 * c + 1) * MR + m] = make_uint2(gv_pack4(xi[4] >> 7, xi[6] >> 7, xi[5] >> 7, xi[7] >> 7),
+                                                                  gv_pack4(xi[4] & 127, xi[6] & 127, xi[5] & 127, xi[7] & 127));
+                    const int in_grp = c & (SUB_K / 8 - 1);
+                    if (in_grp < 2) {
+                        int *e = gti + ((size_t)(c / (SUB_K / 8)) * MR + m) * 8;
+                        e[2 * in_grp] = sumA;
+                        e[2 * in_grp + 1] = sumB;
+                        if (in_grp == 0) e[4] = (E - 13) << 23;      // bits of 2^e: undoes the scale
+                    }
+                }
+            }
+        }
+    } else {
     for (int m = 0; m < p.M; ++m) {
         for (int c0 = tid - lane; c0 < ppr; c0 += GV_THREADS) {   // warp-uniform trip count: the shuffles need all lanes
             const int c = c0 + lane;
@@ -215,22 +282,38 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 8 ? 3 : 2) gemv_stream_kerne
             }
         }
     }
+    }
     __syncthreads();
     stamp(2);
 
-    // ---- main loop ----
+    // ---- main loop: stage j, unit a + 16j + warp ----
     float yacc[NT][4];
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
         for (int i = 0; i < 4; ++i) yacc[nt][i] = 0.f;
-    int R_c = u0 / p.UPR, ku_c = u0 - R_c * p.UPR;   // compute cursor
+    int u = a + warp;
+    int R_c = u / p.UPR, ku_c = u - R_c * p.UPR;   // cursor of this warp's unit
+    int R_acc = -1;                                // row block whose partial sums yacc holds (-1: none)
     // per-lane shared-memory bases: x fragment of MMA jm in unit ku = xs[((32*ku + 4*jm + t) * MR + row)]
     const uint2 *xb[NT];
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) xb[nt] = xs + t * MR + min(nt * 8 + g, p.M - 1);
     auto flush = [&](int R) {
         float4 *dst = part + ((size_t)(R - R_first) * GV_WARPS + warp) * p.P * 8 + g;
+        if constexpr (DP) {   // yacc[0] = {row g tok0, row g tok1, row g+8 tok0, row g+8 tok1} over this lane's k-slots
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                float v = yacc[0][i];
+                v += __shfl_xor_sync(0xffffffffu, v, 1);
+                v += __shfl_xor_sync(0xffffffffu, v, 2);
+                yacc[0][i] = v;
+            }
+            if (t == 0) dst[0] = make_float4(yacc[0][0], yacc[0][1], yacc[0][2], yacc[0][3]);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) yacc[0][i] = 0.f;
+            return;
+        }
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) {
             const int pp = nt * 4 + t;
@@ -240,67 +323,140 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 8 ? 3 : 2) gemv_stream_kerne
         }
     };
 
-    for (int base = 0; base < n_w; base += GV_DEPTH) {
-#pragma unroll
-        for (int d = 0; d < GV_DEPTH; ++d) {
-            if (base + d < n_w) {
-                const GvUnit<MPU> &u = ring[d];
-                const uint32_t wj[8] = {u.w[0].x, u.w[0].y, u.w[0].z, u.w[0].w, u.w[1].x, u.w[1].y, u.w[1].z, u.w[1].w};
+    int s = 0;
+    uint32_t phase = 0;
+    for (int j = 0; j < n_stages; ++j) {
+        gv_mbar_wait(bar0 + 8 * s, phase);
+        if (u < b) {
+            if (R_acc >= 0 && R_acc != R_c) flush(R_acc);
+            R_acc = R_c;
+            const uint4 *wsrc = reinterpret_cast<const uint4 *>(wring + s * GV_STAGE_W_BYTES + warp * GV_UNIT_BYTES) + lane;
+            const uint4 w0 = wsrc[0], w1 = wsrc[32];
+            uint32_t s2[MPU], zb[MPU];
+            if (p.meta_stride) {
+                const uint8_t *m = mring + s * p.stage_m_bytes + warp * (MPU * META_BYTES);
 #pragma unroll
                 for (int h = 0; h < MPU; ++h) {
-                    float acc[NT][4];
+                    s2[h] = *reinterpret_cast<const uint32_t *>(m + h * META_BYTES + 4 * g);
+                    zb[h] = m[h * META_BYTES + META_ZERO_OFF + g];
+                }
+            } else {   // per-channel scales: one meta block per row block, read through L1
+                const uint8_t *m = p.meta + (size_t)R_c * META_BYTES;
+                s2[0] = __ldg(reinterpret_cast<const uint32_t *>(m + 4 * g));
+                zb[0] = __ldg(m + META_ZERO_OFF + g);
+            }
+            const uint32_t wj[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+            if constexpr (DP) {
+                const int *gti = reinterpret_cast<const int *>(gtab);
+#pragma unroll
+                for (int h = 0; h < MPU; ++h) {
+                    int acc[MR][4];
+#pragma unroll
+                    for (int m = 0; m < MR; ++m)
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) acc[m][i] = 0;
 #pragma unroll
                     for (int jj = 0; jj < MMAS_PER_GROUP; ++jj) {
                         const int jm = h * MMAS_PER_GROUP + jj;
-                        const uint32_t w = wj[jm], v = w >> 8;
-                        const uint32_t a0 = gv_lop3_and_or(w, 0x000F000Fu, 0x64006400u);  // row g  : 1024 + q, k-slots 4t, 4t+1
-                        const uint32_t a1 = gv_lop3_and_or(w, 0x00F000F0u, 0x54005400u);  // row g+8:   64 + q, k-slots 4t, 4t+1
-                        const uint32_t a2 = gv_lop3_and_or(v, 0x000F000Fu, 0x64006400u);  // row g  : k-slots 4t+2, 4t+3
-                        const uint32_t a3 = gv_lop3_and_or(v, 0x00F000F0u, 0x54005400u);  // row g+8: k-slots 4t+2, 4t+3
+                        const uint32_t w = wj[jm];
+                        const uint32_t ev = w & 0x0F0F0F0Fu;          // row g  , k-slots (4t, 4t+2, 4t+1, 4t+3)
+                        const uint32_t od = (w >> 4) & 0x0F0F0F0Fu;   // row g+8, same k-slots
 #pragma unroll
-                        for (int nt = 0; nt < NT; ++nt) {
-                            const uint2 xf = xb[nt][(size_t)(32 * ku_c + 4 * jm) * MR];
-                            if (jj == 0) gv_mma_f16<true>(acc[nt], a0, a1, a2, a3, xf.x, xf.y);
-                            else gv_mma_f16<false>(acc[nt], a0, a1, a2, a3, xf.x, xf.y);
+                        for (int m = 0; m < MR; ++m) {
+                            const uint2 xv = xs[(size_t)(32 * ku_c + 4 * jm + t) * MR + min(m, p.M - 1)];
+                            acc[m][0] = gv_dp4a_u8s8(ev, xv.x, acc[m][0]);
+                            acc[m][1] = gv_dp4a_u8s8(ev, xv.y, acc[m][1]);
+                            acc[m][2] = gv_dp4a_u8s8(od, xv.x, acc[m][2]);
+                            acc[m][3] = gv_dp4a_u8s8(od, xv.y, acc[m][3]);
                         }
                     }
-                    const float slo = __uint_as_float(u.s2[h] << 16), shi = __uint_as_float(u.s2[h] & 0xFFFF0000u);
-                    // exact floats 1024 + z (rows g) and 64 + z (rows g+8)
-                    const float zlo = __uint_as_float(0x44800000u + ((u.zb[h] & 0x0Fu) << 13));
-                    const float zhi = __uint_as_float(0x42800000u + ((u.zb[h] & 0xF0u) << 13));
+                    const float slo = __uint_as_float(s2[h] << 16), shi = __uint_as_float(s2[h] & 0xFFFF0000u);
+                    const int zlo = (int)(zb[h] & 0x0Fu), zhi = (int)(zb[h] >> 4);
 #pragma unroll
-                    for (int nt = 0; nt < NT; ++nt) {
-                        const float4 X = *reinterpret_cast<const float4 *>(
-                            gtab + ((size_t)(ku_c * MPU + h) * PAIRS + (PAIRS == 1 ? 0 : nt * 4 + t)) * 4);
-                        const float sl0 = slo * X.z, sl1 = slo * X.w, sh0 = shi * X.z, sh1 = shi * X.w;
-                        yacc[nt][0] = fmaf(sl0, fmaf(-zlo, X.x, acc[nt][0]), yacc[nt][0]);
-                        yacc[nt][1] = fmaf(sl1, fmaf(-zlo, X.y, acc[nt][1]), yacc[nt][1]);
-                        yacc[nt][2] = fmaf(sh0, fmaf(-zhi, X.x, acc[nt][2]), yacc[nt][2]);
-                        yacc[nt][3] = fmaf(sh1, fmaf(-zhi, X.y, acc[nt][3]), yacc[nt][3]);
+                    for (int m = 0; m < MR; ++m) {
+                        const int *e = gti + ((size_t)(ku_c * MPU + h) * MR + min(m, p.M - 1)) * 8;
+                        const int xsum = e[t];
+                        const float e2 = __int_as_float(e[4]);
+                        const int tg = acc[m][0] * 128 + acc[m][1] - zlo * xsum;     // exact: |.| < 2^24
+                        const int tg8 = acc[m][2] * 128 + acc[m][3] - zhi * xsum;
+                        yacc[0][m] = fmaf(slo * e2, (float)tg, yacc[0][m]);
+                        yacc[0][2 + m] = fmaf(shi * e2, (float)tg8, yacc[0][2 + m]);
                     }
                 }
-                // refill this ring slot GV_DEPTH units ahead
-                if (base + d + GV_DEPTH < n_w) {
-                    gv_load_unit<MPU>(ring[d], wp + (size_t)(base + d + GV_DEPTH) * GV_WARPS * GV_UNIT_V4, meta_ptr(R_l, ku_l), zoff);
-                    ku_l += GV_WARPS;
-                    while (ku_l >= p.UPR) { ku_l -= p.UPR; ++R_l; }
+            } else {
+#pragma unroll
+            for (int h = 0; h < MPU; ++h) {
+                // CH independent accumulator chains: a dependent HMMA only issues after the previous one retires
+                constexpr int CH = MMAS_PER_GROUP >= 4 ? 4 : MMAS_PER_GROUP;
+                float accs[CH][NT][4];
+#pragma unroll
+                for (int jj = 0; jj < MMAS_PER_GROUP; ++jj) {
+                    const int jm = h * MMAS_PER_GROUP + jj;
+                    const uint32_t w = wj[jm], v = w >> 8;
+                    const uint32_t a0 = gv_lop3_and_or(w, 0x000F000Fu, 0x64006400u);  // row g  : 1024 + q, k-slots 4t, 4t+1
+                    const uint32_t a1 = gv_lop3_and_or(w, 0x00F000F0u, 0x54005400u);  // row g+8:   64 + q, k-slots 4t, 4t+1
+                    const uint32_t a2 = gv_lop3_and_or(v, 0x000F000Fu, 0x64006400u);  // row g  : k-slots 4t+2, 4t+3
+                    const uint32_t a3 = gv_lop3_and_or(v, 0x00F000F0u, 0x54005400u);  // row g+8: k-slots 4t+2, 4t+3
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt) {
+                        const uint2 xf = xb[nt][(size_t)(32 * ku_c + 4 * jm) * MR];
+                        if (jj < CH) gv_mma_f16<true>(accs[jj % CH][nt], a0, a1, a2, a3, xf.x, xf.y);
+                        else gv_mma_f16<false>(accs[jj % CH][nt], a0, a1, a2, a3, xf.x, xf.y);
+                    }
                 }
-                // advance the compute cursor; leaving a row block publishes its partial sums
-                const int R_prev = R_c;
-                ku_c += GV_WARPS;
-                while (ku_c >= p.UPR) { ku_c -= p.UPR; ++R_c; }
-                if (R_c != R_prev || base + d + 1 == n_w) flush(R_prev);
+                float acc[NT][4];
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        float v = accs[0][nt][i];
+#pragma unroll
+                        for (int c = 1; c < CH; ++c) v += accs[c][nt][i];
+                        acc[nt][i] = v;
+                    }
+                const float slo = __uint_as_float(s2[h] << 16), shi = __uint_as_float(s2[h] & 0xFFFF0000u);
+                // exact floats 1024 + z (rows g) and 64 + z (rows g+8)
+                const float zlo = __uint_as_float(0x44800000u + ((zb[h] & 0x0Fu) << 13));
+                const float zhi = __uint_as_float(0x42800000u + ((zb[h] & 0xF0u) << 13));
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    const float4 X = *reinterpret_cast<const float4 *>(
+                        gtab + ((size_t)(ku_c * MPU + h) * PAIRS + (PAIRS == 1 ? 0 : nt * 4 + t)) * 4);
+                    const float sl0 = slo * X.z, sl1 = slo * X.w, sh0 = shi * X.z, sh1 = shi * X.w;
+                    yacc[nt][0] = fmaf(sl0, fmaf(-zlo, X.x, acc[nt][0]), yacc[nt][0]);
+                    yacc[nt][1] = fmaf(sl1, fmaf(-zlo, X.y, acc[nt][1]), yacc[nt][1]);
+                    yacc[nt][2] = fmaf(sh0, fmaf(-zhi, X.x, acc[nt][2]), yacc[nt][2]);
+                    yacc[nt][3] = fmaf(sh1, fmaf(-zhi, X.y, acc[nt][3]), yacc[nt][3]);
+                }
+            }
             }
         }
+        // this warp is done with ring slot s; the 16th arrival refills it (generic reads -> async-proxy write)
+        if (j + S < n_stages) {
+            __syncwarp();
+            if (lane == 0) {
+                __threadfence_block();
+                const uint32_t old = atomicAdd(&consumed[s], 1u);
+                if ((old & (GV_WARPS - 1)) == GV_WARPS - 1) {
+                    __threadfence_block();
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    issue_stage(j + S);
+                }
+            }
+        }
+        u += GV_STAGE_UNITS;
+        ku_c += GV_STAGE_UNITS;
+        while (ku_c >= p.UPR) { ku_c -= p.UPR; ++R_c; }
+        if (++s == S) { s = 0; phase ^= 1u; }
     }
+    if (R_acc >= 0) flush(R_acc);
     __syncthreads();
     stamp(3);
 
     // ---- combine the warps of this CTA (fixed order), write complete row blocks, publish boundary ones ----
     const int R_last = n_cta > 0 ? (b - 1) / p.UPR : R_first - 1;
     const int items = (R_last - R_first + 1) * p.P * 8;
-    const bool first_partial = n_cta > 0 && (a != R_first * p.UPR || b < (R_first + 1) * p.UPR);
-    const bool last_partial = n_cta > 0 && R_last != R_first && b != (R_last + 1) * p.UPR;
+    const bool first_partial = rec0.z >= 0, last_partial = rec1.x >= 0;
     auto store_y = [&](int R, int pp, int gg, float4 v) {
         const int n0 = R * 16 + gg;
         const int tok = 2 * pp;
@@ -326,7 +482,7 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 8 ? 3 : 2) gemv_stream_kerne
             v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
         }
         const int R = R_first + slot;
-        const bool is_first = slot == 0 && first_partial, is_last = R == R_last && last_partial;
+        const bool is_first = slot == 0 && first_partial, is_last = slot != 0 && R == R_last && last_partial;
         if (is_first || is_last)
             __stcg(p.scratch + (((size_t)cta * 2 + (is_first ? 0 : 1)) * p.P + pp) * 8 + gg, v);
         else
@@ -336,19 +492,17 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 8 ? 3 : 2) gemv_stream_kerne
     if (!first_partial && !last_partial) { stamp(5); return; }
 
     // ---- row blocks shared with neighbouring CTAs: the last arriver sums the contributors in CTA order ----
-    __threadfence();
+    // release: every thread's scratch stores, then the CTA barrier, then one acq_rel ticket per shared row block
+    asm volatile("fence.acq_rel.gpu;" ::: "memory");
     __syncthreads();
-    auto cta_of_unit = [&](int u) -> int {
-        const int big = p.r * (p.q + 1);
-        return u < big ? u / (p.q + 1) : p.r + (u - big) / p.q;   // q > 0 whenever a unit lies beyond the big ranges
-    };
     if (tid < 2) {
         const bool mine = tid == 0 ? first_partial : last_partial;
         int last = 0;
         if (mine) {
             const int R = tid == 0 ? R_first : R_last;
-            const int n_contrib = cta_of_unit((R + 1) * p.UPR - 1) - cta_of_unit(R * p.UPR) + 1;
-            const int prev = atomicAdd(&p.tickets[R], 1);
+            const int n_contrib = tid == 0 ? rec0.w - rec0.z + 1 : rec1.y - rec1.x + 1;
+            int prev;
+            asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], 1;" : "=r"(prev) : "l"(p.tickets + R) : "memory");
             last = prev == n_contrib - 1;
             if (last) p.tickets[R] = 0;   // self-reset for the next launch
         }
@@ -358,14 +512,14 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 8 ? 3 : 2) gemv_stream_kerne
 #pragma unroll 1
     for (int which = 0; which < 2; ++which) {
         if (!flags[which]) continue;
-        __threadfence();
+        asm volatile("fence.acq_rel.gpu;" ::: "memory");
         const int R = which == 0 ? R_first : R_last;
-        const int i_lo = cta_of_unit(R * p.UPR), i_hi = cta_of_unit((R + 1) * p.UPR - 1);
+        const int i_lo = which == 0 ? rec0.z : rec1.x, i_hi = which == 0 ? rec0.w : rec1.y;
         for (int it = tid; it < p.P * 8; it += GV_THREADS) {
             const int gg = it & 7, pp = it >> 3;
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
             for (int i = i_lo; i <= i_hi; ++i) {
-                const int a_i = i * p.q + min(i, p.r);
+                const int a_i = __ldg(p.tab + 2 * i).x;
                 const int wh = (a_i / p.UPR == R) ? 0 : 1;   // contributor i holds R as its first or its last row block
                 const float4 o = __ldcg(p.scratch + (((size_t)i * 2 + wh) * p.P + pp) * 8 + gg);
                 v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
@@ -390,51 +544,92 @@ int gemv_debug_read(unsigned long long *out, int64_t words, unsigned long long *
     return 0;
 }
 
-struct GemvPlan {
-    bool ok;
-    int grid, q, r, n_slots, P, MR;
-    int off_xsum, off_tok, off_part, smem_bytes;
-};
-
 static int gv_env_int(const char *name, int dflt) {
     const char *v = getenv(name);
     return v && *v ? atoi(v) : dflt;
 }
 
-static GemvPlan gemv_plan(const Linear &L, int64_t M, int sm_count) {
+// The work partition of one handle: contiguous unit ranges, one per CTA, and for every range end that cuts
+// a row block the CTAs that share it.  Built once per handle (create), lives in device memory.
+int gemv_build_table(Linear &L, int sm_count) {
+    const int64_t UPR = L.d.K / GV_UNIT_K, UT = L.d.NR * UPR;
+    L.gv_grid = 0;
+    if (UT >= (int64_t)1 << 30) return 0;   // the register-ring kernel takes it
+    int grid = (int)std::min<int64_t>(UT, (int64_t)sm_count * gv_env_int("W4A16_GEMV_CTAS_PER_SM", 1));
+    const int64_t q = UT / grid, r = UT % grid;
+    std::vector<int> start(grid + 1);
+    const int align = gv_env_int("W4A16_GEMV_ALIGN", 1);   // 1: ranges of whole row blocks (no shared row blocks, coarser balance)
+    for (int i = 0; i <= grid; ++i)
+        start[i] = align && L.d.NR >= grid ? (int)((i * L.d.NR / grid) * UPR) : (int)(i * q + std::min<int64_t>(i, r));
+    std::vector<int> rec((size_t)grid * 8, -1);
+    int max_slots = 1;
+    auto contributors = [&](int64_t R, int &lo, int &hi) {
+        const int64_t u0 = R * UPR, u1 = (R + 1) * UPR - 1;
+        lo = (int)(std::upper_bound(start.begin(), start.end(), (int)u0) - start.begin()) - 1;
+        hi = (int)(std::upper_bound(start.begin(), start.end(), (int)u1) - start.begin()) - 1;
+    };
+    for (int i = 0; i < grid; ++i) {
+        const int a = start[i], b = start[i + 1];
+        const int64_t Rf = a / UPR, Rl = (b - 1) / UPR;
+        int *rc = &rec[(size_t)i * 8];
+        rc[0] = a; rc[1] = b;
+        max_slots = std::max<int>(max_slots, (int)(Rl - Rf + 1));
+        if (a != Rf * UPR || b < (Rf + 1) * UPR) contributors(Rf, rc[2], rc[3]);
+        if (Rl != Rf && b != (Rl + 1) * UPR) contributors(Rl, rc[4], rc[5]);
+    }
+    cudaFree(L.gv_tab); L.gv_tab = nullptr;
+    W4_CUDA_OK(cudaMalloc(&L.gv_tab, rec.size() * sizeof(int)));
+    W4_CUDA_OK(cudaMemcpy(L.gv_tab, rec.data(), rec.size() * sizeof(int), cudaMemcpyHostToDevice));
+    L.gv_grid = grid;
+    L.gv_max_slots = max_slots;
+    return 0;
+}
+
+struct GemvPlan {
+    bool ok;
+    int P, MR, S, stage_m_bytes;
+    int off_xs, off_gtab, off_flags, off_part, off_wring, off_mring, smem_bytes;
+};
+
+static GemvPlan gemv_plan(const Linear &L, int64_t M) {
     GemvPlan pl{};
     pl.ok = false;
-    if (M < 1 || M > 16) return pl;
+    if (M < 1 || M > 16 || L.gv_grid <= 0 || !L.gv_tab) return pl;
     const int gs = L.d.gs;
     if (gs != 32 && gs != 64 && gs != 128 && gs != L.d.K) return pl;
-    const int64_t UPR = L.d.K / GV_UNIT_K, UT64 = L.d.NR * UPR;
-    if (UT64 >= (int64_t)1 << 30) return pl;
-    const int UT = (int)UT64;
+    const int64_t UPR = L.d.K / GV_UNIT_K;
+    const bool per_channel = gs == L.d.K && gs != 32 && gs != 64 && gs != 128;
     const int mpu = gs == 32 ? 4 : gs == 64 ? 2 : 1;
     pl.MR = M <= 1 ? 1 : M <= 2 ? 2 : M <= 4 ? 4 : M <= 8 ? 8 : 16;
     pl.P = (int)((M + 1) / 2);
-    int grid = gv_env_int("W4A16_GEMV_CTAS_PER_SM", 2) * sm_count;
-    if (grid > UT) grid = UT;
-    pl.grid = grid;
-    pl.q = UT / grid; pl.r = UT % grid;
-    const int range = pl.q + (pl.r ? 1 : 0);
-    pl.n_slots = (int)((range + UPR - 1) / UPR) + 1;
     const int pairs = pl.MR < 2 ? 1 : pl.MR / 2;
-    int64_t off = (int64_t)pl.MR * L.d.K * 2;                       // xs
-    pl.off_xsum = (int)off; off += (int64_t)UPR * mpu * pairs * 16; // group table {X0, X1, 2^e0, 2^e1}
-    off = (off + 15) & ~(int64_t)15;
-    pl.off_tok = (int)off; off += 16;                               // flags[2] (+pad)
-    off = (off + 15) & ~(int64_t)15;
-    pl.off_part = (int)off; off += (int64_t)pl.n_slots * GV_WARPS * pl.P * 8 * 16;
-    if (off > 200 * 1024) return pl;                                 // x does not fit: the register-ring kernel takes it
+    int64_t off = 8 * GV_MAX_STAGES + 4 * GV_MAX_STAGES;            // mbarriers + arrival counters
+    off = (off + 127) & ~(int64_t)127;
+    pl.off_xs = (int)off; off += (int64_t)pl.MR * L.d.K * 2;         // fp16 activations, fragment order
+    pl.off_gtab = (int)off;                                          // group table: {X0, X1, 2^e0, 2^e1} per token pair,
+    off += pl.MR <= 2 ? (int64_t)UPR * mpu * pl.MR * 32 : (int64_t)UPR * mpu * pairs * 16;   // or 8 ints per token (integer path)
+    pl.off_flags = (int)off; off += 16;
+    pl.off_part = (int)off; off += (int64_t)L.gv_max_slots * GV_WARPS * pl.P * 8 * 16;
+    off = (off + 127) & ~(int64_t)127;
+    pl.stage_m_bytes = per_channel ? 0 : GV_STAGE_UNITS * mpu * META_BYTES;
+    const int64_t stage = GV_STAGE_W_BYTES + pl.stage_m_bytes;
+    const int64_t fixed = off;
+    int64_t budget = pl.MR <= 8 ? GV_SMEM_HALF_SM : GV_SMEM_FULL_SM;
+    int64_t S = (budget - fixed) / stage;
+    if (S < 3) { budget = GV_SMEM_FULL_SM; S = (budget - fixed) / stage; }
+    if (S < 2) return pl;                                            // x does not fit: the register-ring kernel takes it
+    S = std::min<int64_t>(S, std::min<int64_t>(GV_MAX_STAGES, gv_env_int("W4A16_GEMV_STAGES", GV_MAX_STAGES)));
+    pl.S = (int)S;
+    pl.off_wring = (int)off; off += S * GV_STAGE_W_BYTES;
+    pl.off_mring = (int)off; off += S * pl.stage_m_bytes;
     pl.smem_bytes = (int)off;
     pl.ok = true;
     return pl;
 }
 
-bool gemv_stream_usable(const Linear &L, int64_t M, int sm_count) {
+bool gemv_stream_usable(const Linear &L, int64_t M) {
     if (gv_env_int("W4A16_NO_GEMV_STREAM", 0)) return false;
-    return gemv_plan(L, M, sm_count).ok;
+    return gemv_plan(L, M).ok;
 }
 
 int64_t gemv_scratch_floats(int sm_count) {
@@ -443,15 +638,15 @@ int64_t gemv_scratch_floats(int sm_count) {
 }
 
 template <int MR, int MPU>
-static int gv_launch_t(const GemvParams &p, const GemvPlan &pl, cudaStream_t stream, bool pdl) {
-    static int max_smem_set = 0;   // grows monotonically; racing threads only repeat the call
-    if (pl.smem_bytes > 48 * 1024 && pl.smem_bytes > max_smem_set) {
+static int gv_launch_t(const GemvParams &p, const GemvPlan &pl, int grid, cudaStream_t stream, bool pdl) {
+    static bool attr_set = false;   // racing threads only repeat the call
+    if (!attr_set) {
         W4_CUDA_OK(cudaFuncSetAttribute(gemv_stream_kernel<MR, MPU>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        200 * 1024));
-        max_smem_set = 200 * 1024;
+                                        GV_SMEM_FULL_SM));
+        attr_set = true;
     }
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3((unsigned)pl.grid);
+    cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(GV_THREADS);
     cfg.dynamicSmemBytes = (size_t)pl.smem_bytes;
     cfg.stream = stream;
@@ -467,39 +662,39 @@ static int gv_launch_t(const GemvParams &p, const GemvPlan &pl, cudaStream_t str
 
 int launch_gemv_stream(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
                        cudaStream_t stream) {
-    const GemvPlan pl = gemv_plan(L, M, L.scratch->sm_count);
+    const GemvPlan pl = gemv_plan(L, M);
     if (!pl.ok) return fail("launch_gemv_stream: shape not supported by the stream kernel");
     const int gs = L.d.gs;
     const int mpu = gs == 32 ? 4 : gs == 64 ? 2 : 1;
     GemvParams p;
-    p.qw = reinterpret_cast<const uint4 *>(L.qw);
+    p.qw = reinterpret_cast<const uint8_t *>(L.qw);
     p.meta = L.meta;
     p.bias = add_bias && L.has_bias ? L.bias : nullptr;
     p.x = x; p.y = y;
     p.scratch = reinterpret_cast<float4 *>(L.splitk_scratch);
     p.tickets = L.tickets;
+    p.tab = reinterpret_cast<const int4 *>(L.gv_tab);
     p.M = (int)M; p.K = (int)L.d.K; p.N = (int)L.d.N;
     p.UPR = (int)(L.d.K / GV_UNIT_K);
-    p.UT = (int)(L.d.NR * p.UPR);
-    p.q = pl.q; p.r = pl.r;
-    const bool per_channel = gs == L.d.K && gs != 32 && gs != 64 && gs != 128;
-    p.meta_stride = per_channel ? 0 : mpu * META_BYTES;
-    p.G = (int)L.d.G;
-    p.P = pl.P; p.n_slots = pl.n_slots;
-    p.off_xsum = pl.off_xsum; p.off_tok = pl.off_tok; p.off_part = pl.off_part;
+    p.meta_stride = pl.stage_m_bytes ? mpu * META_BYTES : 0;
+    p.P = pl.P;
+    p.n_stages_ring = pl.S;
+    p.stage_m_bytes = pl.stage_m_bytes;
+    p.off_xs = pl.off_xs; p.off_gtab = pl.off_gtab; p.off_flags = pl.off_flags; p.off_part = pl.off_part;
+    p.off_wring = pl.off_wring; p.off_mring = pl.off_mring;
     p.dbg = nullptr;
     if (gv_env_int("W4A16_GV_DEBUG", 0)) {   // timing experiments: launch i stamps ring slot i % 4
         if (!g_gv_dbg) W4_CUDA_OK(cudaMalloc(&g_gv_dbg, GV_DBG_SLOTS * GV_DBG_WORDS * sizeof(unsigned long long)));
         p.dbg = g_gv_dbg + (size_t)(g_gv_dbg_launch++ % GV_DBG_SLOTS) * GV_DBG_WORDS;
     }
-    if ((int64_t)pl.grid * 2 * pl.P * 8 * 4 > L.splitk_floats)
+    if ((int64_t)L.gv_grid * 2 * pl.P * 8 * 4 > L.splitk_floats)
         return fail("launch_gemv_stream: boundary scratch too small for this configuration");
     const bool pdl = gv_env_int("W4A16_NO_PDL", 0) == 0;
-#define W4_GV(MR_)                                                               \
-    do {                                                                         \
-        if (mpu == 1) return gv_launch_t<MR_, 1>(p, pl, stream, pdl);            \
-        if (mpu == 2) return gv_launch_t<MR_, 2>(p, pl, stream, pdl);            \
-        return gv_launch_t<MR_, 4>(p, pl, stream, pdl);                          \
+#define W4_GV(MR_)                                                                     \
+    do {                                                                               \
+        if (mpu == 1) return gv_launch_t<MR_, 1>(p, pl, L.gv_grid, stream, pdl);       \
+        if (mpu == 2) return gv_launch_t<MR_, 2>(p, pl, L.gv_grid, stream, pdl);       \
+        return gv_launch_t<MR_, 4>(p, pl, L.gv_grid, stream, pdl);                     \
     } while (0)
     switch (pl.MR) {
         case 1: W4_GV(1);

@@ -60,6 +60,8 @@ struct Linear {
     __nv_bfloat16 *stage_x = nullptr, *stage_y = nullptr;  // forward_host staging
     int64_t stage_cap = 0;
     float *rowpar_f32 = nullptr;  // unused for now (fp32 all-reduce staging)
+    int *gv_tab = nullptr;        // decode stream kernel: per-CTA unit range + row-block sharing table (device)
+    int gv_grid = 0, gv_max_slots = 0;
     DeviceScratch *scratch = nullptr;
 };
 
@@ -91,7 +93,8 @@ int launch_decode(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int
 const char *decode_kernel_name(const Linear &L, int64_t M);
 int decode_scratch_need(const Linear &L, int sm_count, int64_t *scratch_floats, int64_t *tickets);
 // decode, M <= 16: the single-wave stream kernel (w4a16_gemv.cu); the register-ring kernel above is its fallback
-bool gemv_stream_usable(const Linear &L, int64_t M, int sm_count);
+bool gemv_stream_usable(const Linear &L, int64_t M);
+int gemv_build_table(Linear &L, int sm_count);
 int64_t gemv_scratch_floats(int sm_count);
 int launch_gemv_stream(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
                        cudaStream_t stream);
