@@ -84,7 +84,7 @@ static void free_linear(Linear *L) {
     DeviceGuard g(L->device);
     cudaFree(L->qw); cudaFree(L->meta); cudaFree(L->bias); cudaFree(L->perm); cudaFree(L->tickets);
     cudaFree(L->splitk_scratch); cudaFree(L->x_gather); cudaFree(L->stage_x); cudaFree(L->stage_y);
-    cudaFree(L->rowpar_f32); cudaFree(L->gv_tab);
+    cudaFree(L->rowpar_f32); cudaFree(L->gv_tab); cudaFree(L->gu_rb_start);
     delete L;
 }
 
@@ -242,7 +242,7 @@ int w4a16_create_shard(w4a16_handle_t *out, int64_t in_features, int64_t out_fea
     if (cudaMemset(L->tickets, 0, (size_t)nt * 4) != cudaSuccess) return bail("cudaMemset(tickets) failed");
     if (sf > 0) { W4_ALLOC(L->splitk_scratch, (size_t)sf * 4); L->splitk_floats = sf; }
 #undef W4_ALLOC
-    if (gemv_build_table(*L, ds->sm_count)) { free_linear(L); return 1; }
+    if (gemv_build_table(*L, ds->sm_count) || gemv_umma_build_table(*L, ds->sm_count)) { free_linear(L); return 1; }
     *out = reinterpret_cast<w4a16_handle_t>(L);
     return 0;
 }

@@ -60,6 +60,7 @@ struct GemvParams {
     int UPR;                    // units per row block = K / 128
     int meta_stride;            // bytes of meta per unit (MPU*48), 0 for per-channel scales
     int P;                      // ceil(M/2): fragment column pairs that hold real tokens
+    int fast;                   // whole row blocks per CTA, full ring stages, grouped meta: the streamlined loop applies
     int n_stages_ring;          // stages in the shared-memory ring
     int stage_m_bytes;          // meta bytes per ring stage (16-byte multiple)
     // shared-memory carve-up (bytes from the start of dynamic smem)
@@ -323,9 +324,90 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 8 ? 2 : 1) gemv_stream_kerne
         }
     };
 
+    bool fast_done = false;
+    if constexpr (DP) {
+        if (p.fast) {
+            // Fast path (whole row blocks per CTA, K % 2048 == 0 so every ring stage is full, grouped meta):
+            // the same arithmetic as the general loop below with every address a running 32-bit shared-memory
+            // offset and every branch warp-uniform.
+            const uint32_t my_w = wring_s + (uint32_t)(warp * GV_UNIT_BYTES + lane * 16);
+            const uint32_t my_m = mring_s + (uint32_t)(warp * (MPU * META_BYTES) + 4 * g);
+            const uint32_t my_z = mring_s + (uint32_t)(warp * (MPU * META_BYTES) + META_ZERO_OFF + g);
+            const uint32_t xk0 = gv_smem_u32(xs) + (uint32_t)((32 * warp + t) * MR * 8);
+            const uint32_t gk0 = gv_smem_u32(gtab) + (uint32_t)(warp * MPU * MR * 32 + 4 * t);
+            uint32_t xk = xk0, gk = gk0, woff = 0, moff = 0;
+            int sk = 0, R = R_first, s = 0;
+            uint32_t phase = 0;
+            for (int j = 0; j < n_stages; ++j) {
+                gv_mbar_wait(bar0 + 8 * s, phase);
+                uint32_t wj[8], s2[MPU], zb[MPU];
+                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(wj[0]), "=r"(wj[1]), "=r"(wj[2]), "=r"(wj[3]) : "r"(my_w + woff));
+                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4+512];" : "=r"(wj[4]), "=r"(wj[5]), "=r"(wj[6]), "=r"(wj[7]) : "r"(my_w + woff));
+#pragma unroll
+                for (int h = 0; h < MPU; ++h) {
+                    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(s2[h]) : "r"(my_m + moff + h * META_BYTES));
+                    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(zb[h]) : "r"(my_z + moff + h * META_BYTES));
+                }
+#pragma unroll
+                for (int h = 0; h < MPU; ++h) {
+                    int acc[MR][4];
+#pragma unroll
+                    for (int m = 0; m < MR; ++m)
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) acc[m][i] = 0;
+#pragma unroll
+                    for (int jj = 0; jj < MMAS_PER_GROUP; ++jj) {
+                        const int jm = h * MMAS_PER_GROUP + jj;
+                        const uint32_t w = wj[jm];
+                        const uint32_t ev = w & 0x0F0F0F0Fu;          // row g  , k-slots (4t, 4t+2, 4t+1, 4t+3)
+                        const uint32_t od = (w >> 4) & 0x0F0F0F0Fu;   // row g+8, same k-slots
+#pragma unroll
+                        for (int m = 0; m < MR; ++m) {
+                            uint32_t xh, xl;
+                            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(xh), "=r"(xl) : "r"(xk + (uint32_t)((4 * jm * MR + m) * 8)));
+                            acc[m][0] = gv_dp4a_u8s8(ev, xh, acc[m][0]);
+                            acc[m][1] = gv_dp4a_u8s8(ev, xl, acc[m][1]);
+                            acc[m][2] = gv_dp4a_u8s8(od, xh, acc[m][2]);
+                            acc[m][3] = gv_dp4a_u8s8(od, xl, acc[m][3]);
+                        }
+                    }
+                    const float slo = __uint_as_float(s2[h] << 16), shi = __uint_as_float(s2[h] & 0xFFFF0000u);
+                    const int zlo = (int)(zb[h] & 0x0Fu), zhi = (int)(zb[h] >> 4);
+#pragma unroll
+                    for (int m = 0; m < MR; ++m) {
+                        int xsum; uint32_t e2b;
+                        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(xsum) : "r"(gk + (uint32_t)((h * MR + m) * 32)));
+                        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(e2b) : "r"(gk + (uint32_t)((h * MR + m) * 32 + 16) - 4u * (uint32_t)t));
+                        const float e2 = __uint_as_float(e2b);
+                        const int tg = acc[m][0] * 128 + acc[m][1] - zlo * xsum;     // exact: |.| < 2^24
+                        const int tg8 = acc[m][2] * 128 + acc[m][3] - zhi * xsum;
+                        yacc[0][m] = fmaf(slo * e2, (float)tg, yacc[0][m]);
+                        yacc[0][2 + m] = fmaf(shi * e2, (float)tg8, yacc[0][2 + m]);
+                    }
+                }
+                if (j + S < n_stages) {   // warp-uniform: the 16th arrival refills this ring slot
+                    __syncwarp();
+                    if (lane == 0) {
+                        __threadfence_block();
+                        const uint32_t old = atomicAdd(&consumed[s], 1u);
+                        if ((old & (GV_WARPS - 1)) == GV_WARPS - 1) {
+                            __threadfence_block();
+                            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                            issue_stage(j + S);
+                        }
+                    }
+                }
+                woff += GV_STAGE_W_BYTES; moff += (uint32_t)p.stage_m_bytes;
+                if (++s == S) { s = 0; phase ^= 1u; woff = 0; moff = 0; }
+                sk += GV_STAGE_UNITS; xk += GV_STAGE_UNITS * 32 * MR * 8; gk += GV_STAGE_UNITS * MPU * MR * 32;
+                if (sk == p.UPR) { flush(R); ++R; sk = 0; xk = xk0; gk = gk0; }
+            }
+            fast_done = true;
+        }
+    }
     int s = 0;
     uint32_t phase = 0;
-    for (int j = 0; j < n_stages; ++j) {
+    for (int j = 0; j < (fast_done ? 0 : n_stages); ++j) {
         gv_mbar_wait(bar0 + 8 * s, phase);
         if (u < b) {
             if (R_acc >= 0 && R_acc != R_c) flush(R_acc);
@@ -449,7 +531,7 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 8 ? 2 : 1) gemv_stream_kerne
         while (ku_c >= p.UPR) { ku_c -= p.UPR; ++R_c; }
         if (++s == S) { s = 0; phase ^= 1u; }
     }
-    if (R_acc >= 0) flush(R_acc);
+    if (!fast_done && R_acc >= 0) flush(R_acc);
     __syncthreads();
     stamp(3);
 
@@ -549,6 +631,13 @@ static int gv_env_int(const char *name, int dflt) {
     return v && *v ? atoi(v) : dflt;
 }
 
+// timing experiments (W4A16_GV_DEBUG=1): launch i stamps ring slot i % 4
+unsigned long long *gemv_debug_slot() {
+    if (!gv_env_int("W4A16_GV_DEBUG", 0)) return nullptr;
+    if (!g_gv_dbg && cudaMalloc(&g_gv_dbg, GV_DBG_SLOTS * GV_DBG_WORDS * sizeof(unsigned long long)) != cudaSuccess) return nullptr;
+    return g_gv_dbg + (size_t)(g_gv_dbg_launch++ % GV_DBG_SLOTS) * GV_DBG_WORDS;
+}
+
 // The work partition of one handle: contiguous unit ranges, one per CTA, and for every range end that cuts
 // a row block the CTAs that share it.  Built once per handle (create), lives in device memory.
 int gemv_build_table(Linear &L, int sm_count) {
@@ -582,6 +671,7 @@ int gemv_build_table(Linear &L, int sm_count) {
     W4_CUDA_OK(cudaMemcpy(L.gv_tab, rec.data(), rec.size() * sizeof(int), cudaMemcpyHostToDevice));
     L.gv_grid = grid;
     L.gv_max_slots = max_slots;
+    L.gv_aligned = align && L.d.NR >= grid;
     return 0;
 }
 
@@ -679,14 +769,12 @@ int launch_gemv_stream(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y
     p.meta_stride = pl.stage_m_bytes ? mpu * META_BYTES : 0;
     p.P = pl.P;
     p.n_stages_ring = pl.S;
+    p.fast = L.gv_aligned && (L.d.K % (GV_UNIT_K * GV_STAGE_UNITS) == 0) && pl.stage_m_bytes != 0 &&
+             gv_env_int("W4A16_GEMV_FAST", 1);
     p.stage_m_bytes = pl.stage_m_bytes;
     p.off_xs = pl.off_xs; p.off_gtab = pl.off_gtab; p.off_flags = pl.off_flags; p.off_part = pl.off_part;
     p.off_wring = pl.off_wring; p.off_mring = pl.off_mring;
-    p.dbg = nullptr;
-    if (gv_env_int("W4A16_GV_DEBUG", 0)) {   // timing experiments: launch i stamps ring slot i % 4
-        if (!g_gv_dbg) W4_CUDA_OK(cudaMalloc(&g_gv_dbg, GV_DBG_SLOTS * GV_DBG_WORDS * sizeof(unsigned long long)));
-        p.dbg = g_gv_dbg + (size_t)(g_gv_dbg_launch++ % GV_DBG_SLOTS) * GV_DBG_WORDS;
-    }
+    p.dbg = gemv_debug_slot();
     if ((int64_t)L.gv_grid * 2 * pl.P * 8 * 4 > L.splitk_floats)
         return fail("launch_gemv_stream: boundary scratch too small for this configuration");
     const bool pdl = gv_env_int("W4A16_NO_PDL", 0) == 0;

@@ -62,6 +62,9 @@ struct Linear {
     float *rowpar_f32 = nullptr;  // unused for now (fp32 all-reduce staging)
     int *gv_tab = nullptr;        // decode stream kernel: per-CTA unit range + row-block sharing table (device)
     int gv_grid = 0, gv_max_slots = 0;
+    bool gv_aligned = false;      // every CTA range is a whole number of row blocks
+    int *gu_rb_start = nullptr;   // tcgen05 decode kernel: first row block of every CTA (device)
+    int gu_grid = 0, gu_max_rb = 0;
     DeviceScratch *scratch = nullptr;
 };
 
@@ -98,6 +101,11 @@ int gemv_build_table(Linear &L, int sm_count);
 int64_t gemv_scratch_floats(int sm_count);
 int launch_gemv_stream(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
                        cudaStream_t stream);
+// decode, M <= 4: tcgen05 kernel (w4a16_gemv_umma.cu)
+bool gemv_umma_usable(const Linear &L, int64_t M);
+int gemv_umma_build_table(Linear &L, int sm_count);
+int launch_gemv_umma(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
+                     cudaStream_t stream);
 int gemv_debug_read(unsigned long long *out, int64_t words, unsigned long long *launches);
 // prefill (tcgen05): any M
 int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
