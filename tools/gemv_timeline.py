@@ -63,20 +63,31 @@ def main():
     a = np.frombuffer(buf, dtype=np.uint64).reshape(4, 1024, 8).astype(np.int64)
     last = int(n.value) - 1
     order = [(last - 2) % 4, (last - 1) % 4, last % 4]
-    live = a[order[0], :, 0] > 0
-    ncta = int(live.sum())
+    ncta = int((a[order[0], :256, 0] > 0).sum())
     t0 = a[order[0], :ncta, 0].min()
-    names = ["start", "dep-wait", "staged", "streamed", "combined", "end"]
+    names = ["start", "dep-wait", "staged", "streamed", "combined", "end", "stage0-in", "last-in"]
     print(f"shape {args.shape} K={K} N={N} M={args.m} kernel={lins[0].kernel_for(args.m)} ctas={ncta} launches={n.value}")
     for j, slot in enumerate(order):
         print(f"-- launch {j - 2:+d}")
         for i, nm in enumerate(names):
-            if i >= 6:
-                v = a[slot, :ncta, i].astype(float)
-                print(f"   {nm:9s} min {v.min():8.0f}  med {np.median(v):8.0f}  max {v.max():8.0f} cycles (warp 0)")
+            if a[slot, :ncta, i].max() == 0:
                 continue
             v = (a[slot, :ncta, i] - t0) / 1e3
             print(f"   {nm:9s} min {v.min():8.2f}  med {np.median(v):8.2f}  max {v.max():8.2f} us")
+        if j == 2:
+            trace(a, slot)
+
+
+def trace(a, slot):
+    tr = a[slot].reshape(-1)[2048:2048 + 16 * 8].reshape(16, 8)
+    if tr.max() == 0:
+        return
+    t0 = tr[0, 0]
+    print("   warp-0 checkpoints of CTA 7 (cycles): top, waited, loads-in, refill-issued, imma-done, end")
+    for j in range(16):
+        if tr[j, 0] == 0:
+            break
+        print("    unit", j, " ".join(f"{int(v - t0):7d}" for v in tr[j, :6]))
 
 
 if __name__ == "__main__":

@@ -1,0 +1,384 @@
+// w4a16_gemv_imma.cu -- decode GEMV for M <= 4 tokens on the int8 tensor-core path (IMMA.16832.U8.S8).
+//
+// Replaces awq_gemv_int4_kt_bf16 / kt_mloop_m4 (awq_gemv.cu:377-665) and gptq_gemm_int4_bf16_tiled
+// (gptq_dequant.cu:243-318) as dispatched by marlin_gemm_pooled / marlin_gemm (marlin_cuda.rs:843-953,
+// 1655-1753).  One CTA of 16 warps per SM owns a contiguous range of whole row blocks of the W4T stream; warp w
+// takes units a+w, a+w+16, ... and pulls them through a PRIVATE shared-memory ring with cp.async (LDGSTS, 16 B per
+// lane: every lane copies exactly the two 16-byte pieces it later reads), the first D units issued BEFORE
+// griddepcontrol.wait.  No mbarriers and no CTA barrier inside the stream.  (Measured, tools/ubench/pdlstream.cu:
+// cp.async.bulk executes one request at a time per SM -- 16 KB requests cap the chip at ~5.6 TB/s, 8 KB at 3.4 --
+// while the per-warp LDGSTS ring sustains 6.4-6.8 TB/s in a PDL chain of 14-51 MB launches.)
+//
+// Arithmetic (the reference's GEMV form, awq_gemv.cu:597-664, regrouped so the zero point leaves the loop):
+//     y[m,n] = sum_g s[g,n] * 2^e[g,m] * ( sum_{k in g} q[k,n] * xt[m,k]  -  z[g,n] * X[g,m] )
+//   xt[m,k] = round(x[m,k] * 2^-e[g,m]) in [-16383, 16383]  (per group and token the power of two puts max|x| in
+//             [2^13, 2^14): exact for every element within 2^6 of the group's maximum, |error| <= 2^-14 of that
+//             maximum below), carried as two signed-byte planes xt = 128*hi + lo;
+//   X[g,m]  = sum_{k in g} xt[m,k]  (int32, once per CTA while the first weights are in flight).
+// One W4T word holds 8 nibbles = rows {g, g+8} x 4 k:  `w & 0x0F0F0F0F` IS the u8x4 A-fragment register of row g,
+// `w & 0xF0F0F0F0` the one of row g+8 scaled by 16 (undone exactly in the scale): 2 LOP3 per 8 weights, no
+// shift.  Two words make the four A registers of mma.m16n8k32.u8.s8; the 8 B columns are (hi, lo) planes of up to
+// 4 tokens; accumulation is exact int32.  Per 1 KB unit (2048 weights) a warp issues 2 LDS.128 + 16 LOP3 +
+// 4 LDS.64 + 4 IMMA + ~20 instructions of group epilogue: about half of the dp4a loop it replaces.
+#include <algorithm>
+
+#include "w4a16_gemv_common.cuh"
+
+namespace w4 {
+
+__device__ __forceinline__ void gi_imma(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                        uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// MR = token slots (1, 2 or 4; M <= MR).  MPU = groups per 128-k unit (1, 2, 4 for group size 128, 64, 32).
+// DI = loop iterations in flight in the warp's ring; one iteration = 2 units (two independent IMMA chains per warp
+// hide the tensor-pipe and shared-memory latencies that 4 warps per scheduler cannot).
+template <int MR, int MPU, int DI>
+__global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvParams p) {
+    constexpr int COLS = 2 * MR;               // B columns holding data: (hi, lo) plane of each token slot
+    constexpr int IPG = 4 / MPU;               // IMMAs per group
+    constexpr int SUB_K = GV_UNIT_K / MPU;     // k per group inside a unit
+    constexpr int GL = SUB_K / 8;              // staging lanes (8-element pieces) per group
+    constexpr int SLOT = GV_UNIT_BYTES + ((MPU * META_BYTES + 15) & ~15);   // one unit: weights + its meta blocks
+    extern __shared__ __align__(128) uint8_t gv_smem[];
+    uint8_t *xs = gv_smem + p.off_xs;                                   // [K/32][4 t][COLS][8 B]: B fragments
+    int2 *gtab = reinterpret_cast<int2 *>(gv_smem + p.off_gtab);        // [K/SUB_K][MR] {X, bits of 2^e}
+    float2 *part = reinterpret_cast<float2 *>(gv_smem + p.off_part);    // [slots][GV_WARPS][8 g][MR] {row g, row g+8}
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, t = lane & 3;
+    const int cta = blockIdx.x;
+    const int4 rec0 = __ldg(p.tab + 2 * cta);
+    const int a = rec0.x, b = rec0.y;          // unit range: whole row blocks
+    const int R_first = a / p.UPR, n_slots = (b - a) / p.UPR;
+    const int n_w = (b - a - warp + GV_WARPS - 1) / GV_WARPS;          // units of this warp: a + warp + 16 j
+    const int n_it = (n_w + 1) >> 1;
+    const uint32_t ring = gv_smem_u32(gv_smem + p.off_wring) + (uint32_t)(warp * DI * 2 * SLOT);
+
+    // iteration `it` of this warp = its units 2 it and 2 it + 1 -> ring slot it % DI.  One commit group per call,
+    // empty past the end (uniform group counting).
+    const uint8_t *src_w = p.qw + ((size_t)(a + warp) * GV_UNIT_BYTES + lane * 16);
+    const uint8_t *src_m = p.meta + ((size_t)(a + warp) * (MPU * META_BYTES) + lane * 16);
+    auto issue_pair = [&](int it, int slot) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int j = 2 * it + h;
+            if (j < n_w) {
+                const uint32_t dst = ring + (uint32_t)((slot * 2 + h) * SLOT + lane * 16);
+                const uint8_t *sw = src_w + (size_t)j * (GV_WARPS * GV_UNIT_BYTES);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(sw) : "memory");
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 512), "l"(sw + 512) : "memory");
+                if (lane < MPU * 3)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + GV_UNIT_BYTES),
+                                 "l"(src_m + (size_t)j * (GV_WARPS * MPU * META_BYTES)) : "memory");
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+
+    // ---- prefetch: weights and meta are immutable, independent of the previous kernel ----
+#pragma unroll
+    for (int it = 0; it < DI; ++it) issue_pair(it, it);
+    for (int i = tid; i < n_slots * GV_WARPS * 8 * MR; i += GV_THREADS) part[i] = make_float2(0.f, 0.f);
+    auto stamp = [&](int i) {
+        if (p.dbg && tid == 0) {
+            unsigned long long tt;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt));
+            p.dbg[(size_t)cta * 8 + i] = tt;
+        }
+    };
+    stamp(0);
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (p.fast) {   // one thread waits for the previous kernel; the others park at a hardware barrier (no issue slots)
+        if (tid == 0) asm volatile("griddepcontrol.wait;" ::: "memory");
+        __syncthreads();
+    } else {
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+    }
+    stamp(1);
+
+    // ---- stage the activations: per-(group, token) power-of-two scale, two signed-byte planes in B-fragment
+    //      order, integer group sums.  x is [M][K] contiguous, so 8-element piece i sits at x + 8 i. ----
+    {
+        const int ppr = p.K >> 3, total = p.M * ppr;
+        const uint4 *x16 = reinterpret_cast<const uint4 *>(p.x);
+        constexpr int BATCH = 4;               // loads in flight per thread
+        for (int base = 0; base < total; base += BATCH * GV_THREADS) {   // warp-uniform trip count (shuffles)
+            uint4 v[BATCH];
+#pragma unroll
+            for (int r = 0; r < BATCH; ++r) {
+                const int i = base + r * GV_THREADS + tid;
+                v[r] = i < total ? __ldg(x16 + i) : make_uint4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (int r = 0; r < BATCH; ++r) {
+                const int i = base + r * GV_THREADS + tid;
+                if (base + r * GV_THREADS >= total) break;               // warp-uniform
+                const uint32_t w4[4] = {v[r].x, v[r].y, v[r].z, v[r].w};
+                uint32_t mx = 0;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) mx = max(mx, max(w4[q] & 0x7FFFu, (w4[q] >> 16) & 0x7FFFu));
+#pragma unroll
+                for (int o = GL / 2; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+                int E = (int)(mx >> 7);                                  // biased exponent of the group's max |x|
+                E = min(max(E, 14), 254);
+                const float scale = __int_as_float((267 - E) << 23);     // max|x| lands in [2^13, 2^14)
+                int xi[8];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    xi[2 * q] = __float2int_rn(__uint_as_float(w4[q] << 16) * scale);
+                    xi[2 * q + 1] = __float2int_rn(__uint_as_float(w4[q] & 0xFFFF0000u) * scale);
+                }
+                int sum = ((xi[0] + xi[1]) + (xi[2] + xi[3])) + ((xi[4] + xi[5]) + (xi[6] + xi[7]));
+#pragma unroll
+                for (int o = GL / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                if (i < total) {
+                    const int m = i / ppr, c = i - m * ppr;              // token, piece within the row
+                    // k = 8c: unit ku = c >> 4, word j = (c & 15) >> 1, IMMA j >> 1 (half j & 1), quads t = 2(c&1), +1
+                    const int j = (c & 15) >> 1;
+                    uint8_t *dst = xs + ((size_t)(((c >> 4) * 4 + (j >> 1)) * 4 + 2 * (c & 1)) * COLS + 2 * m) * 8 +
+                                   (j & 1) * 4;
+                    // byte order (k0, k2, k1, k3): the k order of the bytes of `w & 0x0F0F0F0F`
+                    *reinterpret_cast<uint32_t *>(dst) = gv_pack4(xi[0] >> 7, xi[2] >> 7, xi[1] >> 7, xi[3] >> 7);
+                    *reinterpret_cast<uint32_t *>(dst + 8) = gv_pack4(xi[0] & 127, xi[2] & 127, xi[1] & 127, xi[3] & 127);
+                    *reinterpret_cast<uint32_t *>(dst + COLS * 8) = gv_pack4(xi[4] >> 7, xi[6] >> 7, xi[5] >> 7, xi[7] >> 7);
+                    *reinterpret_cast<uint32_t *>(dst + COLS * 8 + 8) =
+                        gv_pack4(xi[4] & 127, xi[6] & 127, xi[5] & 127, xi[7] & 127);
+                    if ((c & (GL - 1)) == 0) gtab[(size_t)(c / GL) * MR + m] = make_int2(sum, (E - 13) << 23);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    stamp(2);
+
+    // ---- main loop: iteration `it` handles this warp's units A = 2 it and B = 2 it + 1 (stream units a + warp + 32 it, + 16) ----
+    float y0 = 0.f, y1 = 0.f;                  // rows g / g+8 of the current row block, token slot t
+    int R_A = (a + warp) / p.UPR, ku_A = (a + warp) - R_A * p.UPR;
+    int R_acc = -1;
+    const uint32_t xs_l = gv_smem_u32(xs) + (uint32_t)((t * COLS + (g & (COLS - 1))) * 8);
+    const uint32_t gt_l = gv_smem_u32(gtab) + (uint32_t)((t & (MR - 1)) * 8);
+    auto flush = [&](int R) {
+        if (t < MR) part[(((size_t)(R - R_first) * GV_WARPS + warp) * 8 + g) * MR + t] = make_float2(y0, y1);
+        y0 = 0.f; y1 = 0.f;
+    };
+    // integer part of one unit: 4 IMMAs into MPU group accumulators
+    auto unit_mma = [&](const uint32_t (&wj)[8], int ku, int (&acc)[MPU][4]) {
+        const uint32_t xk = xs_l + (uint32_t)ku * (4 * 4 * COLS * 8);
+#pragma unroll
+        for (int h = 0; h < MPU; ++h) {
+            int c1[4] = {0, 0, 0, 0};          // second accumulator chain when a group spans several IMMAs
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[h][q] = 0;
+#pragma unroll
+            for (int ii = 0; ii < IPG; ++ii) {
+                const int i = h * IPG + ii;
+                uint32_t b0, b1;
+                asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(b0), "=r"(b1) : "r"(xk + (uint32_t)(i * 4 * COLS * 8)));
+                const uint32_t wa = wj[2 * i], wb = wj[2 * i + 1];
+                if (ii & 1) gi_imma(c1, wa & 0x0F0F0F0Fu, wa & 0xF0F0F0F0u, wb & 0x0F0F0F0Fu, wb & 0xF0F0F0F0u, b0, b1);
+                else gi_imma(acc[h], wa & 0x0F0F0F0Fu, wa & 0xF0F0F0F0u, wb & 0x0F0F0F0Fu, wb & 0xF0F0F0F0u, b0, b1);
+            }
+            if (IPG > 1) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) acc[h][q] += c1[q];
+            }
+        }
+    };
+    // float part: acc = {row g hi, row g lo, row g+8 hi, row g+8 lo} of token slot t; rows g+8 carry a factor 16
+    auto unit_fin = [&](const int (&acc)[MPU][4], const uint32_t (&s2)[MPU], const uint32_t (&zb)[MPU], int ku) {
+#pragma unroll
+        for (int h = 0; h < MPU; ++h) {
+            int X, e2b;
+            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(X), "=r"(e2b) : "r"(gt_l + (uint32_t)((ku * MPU + h) * MR * 8)));
+            const float e2 = __int_as_float(e2b);
+            const int tg = acc[h][0] * 128 + acc[h][1] - (int)(zb[h] & 0x0Fu) * X;
+            const int tg8 = acc[h][2] * 128 + acc[h][3] - (int)(zb[h] & 0xF0u) * X;
+            const float slo = __uint_as_float(s2[h] << 16) * e2;
+            const float shi = __uint_as_float(s2[h] & 0xFFFF0000u) * (e2 * 0.0625f);
+            y0 = fmaf(slo, (float)tg, y0);
+            y1 = fmaf(shi, (float)tg8, y1);
+        }
+    };
+    int slot = 0;
+    for (int it = 0; it < n_it; ++it) {
+        asm volatile("cp.async.wait_group %0;" ::"n"(DI - 1) : "memory");   // this lane's copies of the pair have landed ...
+        __syncwarp();                           // ... and so have the other lanes' (meta is read across lanes)
+        if (it == 0 && warp == 0) stamp(6);
+        const bool has_B = 2 * it + 1 < n_w;    // warp-uniform
+        int R_B = R_A, ku_B = ku_A;
+        if (has_B) { ku_B += GV_WARPS; while (ku_B >= p.UPR) { ku_B -= p.UPR; ++R_B; } }
+        const uint32_t sA = ring + (uint32_t)(slot * 2 * SLOT), sB = sA + SLOT;
+        uint32_t wA[8], wB[8], s2A[MPU], zbA[MPU], s2B[MPU], zbB[MPU];
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(wA[0]), "=r"(wA[1]), "=r"(wA[2]), "=r"(wA[3]) : "r"(sA + lane * 16));
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4+512];" : "=r"(wA[4]), "=r"(wA[5]), "=r"(wA[6]), "=r"(wA[7]) : "r"(sA + lane * 16));
+#pragma unroll
+        for (int h = 0; h < MPU; ++h) {
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(s2A[h]) : "r"(sA + GV_UNIT_BYTES + h * META_BYTES + 4 * g));
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(zbA[h]) : "r"(sA + GV_UNIT_BYTES + h * META_BYTES + META_ZERO_OFF + g));
+        }
+        if (has_B) {
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(wB[0]), "=r"(wB[1]), "=r"(wB[2]), "=r"(wB[3]) : "r"(sB + lane * 16));
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4+512];" : "=r"(wB[4]), "=r"(wB[5]), "=r"(wB[6]), "=r"(wB[7]) : "r"(sB + lane * 16));
+#pragma unroll
+            for (int h = 0; h < MPU; ++h) {
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(s2B[h]) : "r"(sB + GV_UNIT_BYTES + h * META_BYTES + 4 * g));
+                asm volatile("ld.shared.u8 %0, [%1];" : "=r"(zbB[h]) : "r"(sB + GV_UNIT_BYTES + h * META_BYTES + META_ZERO_OFF + g));
+            }
+        } else {                                // odd tail: a unit of zero weights with zero scales contributes nothing
+#pragma unroll
+            for (int q = 0; q < 8; ++q) wB[q] = 0;
+#pragma unroll
+            for (int h = 0; h < MPU; ++h) { s2B[h] = 0; zbB[h] = 0; }
+        }
+        __syncwarp();                           // every lane has read the slot: refill it with iteration it + DI
+        issue_pair(it + DI, slot);
+        int accA[MPU][4], accB[MPU][4];
+        unit_mma(wA, ku_A, accA);
+        unit_mma(wB, ku_B, accB);
+        if (R_acc != R_A) { if (R_acc >= 0) flush(R_acc); R_acc = R_A; }
+        unit_fin(accA, s2A, zbA, ku_A);
+        if (R_acc != R_B) { flush(R_acc); R_acc = R_B; }
+        unit_fin(accB, s2B, zbB, ku_B);
+        ku_A += 2 * GV_WARPS;
+        while (ku_A >= p.UPR) { ku_A -= p.UPR; ++R_A; }
+        if (++slot == DI) slot = 0;
+    }
+    if (warp == 0) stamp(7);
+    if (R_acc >= 0) flush(R_acc);
+    __syncthreads();
+    stamp(3);
+
+    // ---- combine the 16 warps (fixed tree: deterministic) and write y ----
+    // thread (item, q): item = (slot, row g, token), q = quarter of the warps; quarters are adjacent lanes
+    for (int it = tid; it < n_slots * 32 * MR; it += GV_THREADS) {      // multiples of 32: whole warps
+        const int q = it & 3, e = (it >> 2) & (8 * MR - 1), slot = it / (32 * MR);
+        const float2 *src = part + ((size_t)slot * GV_WARPS + 4 * q) * 8 * MR + e;
+        float2 v = src[0];
+#pragma unroll
+        for (int w = 1; w < 4; ++w) { const float2 o = src[w * 8 * MR]; v.x += o.x; v.y += o.y; }
+        v.x += __shfl_xor_sync(0xffffffffu, v.x, 1); v.y += __shfl_xor_sync(0xffffffffu, v.y, 1);
+        v.x += __shfl_xor_sync(0xffffffffu, v.x, 2); v.y += __shfl_xor_sync(0xffffffffu, v.y, 2);
+        const int tok = e % MR, n0 = (R_first + slot) * 16 + e / MR;
+        if (q == 0 && tok < p.M) {
+            const float b0 = p.bias ? __bfloat162float(p.bias[n0]) : 0.f;
+            const float b1 = p.bias ? __bfloat162float(p.bias[n0 + 8]) : 0.f;
+            p.y[(size_t)tok * p.N + n0] = __float2bfloat16_rn(v.x + b0);
+            p.y[(size_t)tok * p.N + n0 + 8] = __float2bfloat16_rn(v.y + b1);
+        }
+    }
+    stamp(4);
+    stamp(5);
+}
+
+// ---- host side ---------------------------------------------------------------------------
+struct ImmaPlan {
+    bool ok;
+    int MR, mpu, S, stage_m_bytes;
+    int off_xs, off_gtab, off_part, off_wring, off_mring, smem_bytes;
+};
+
+static ImmaPlan imma_plan(const Linear &L, int64_t M) {
+    ImmaPlan pl{};
+    pl.ok = false;
+    if (M < 1 || M > 4 || L.gv_grid <= 0 || !L.gv_tab || !L.gv_aligned) return pl;
+    const int gs = L.d.gs;
+    if (gs != 32 && gs != 64 && gs != 128) return pl;               // per-channel scales: the f16 stream kernel
+    pl.mpu = 128 / gs;
+    pl.MR = M <= 1 ? 1 : M <= 2 ? 2 : 4;
+    int64_t off = 0;
+    pl.off_xs = (int)off; off += L.d.K * 2 * pl.MR;                  // two byte planes per token slot
+    pl.off_gtab = (int)off; off += (L.d.K / gs) * pl.MR * 8;
+    off = (off + 15) & ~(int64_t)15;
+    pl.off_part = (int)off; off += (int64_t)L.gv_max_slots * GV_WARPS * 8 * pl.MR * 8;
+    off = (off + 127) & ~(int64_t)127;
+    const int64_t slot = GV_UNIT_BYTES + ((pl.mpu * META_BYTES + 15) & ~15);
+    const int64_t depth = GV_WARPS * 2 * slot;                       // one more iteration (2 units) in flight per warp
+    // two CTAs per SM (this linear + the next one's prefetch): 228 KB minus 1 KB reserved per CTA, halved
+    int64_t D = (GV_SMEM_2CTA - off) / depth;
+    if (D < 2) D = (GV_SMEM_FULL_SM - off) / depth;                  // large K x M: one CTA per SM
+    if (D < 2) return pl;
+    D = std::min<int64_t>(D, std::min<int64_t>(3, gv_env_int("W4A16_GEMV_STAGES", 3)));
+    if (D < 2) D = 2;
+    pl.S = (int)D;
+    pl.stage_m_bytes = 0;
+    pl.off_wring = (int)off; off += D * depth;
+    pl.off_mring = pl.off_wring;
+    pl.smem_bytes = (int)off;
+    pl.ok = true;
+    return pl;
+}
+
+bool gemv_imma_usable(const Linear &L, int64_t M) {
+    if (gv_env_int("W4A16_NO_GEMV_IMMA", 0)) return false;
+    return imma_plan(L, M).ok;
+}
+
+template <int MR, int MPU, int DI>
+static int gi_launch_t(const GemvParams &p, const ImmaPlan &pl, int grid, cudaStream_t stream, bool pdl) {
+    static bool attr_set = false;   // racing threads only repeat the call
+    if (!attr_set) {
+        W4_CUDA_OK(cudaFuncSetAttribute(gemv_imma_kernel<MR, MPU, DI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        GV_SMEM_FULL_SM));
+        attr_set = true;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(GV_THREADS);
+    cfg.dynamicSmemBytes = (size_t)pl.smem_bytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    W4_CUDA_OK(cudaLaunchKernelEx(&cfg, gemv_imma_kernel<MR, MPU, DI>, p));
+    count_launch();
+    return 0;
+}
+
+int launch_gemv_imma(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
+                     cudaStream_t stream) {
+    const ImmaPlan pl = imma_plan(L, M);
+    if (!pl.ok) return fail("launch_gemv_imma: shape not supported by the IMMA stream kernel");
+    GemvParams p{};
+    p.qw = reinterpret_cast<const uint8_t *>(L.qw);
+    p.meta = L.meta;
+    p.bias = add_bias && L.has_bias ? L.bias : nullptr;
+    p.x = x; p.y = y;
+    p.tab = reinterpret_cast<const int4 *>(L.gv_tab);
+    p.M = (int)M; p.K = (int)L.d.K; p.N = (int)L.d.N;
+    p.UPR = (int)(L.d.K / GV_UNIT_K);
+    p.meta_stride = pl.mpu * META_BYTES;
+    p.n_stages_ring = pl.S;
+    p.stage_m_bytes = pl.stage_m_bytes;
+    p.off_xs = pl.off_xs; p.off_gtab = pl.off_gtab; p.off_part = pl.off_part;
+    p.off_wring = pl.off_wring; p.off_mring = pl.off_mring;
+    p.dbg = gemv_debug_slot();
+    p.fast = gv_env_int("W4A16_GV_WAIT1", 1);
+    const bool pdl = gv_env_int("W4A16_NO_PDL", 0) == 0;
+#define W4_GI2(MR_, MPU_)                                                              \
+    do {                                                                               \
+        if (pl.S == 3) return gi_launch_t<MR_, MPU_, 3>(p, pl, L.gv_grid, stream, pdl); \
+        return gi_launch_t<MR_, MPU_, 2>(p, pl, L.gv_grid, stream, pdl);               \
+    } while (0)
+#define W4_GI(MR_)                                                                     \
+    do {                                                                               \
+        if (pl.mpu == 1) W4_GI2(MR_, 1);                                               \
+        if (pl.mpu == 2) W4_GI2(MR_, 2);                                               \
+        W4_GI2(MR_, 4);                                                                \
+    } while (0)
+    switch (pl.MR) {
+        case 1: W4_GI(1);
+        case 2: W4_GI(2);
+        default: W4_GI(4);
+    }
+#undef W4_GI2
+#undef W4_GI
+}
+
+}  // namespace w4

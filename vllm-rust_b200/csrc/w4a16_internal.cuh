@@ -101,6 +101,10 @@ int gemv_build_table(Linear &L, int sm_count);
 int64_t gemv_scratch_floats(int sm_count);
 int launch_gemv_stream(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
                        cudaStream_t stream);
+// decode, M <= 4: int8 tensor-core stream kernel (w4a16_gemv_imma.cu)
+bool gemv_imma_usable(const Linear &L, int64_t M);
+int launch_gemv_imma(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
+                     cudaStream_t stream);
 // decode, M <= 4: tcgen05 kernel (w4a16_gemv_umma.cu)
 bool gemv_umma_usable(const Linear &L, int64_t M);
 int gemv_umma_build_table(Linear &L, int sm_count);
