@@ -37,7 +37,9 @@ __device__ __forceinline__ void gi_imma(int (&c)[4], uint32_t a0, uint32_t a1, u
 // MR = token slots (1, 2 or 4; M <= MR).  MPU = groups per 128-k unit (1, 2, 4 for group size 128, 64, 32).
 // DI = loop iterations in flight in the warp's ring; one iteration = 2 units (two independent IMMA chains per warp
 // hide the tensor-pipe and shared-memory latencies that 4 warps per scheduler cannot).
-template <int MR, int MPU, int DI>
+// REG = every row block is a whole number of 32-unit strides (K % 4096 == 0): the two units of an iteration share
+// their row block and every warp visits every row block, so the loop carries no row-block bookkeeping.
+template <int MR, int MPU, int DI, bool REG>
 __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvParams p) {
     constexpr int COLS = 2 * MR;               // B columns holding data: (hi, lo) plane of each token slot
     constexpr int IPG = 4 / MPU;               // IMMAs per group
@@ -59,31 +61,40 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
     const int n_it = (n_w + 1) >> 1;
     const uint32_t ring = gv_smem_u32(gv_smem + p.off_wring) + (uint32_t)(warp * DI * 2 * SLOT);
 
-    // iteration `it` of this warp = its units 2 it and 2 it + 1 -> ring slot it % DI.  One commit group per call,
-    // empty past the end (uniform group counting).
-    const uint8_t *src_w = p.qw + ((size_t)(a + warp) * GV_UNIT_BYTES + lane * 16);
-    const uint8_t *src_m = p.meta + ((size_t)(a + warp) * (MPU * META_BYTES) + lane * 16);
-    auto issue_pair = [&](int it, int slot) {
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const int j = 2 * it + h;
-            if (j < n_w) {
-                const uint32_t dst = ring + (uint32_t)((slot * 2 + h) * SLOT + lane * 16);
-                const uint8_t *sw = src_w + (size_t)j * (GV_WARPS * GV_UNIT_BYTES);
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(sw) : "memory");
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 512), "l"(sw + 512) : "memory");
-                if (lane < MPU * 3)
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + GV_UNIT_BYTES),
-                                 "l"(src_m + (size_t)j * (GV_WARPS * MPU * META_BYTES)) : "memory");
-            }
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
+    // Iterations are issued in order: iteration i = this warp's units 2 i and 2 i + 1 -> ring slot i % DI.  One commit
+    // group per call, empty past the end (uniform group counting); running pointers, predicated copies, no branches.
+    const uint8_t *nxt_w = p.qw + ((size_t)(a + warp) * GV_UNIT_BYTES + lane * 16);
+    const uint8_t *nxt_m = p.meta + ((size_t)(a + warp) * (MPU * META_BYTES) + lane * 16);
+    int nxt_j = 0;                             // first unit of the next iteration to issue
+    auto issue_next = [&](int slot) {
+        const uint32_t dst = ring + (uint32_t)(slot * 2 * SLOT + lane * 16);
+        const uint32_t okA = nxt_j < n_w, okB = nxt_j + 1 < n_w, okM = lane < MPU * 3;
+        asm volatile(
+            "{\n\t.reg .pred pa, pb, pma, pmb;\n\t"
+            "setp.ne.u32 pa, %4, 0;\n\t"
+            "setp.ne.u32 pb, %5, 0;\n\t"
+            "setp.ne.u32 pma, %6, 0;\n\t"
+            "and.pred pmb, pma, pb;\n\t"
+            "and.pred pma, pma, pa;\n\t"
+            "@pa cp.async.cg.shared.global [%0], [%2], 16;\n\t"
+            "@pa cp.async.cg.shared.global [%0+512], [%2+512], 16;\n\t"
+            "@pb cp.async.cg.shared.global [%1], [%2+16384], 16;\n\t"
+            "@pb cp.async.cg.shared.global [%1+512], [%2+16896], 16;\n\t"
+            "@pma cp.async.cg.shared.global [%0+1024], [%3], 16;\n\t"
+            "@pmb cp.async.cg.shared.global [%1+1024], [%3+%7], 16;\n\t"
+            "cp.async.commit_group;\n\t}"
+            ::"r"(dst), "r"(dst + SLOT), "l"(nxt_w), "l"(nxt_m), "r"(okA), "r"(okB), "r"(okM),
+              "n"(GV_WARPS * MPU * META_BYTES) : "memory");
+        nxt_w += 2 * GV_WARPS * GV_UNIT_BYTES;
+        nxt_m += 2 * GV_WARPS * MPU * META_BYTES;
+        nxt_j += 2;
     };
 
     // ---- prefetch: weights and meta are immutable, independent of the previous kernel ----
 #pragma unroll
-    for (int it = 0; it < DI; ++it) issue_pair(it, it);
-    for (int i = tid; i < n_slots * GV_WARPS * 8 * MR; i += GV_THREADS) part[i] = make_float2(0.f, 0.f);
+    for (int it = 0; it < DI; ++it) issue_next(it);
+    if (!REG)   // a warp may never visit some row block of the range (REG: every warp writes every slot)
+        for (int i = tid; i < n_slots * GV_WARPS * 8 * MR; i += GV_THREADS) part[i] = make_float2(0.f, 0.f);
     auto stamp = [&](int i) {
         if (p.dbg && tid == 0) {
             unsigned long long tt;
@@ -157,18 +168,13 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
     stamp(2);
 
     // ---- main loop: iteration `it` handles this warp's units A = 2 it and B = 2 it + 1 (stream units a + warp + 32 it, + 16) ----
+    constexpr uint32_t XU = 4 * 4 * COLS * 8;  // bytes of B fragments per unit
+    constexpr uint32_t GU = MPU * MR * 8;      // bytes of group table per unit
     float y0 = 0.f, y1 = 0.f;                  // rows g / g+8 of the current row block, token slot t
-    int R_A = (a + warp) / p.UPR, ku_A = (a + warp) - R_A * p.UPR;
-    int R_acc = -1;
     const uint32_t xs_l = gv_smem_u32(xs) + (uint32_t)((t * COLS + (g & (COLS - 1))) * 8);
     const uint32_t gt_l = gv_smem_u32(gtab) + (uint32_t)((t & (MR - 1)) * 8);
-    auto flush = [&](int R) {
-        if (t < MR) part[(((size_t)(R - R_first) * GV_WARPS + warp) * 8 + g) * MR + t] = make_float2(y0, y1);
-        y0 = 0.f; y1 = 0.f;
-    };
-    // integer part of one unit: 4 IMMAs into MPU group accumulators
-    auto unit_mma = [&](const uint32_t (&wj)[8], int ku, int (&acc)[MPU][4]) {
-        const uint32_t xk = xs_l + (uint32_t)ku * (4 * 4 * COLS * 8);
+    // integer part of one unit: 4 IMMAs into MPU group accumulators (xk = this lane's B fragments of the unit)
+    auto unit_mma = [&](const uint32_t (&wj)[8], uint32_t xk, int (&acc)[MPU][4]) {
 #pragma unroll
         for (int h = 0; h < MPU; ++h) {
             int c1[4] = {0, 0, 0, 0};          // second accumulator chain when a group spans several IMMAs
@@ -190,11 +196,11 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
         }
     };
     // float part: acc = {row g hi, row g lo, row g+8 hi, row g+8 lo} of token slot t; rows g+8 carry a factor 16
-    auto unit_fin = [&](const int (&acc)[MPU][4], const uint32_t (&s2)[MPU], const uint32_t (&zb)[MPU], int ku) {
+    auto unit_fin = [&](const int (&acc)[MPU][4], const uint32_t (&s2)[MPU], const uint32_t (&zb)[MPU], uint32_t gk) {
 #pragma unroll
         for (int h = 0; h < MPU; ++h) {
             int X, e2b;
-            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(X), "=r"(e2b) : "r"(gt_l + (uint32_t)((ku * MPU + h) * MR * 8)));
+            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(X), "=r"(e2b) : "r"(gk + (uint32_t)(h * MR * 8)));
             const float e2 = __int_as_float(e2b);
             const int tg = acc[h][0] * 128 + acc[h][1] - (int)(zb[h] & 0x0Fu) * X;
             const int tg8 = acc[h][2] * 128 + acc[h][3] - (int)(zb[h] & 0xF0u) * X;
@@ -204,6 +210,51 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
             y1 = fmaf(shi, (float)tg8, y1);
         }
     };
+    auto load_unit = [&](uint32_t su, uint32_t (&w)[8], uint32_t (&s2)[MPU], uint32_t (&zb)[MPU]) {
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "r"(su + lane * 16));
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4+512];" : "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "r"(su + lane * 16));
+#pragma unroll
+        for (int h = 0; h < MPU; ++h) {
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(s2[h]) : "r"(su + GV_UNIT_BYTES + h * META_BYTES + 4 * g));
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(zb[h]) : "r"(su + GV_UNIT_BYTES + h * META_BYTES + META_ZERO_OFF + g));
+        }
+    };
+    if constexpr (REG) {
+        // every iteration: units (R, ku = warp + 32 m) and (R, ku + 16); UPR / 32 iterations per row block
+        const int ipr = p.UPR >> 5;
+        uint32_t sA = ring;
+        int slot = 0;
+        bool first = true;
+        for (int s = 0; s < n_slots; ++s) {
+            uint32_t xk = xs_l + (uint32_t)warp * XU, gk = gt_l + (uint32_t)warp * GU;
+            for (int m = 0; m < ipr; ++m) {
+                asm volatile("cp.async.wait_group %0;" ::"n"(DI - 1) : "memory");
+                __syncwarp();
+                if (first) { if (warp == 0) stamp(6); first = false; }
+                uint32_t wA[8], wB[8], s2A[MPU], zbA[MPU], s2B[MPU], zbB[MPU];
+                load_unit(sA, wA, s2A, zbA);
+                load_unit(sA + SLOT, wB, s2B, zbB);
+                __syncwarp();                   // every lane has read the slot: refill it with iteration it + DI
+                issue_next(slot);
+                int accA[MPU][4], accB[MPU][4];
+                unit_mma(wA, xk, accA);
+                unit_mma(wB, xk + GV_WARPS * XU, accB);
+                unit_fin(accA, s2A, zbA, gk);
+                unit_fin(accB, s2B, zbB, gk + GV_WARPS * GU);
+                xk += 2 * GV_WARPS * XU; gk += 2 * GV_WARPS * GU;
+                sA += 2 * SLOT;
+                if (++slot == DI) { slot = 0; sA = ring; }
+            }
+            if (t < MR) part[(((size_t)s * GV_WARPS + warp) * 8 + g) * MR + t] = make_float2(y0, y1);
+            y0 = 0.f; y1 = 0.f;
+        }
+    } else {
+    int R_A = (a + warp) / p.UPR, ku_A = (a + warp) - R_A * p.UPR;
+    int R_acc = -1;
+    auto flush = [&](int R) {
+        if (t < MR) part[(((size_t)(R - R_first) * GV_WARPS + warp) * 8 + g) * MR + t] = make_float2(y0, y1);
+        y0 = 0.f; y1 = 0.f;
+    };
     int slot = 0;
     for (int it = 0; it < n_it; ++it) {
         asm volatile("cp.async.wait_group %0;" ::"n"(DI - 1) : "memory");   // this lane's copies of the pair have landed ...
@@ -212,23 +263,11 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
         const bool has_B = 2 * it + 1 < n_w;    // warp-uniform
         int R_B = R_A, ku_B = ku_A;
         if (has_B) { ku_B += GV_WARPS; while (ku_B >= p.UPR) { ku_B -= p.UPR; ++R_B; } }
-        const uint32_t sA = ring + (uint32_t)(slot * 2 * SLOT), sB = sA + SLOT;
+        const uint32_t sA = ring + (uint32_t)(slot * 2 * SLOT);
         uint32_t wA[8], wB[8], s2A[MPU], zbA[MPU], s2B[MPU], zbB[MPU];
-        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(wA[0]), "=r"(wA[1]), "=r"(wA[2]), "=r"(wA[3]) : "r"(sA + lane * 16));
-        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4+512];" : "=r"(wA[4]), "=r"(wA[5]), "=r"(wA[6]), "=r"(wA[7]) : "r"(sA + lane * 16));
-#pragma unroll
-        for (int h = 0; h < MPU; ++h) {
-            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(s2A[h]) : "r"(sA + GV_UNIT_BYTES + h * META_BYTES + 4 * g));
-            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(zbA[h]) : "r"(sA + GV_UNIT_BYTES + h * META_BYTES + META_ZERO_OFF + g));
-        }
+        load_unit(sA, wA, s2A, zbA);
         if (has_B) {
-            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(wB[0]), "=r"(wB[1]), "=r"(wB[2]), "=r"(wB[3]) : "r"(sB + lane * 16));
-            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4+512];" : "=r"(wB[4]), "=r"(wB[5]), "=r"(wB[6]), "=r"(wB[7]) : "r"(sB + lane * 16));
-#pragma unroll
-            for (int h = 0; h < MPU; ++h) {
-                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(s2B[h]) : "r"(sB + GV_UNIT_BYTES + h * META_BYTES + 4 * g));
-                asm volatile("ld.shared.u8 %0, [%1];" : "=r"(zbB[h]) : "r"(sB + GV_UNIT_BYTES + h * META_BYTES + META_ZERO_OFF + g));
-            }
+            load_unit(sA + SLOT, wB, s2B, zbB);
         } else {                                // odd tail: a unit of zero weights with zero scales contributes nothing
 #pragma unroll
             for (int q = 0; q < 8; ++q) wB[q] = 0;
@@ -236,20 +275,21 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
             for (int h = 0; h < MPU; ++h) { s2B[h] = 0; zbB[h] = 0; }
         }
         __syncwarp();                           // every lane has read the slot: refill it with iteration it + DI
-        issue_pair(it + DI, slot);
+        issue_next(slot);
         int accA[MPU][4], accB[MPU][4];
-        unit_mma(wA, ku_A, accA);
-        unit_mma(wB, ku_B, accB);
+        unit_mma(wA, xs_l + (uint32_t)ku_A * XU, accA);
+        unit_mma(wB, xs_l + (uint32_t)ku_B * XU, accB);
         if (R_acc != R_A) { if (R_acc >= 0) flush(R_acc); R_acc = R_A; }
-        unit_fin(accA, s2A, zbA, ku_A);
+        unit_fin(accA, s2A, zbA, gt_l + (uint32_t)ku_A * GU);
         if (R_acc != R_B) { flush(R_acc); R_acc = R_B; }
-        unit_fin(accB, s2B, zbB, ku_B);
+        unit_fin(accB, s2B, zbB, gt_l + (uint32_t)ku_B * GU);
         ku_A += 2 * GV_WARPS;
         while (ku_A >= p.UPR) { ku_A -= p.UPR; ++R_A; }
         if (++slot == DI) slot = 0;
     }
-    if (warp == 0) stamp(7);
     if (R_acc >= 0) flush(R_acc);
+    }
+    if (warp == 0) stamp(7);
     __syncthreads();
     stamp(3);
 
@@ -318,11 +358,11 @@ bool gemv_imma_usable(const Linear &L, int64_t M) {
     return imma_plan(L, M).ok;
 }
 
-template <int MR, int MPU, int DI>
+template <int MR, int MPU, int DI, bool REG>
 static int gi_launch_t(const GemvParams &p, const ImmaPlan &pl, int grid, cudaStream_t stream, bool pdl) {
     static bool attr_set = false;   // racing threads only repeat the call
     if (!attr_set) {
-        W4_CUDA_OK(cudaFuncSetAttribute(gemv_imma_kernel<MR, MPU, DI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        W4_CUDA_OK(cudaFuncSetAttribute(gemv_imma_kernel<MR, MPU, DI, REG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         GV_SMEM_FULL_SM));
         attr_set = true;
     }
@@ -336,7 +376,7 @@ static int gi_launch_t(const GemvParams &p, const ImmaPlan &pl, int grid, cudaSt
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    W4_CUDA_OK(cudaLaunchKernelEx(&cfg, gemv_imma_kernel<MR, MPU, DI>, p));
+    W4_CUDA_OK(cudaLaunchKernelEx(&cfg, gemv_imma_kernel<MR, MPU, DI, REG>, p));
     count_launch();
     return 0;
 }
@@ -361,10 +401,15 @@ int launch_gemv_imma(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, 
     p.dbg = gemv_debug_slot();
     p.fast = gv_env_int("W4A16_GV_WAIT1", 1);
     const bool pdl = gv_env_int("W4A16_NO_PDL", 0) == 0;
+    const bool reg = (L.d.K % (32 * GV_UNIT_K)) == 0 && gv_env_int("W4A16_GV_REG", 1);
 #define W4_GI2(MR_, MPU_)                                                              \
     do {                                                                               \
-        if (pl.S == 3) return gi_launch_t<MR_, MPU_, 3>(p, pl, L.gv_grid, stream, pdl); \
-        return gi_launch_t<MR_, MPU_, 2>(p, pl, L.gv_grid, stream, pdl);               \
+        if (reg) {                                                                     \
+            if (pl.S == 3) return gi_launch_t<MR_, MPU_, 3, true>(p, pl, L.gv_grid, stream, pdl);  \
+            return gi_launch_t<MR_, MPU_, 2, true>(p, pl, L.gv_grid, stream, pdl);     \
+        }                                                                              \
+        if (pl.S == 3) return gi_launch_t<MR_, MPU_, 3, false>(p, pl, L.gv_grid, stream, pdl); \
+        return gi_launch_t<MR_, MPU_, 2, false>(p, pl, L.gv_grid, stream, pdl);        \
     } while (0)
 #define W4_GI(MR_)                                                                     \
     do {                                                                               \
