@@ -2,12 +2,13 @@
 //
 // Replaces awq_gemv_int4_kt_bf16 / kt_mloop_m4 (awq_gemv.cu:377-665) and gptq_gemm_int4_bf16_tiled
 // (gptq_dequant.cu:243-318) as dispatched by marlin_gemm_pooled / marlin_gemm (marlin_cuda.rs:843-953,
-// 1655-1753).  One CTA of 16 warps per SM owns a contiguous range of whole row blocks of the W4T stream; warp w
-// takes units a+w, a+w+16, ... and pulls them through a PRIVATE shared-memory ring with cp.async (LDGSTS, 16 B per
-// lane: every lane copies exactly the two 16-byte pieces it later reads), the first D units issued BEFORE
-// griddepcontrol.wait.  No mbarriers and no CTA barrier inside the stream.  (Measured, tools/ubench/pdlstream.cu:
-// cp.async.bulk executes one request at a time per SM -- 16 KB requests cap the chip at ~5.6 TB/s, 8 KB at 3.4 --
-// while the per-warp LDGSTS ring sustains 6.4-6.8 TB/s in a PDL chain of 14-51 MB launches.)
+// 1655-1753).  One CTA of 16 warps per SM owns a contiguous range of whole row blocks of the W4T stream and pulls it
+// through a shared-memory ring of DI stages of 32 units (32 KB of weights + their meta blocks) with cp.async.bulk,
+// the first DI stages issued BEFORE griddepcontrol.wait; in a stage warp w owns units w and w + 16.
+// Measured (tools/ubench/pdlstream.cu, tmalat.cu): cp.async.bulk executes ONE request at a time per SM (~0.4 us
+// each), so 8 KB requests cap the chip at 3.4 TB/s, 16 KB at 5.6, 32 KB reach 6.2-6.5; a per-warp cp.async (LDGSTS)
+// ring sustains 6.4-6.8 TB/s but costs 8 LSU cycles per 512 B, which the co-resident CTA of the NEXT kernel spends
+// exactly while this one stages its activations.  Hence 32 KB bulk requests.
 //
 // Arithmetic (the reference's GEMV form, awq_gemv.cu:597-664, regrouped so the zero point leaves the loop):
 //     y[m,n] = sum_g s[g,n] * 2^e[g,m] * ( sum_{k in g} q[k,n] * xt[m,k]  -  z[g,n] * X[g,m] )
@@ -45,7 +46,6 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
     constexpr int IPG = 4 / MPU;               // IMMAs per group
     constexpr int SUB_K = GV_UNIT_K / MPU;     // k per group inside a unit
     constexpr int GL = SUB_K / 8;              // staging lanes (8-element pieces) per group
-    constexpr int SLOT = GV_UNIT_BYTES + ((MPU * META_BYTES + 15) & ~15);   // one unit: weights + its meta blocks
     extern __shared__ __align__(128) uint8_t gv_smem[];
     uint8_t *xs = gv_smem + p.off_xs;                                   // [K/32][4 t][COLS][8 B]: B fragments
     int2 *gtab = reinterpret_cast<int2 *>(gv_smem + p.off_gtab);        // [K/SUB_K][MR] {X, bits of 2^e}
@@ -57,18 +57,33 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
     const int4 rec0 = __ldg(p.tab + 2 * cta);
     const int a = rec0.x, b = rec0.y;          // unit range: whole row blocks
     const int R_first = a / p.UPR, n_slots = (b - a) / p.UPR;
-    const int n_w = (b - a - warp + GV_WARPS - 1) / GV_WARPS;          // units of this warp: a + warp + 16 j
-    const int n_it = (n_w + 1) >> 1;
-    const uint32_t ring = gv_smem_u32(gv_smem + p.off_wring) + (uint32_t)(warp * DI * 2 * SLOT);
+    const int n_st = (b - a + 2 * GV_WARPS - 1) / (2 * GV_WARPS);      // stages of 32 units
+    constexpr uint32_t STAGE_W = 2 * GV_WARPS * GV_UNIT_BYTES, STAGE_M = 2 * GV_WARPS * MPU * META_BYTES;
+    constexpr uint32_t STAGE = STAGE_W + STAGE_M;
+    const uint32_t ring = gv_smem_u32(gv_smem + p.off_wring);
+    const uint32_t bar_full = gv_smem_u32(gv_smem);                    // DI mbarriers at the start of smem
 
-    // Iterations are issued in order: iteration i = this warp's units 2 i and 2 i + 1 -> ring slot i % DI.  One commit
-    // group per call, empty past the end (uniform group counting); running pointers, predicated copies, no branches.
-    const uint8_t *nxt_w = p.qw + ((size_t)(a + warp) * GV_UNIT_BYTES + lane * 16);
-    const uint8_t *nxt_m = p.meta + ((size_t)(a + warp) * (MPU * META_BYTES) + lane * 16);
-    int nxt_j = 0;                             // first unit of the next iteration to issue
-    auto issue_next = [&](int slot) {
-        const uint32_t dst = ring + (uint32_t)(slot * 2 * SLOT + lane * 16);
-        const uint32_t okA = nxt_j < n_w, okB = nxt_j + 1 < n_w, okM = lane < MPU * 3;
+    // The first DI stages: one bulk copy of the weights + one of the meta blocks per stage, on full[stage] (no LSU
+    // issue slots: the CTA of the previous kernel on this SM is staging its activations right now).
+    auto issue_stage = [&](int j, int slot) {
+        const int u_lo = a + j * (2 * GV_WARPS);
+        const int cnt = min(2 * GV_WARPS, b - u_lo);
+        const uint32_t wb = (uint32_t)cnt * GV_UNIT_BYTES, mb = (uint32_t)cnt * (MPU * META_BYTES);
+        const uint32_t bar = bar_full + 8 * slot, dst = ring + (uint32_t)slot * STAGE;
+        gv_mbar_expect_tx(bar, wb + mb);
+        gv_bulk_g2s(dst, p.qw + (size_t)u_lo * GV_UNIT_BYTES, wb, bar);
+        gv_bulk_g2s(dst + STAGE_W, p.meta + (size_t)u_lo * (MPU * META_BYTES), mb, bar);
+    };
+    // Every later stage: each warp refills ITS OWN two units of the slot with cp.async (16 B per lane: a lane copies
+    // exactly the pieces it later reads; only this warp ever read the bytes it overwrites, so a __syncwarp orders the
+    // reuse).  One commit group per call, empty past the end; running pointers, predicated copies, no branches.
+    const uint32_t offW = (uint32_t)(warp * GV_UNIT_BYTES + lane * 16);
+    const uint32_t offM = STAGE_W + (uint32_t)(warp * MPU * META_BYTES);
+    const uint8_t *nxt_w = p.qw + ((size_t)(a + DI * 2 * GV_WARPS + warp) * GV_UNIT_BYTES + lane * 16);
+    const uint8_t *nxt_m = p.meta + ((size_t)(a + DI * 2 * GV_WARPS + warp) * (MPU * META_BYTES) + lane * 16);
+    int nxt_u = a + DI * 2 * GV_WARPS + warp;  // unit A of the next stage to refill
+    auto refill = [&](uint32_t sb) {
+        const uint32_t okA = nxt_u < b, okB = nxt_u + GV_WARPS < b, okM = lane < MPU * 3;
         asm volatile(
             "{\n\t.reg .pred pa, pb, pma, pmb;\n\t"
             "setp.ne.u32 pa, %4, 0;\n\t"
@@ -78,21 +93,27 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
             "and.pred pma, pma, pa;\n\t"
             "@pa cp.async.cg.shared.global [%0], [%2], 16;\n\t"
             "@pa cp.async.cg.shared.global [%0+512], [%2+512], 16;\n\t"
-            "@pb cp.async.cg.shared.global [%1], [%2+16384], 16;\n\t"
-            "@pb cp.async.cg.shared.global [%1+512], [%2+16896], 16;\n\t"
-            "@pma cp.async.cg.shared.global [%0+1024], [%3], 16;\n\t"
-            "@pmb cp.async.cg.shared.global [%1+1024], [%3+%7], 16;\n\t"
+            "@pb cp.async.cg.shared.global [%0+16384], [%2+16384], 16;\n\t"
+            "@pb cp.async.cg.shared.global [%0+16896], [%2+16896], 16;\n\t"
+            "@pma cp.async.cg.shared.global [%1], [%3], 16;\n\t"
+            "@pmb cp.async.cg.shared.global [%1+%7], [%3+%7], 16;\n\t"
             "cp.async.commit_group;\n\t}"
-            ::"r"(dst), "r"(dst + SLOT), "l"(nxt_w), "l"(nxt_m), "r"(okA), "r"(okB), "r"(okM),
+            ::"r"(sb + offW), "r"(sb + offM + lane * 16), "l"(nxt_w), "l"(nxt_m), "r"(okA), "r"(okB), "r"(okM),
               "n"(GV_WARPS * MPU * META_BYTES) : "memory");
         nxt_w += 2 * GV_WARPS * GV_UNIT_BYTES;
         nxt_m += 2 * GV_WARPS * MPU * META_BYTES;
-        nxt_j += 2;
+        nxt_u += 2 * GV_WARPS;
     };
 
     // ---- prefetch: weights and meta are immutable, independent of the previous kernel ----
+    if (tid == 0) {
 #pragma unroll
-    for (int it = 0; it < DI; ++it) issue_next(it);
+        for (int s = 0; s < DI; ++s) gv_mbar_init(bar_full + 8 * s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#pragma unroll
+        for (int s = 0; s < DI; ++s) if (s < n_st) issue_stage(s, s);
+    }
     if (!REG)   // a warp may never visit some row block of the range (REG: every warp writes every slot)
         for (int i = tid; i < n_slots * GV_WARPS * 8 * MR; i += GV_THREADS) part[i] = make_float2(0.f, 0.f);
     auto stamp = [&](int i) {
@@ -210,40 +231,47 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
             y1 = fmaf(shi, (float)tg8, y1);
         }
     };
-    auto load_unit = [&](uint32_t su, uint32_t (&w)[8], uint32_t (&s2)[MPU], uint32_t (&zb)[MPU]) {
-        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "r"(su + lane * 16));
-        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4+512];" : "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "r"(su + lane * 16));
+    auto load_unit = [&](uint32_t sw, uint32_t sm, uint32_t (&w)[8], uint32_t (&s2)[MPU], uint32_t (&zb)[MPU]) {
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "r"(sw));
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4+512];" : "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "r"(sw));
 #pragma unroll
         for (int h = 0; h < MPU; ++h) {
-            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(s2[h]) : "r"(su + GV_UNIT_BYTES + h * META_BYTES + 4 * g));
-            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(zb[h]) : "r"(su + GV_UNIT_BYTES + h * META_BYTES + META_ZERO_OFF + g));
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(s2[h]) : "r"(sm + h * META_BYTES + 4 * g));
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(zb[h]) : "r"(sm + h * META_BYTES + META_ZERO_OFF + g));
+        }
+    };
+    // stage `it` is complete in its slot: the first DI came by bulk copy (mbarrier), the rest by this warp's cp.async
+    auto wait_stage = [&](int it) {
+        if (it < DI) {
+            gv_mbar_wait(bar_full + 8 * it, 0);
+        } else {
+            asm volatile("cp.async.wait_group %0;" ::"n"(DI - 1) : "memory");
+            __syncwarp();                       // meta is read across lanes
         }
     };
     if constexpr (REG) {
         // every iteration: units (R, ku = warp + 32 m) and (R, ku + 16); UPR / 32 iterations per row block
         const int ipr = p.UPR >> 5;
-        uint32_t sA = ring;
-        int slot = 0;
-        bool first = true;
+        uint32_t sb = ring;                    // base of the current ring slot
+        int slot = 0, it = 0;
         for (int s = 0; s < n_slots; ++s) {
             uint32_t xk = xs_l + (uint32_t)warp * XU, gk = gt_l + (uint32_t)warp * GU;
-            for (int m = 0; m < ipr; ++m) {
-                asm volatile("cp.async.wait_group %0;" ::"n"(DI - 1) : "memory");
-                __syncwarp();
-                if (first) { if (warp == 0) stamp(6); first = false; }
+            for (int m = 0; m < ipr; ++m, ++it) {
+                wait_stage(it);
+                if (it == 0 && warp == 0) stamp(6);
                 uint32_t wA[8], wB[8], s2A[MPU], zbA[MPU], s2B[MPU], zbB[MPU];
-                load_unit(sA, wA, s2A, zbA);
-                load_unit(sA + SLOT, wB, s2B, zbB);
-                __syncwarp();                   // every lane has read the slot: refill it with iteration it + DI
-                issue_next(slot);
+                load_unit(sb + offW, sb + offM, wA, s2A, zbA);
+                load_unit(sb + offW + GV_WARPS * GV_UNIT_BYTES, sb + offM + GV_WARPS * MPU * META_BYTES, wB, s2B, zbB);
+                __syncwarp();                   // every lane has read this warp's units: refill them with stage it + DI
+                refill(sb);
                 int accA[MPU][4], accB[MPU][4];
                 unit_mma(wA, xk, accA);
                 unit_mma(wB, xk + GV_WARPS * XU, accB);
                 unit_fin(accA, s2A, zbA, gk);
                 unit_fin(accB, s2B, zbB, gk + GV_WARPS * GU);
                 xk += 2 * GV_WARPS * XU; gk += 2 * GV_WARPS * GU;
-                sA += 2 * SLOT;
-                if (++slot == DI) { slot = 0; sA = ring; }
+                sb += STAGE;
+                if (++slot == DI) { slot = 0; sb = ring; }
             }
             if (t < MR) part[(((size_t)s * GV_WARPS + warp) * 8 + g) * MR + t] = make_float2(y0, y1);
             y0 = 0.f; y1 = 0.f;
@@ -256,26 +284,37 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
         y0 = 0.f; y1 = 0.f;
     };
     int slot = 0;
-    for (int it = 0; it < n_it; ++it) {
-        asm volatile("cp.async.wait_group %0;" ::"n"(DI - 1) : "memory");   // this lane's copies of the pair have landed ...
-        __syncwarp();                           // ... and so have the other lanes' (meta is read across lanes)
+    for (int it = 0; it < n_st; ++it) {
+        wait_stage(it);
         if (it == 0 && warp == 0) stamp(6);
-        const bool has_B = 2 * it + 1 < n_w;    // warp-uniform
+        const int uA = a + it * 2 * GV_WARPS + warp;
+        const bool has_A = uA < b, has_B = uA + GV_WARPS < b;    // warp-uniform
         int R_B = R_A, ku_B = ku_A;
         if (has_B) { ku_B += GV_WARPS; while (ku_B >= p.UPR) { ku_B -= p.UPR; ++R_B; } }
-        const uint32_t sA = ring + (uint32_t)(slot * 2 * SLOT);
+        const uint32_t sb = ring + (uint32_t)slot * STAGE;
         uint32_t wA[8], wB[8], s2A[MPU], zbA[MPU], s2B[MPU], zbB[MPU];
-        load_unit(sA, wA, s2A, zbA);
+        if (has_A) {
+            load_unit(sb + offW, sb + offM, wA, s2A, zbA);
+        } else {                                // past the range: zero weights with zero scales contribute nothing
+#pragma unroll
+            for (int q = 0; q < 8; ++q) wA[q] = 0;
+#pragma unroll
+            for (int h = 0; h < MPU; ++h) { s2A[h] = 0; zbA[h] = 0; }
+        }
         if (has_B) {
-            load_unit(sA + SLOT, wB, s2B, zbB);
-        } else {                                // odd tail: a unit of zero weights with zero scales contributes nothing
+            load_unit(sb + offW + GV_WARPS * GV_UNIT_BYTES, sb + offM + GV_WARPS * MPU * META_BYTES, wB, s2B, zbB);
+        } else {
 #pragma unroll
             for (int q = 0; q < 8; ++q) wB[q] = 0;
 #pragma unroll
             for (int h = 0; h < MPU; ++h) { s2B[h] = 0; zbB[h] = 0; }
         }
-        __syncwarp();                           // every lane has read the slot: refill it with iteration it + DI
-        issue_next(slot);
+        __syncwarp();
+        refill(sb);
+        if (!has_A) {                           // nothing of this stage belongs to this warp (only in the last stage)
+            if (++slot == DI) slot = 0;
+            continue;
+        }
         int accA[MPU][4], accB[MPU][4];
         unit_mma(wA, xs_l + (uint32_t)ku_A * XU, accA);
         unit_mma(wB, xs_l + (uint32_t)ku_B * XU, accB);
@@ -330,14 +369,13 @@ static ImmaPlan imma_plan(const Linear &L, int64_t M) {
     if (gs != 32 && gs != 64 && gs != 128) return pl;               // per-channel scales: the f16 stream kernel
     pl.mpu = 128 / gs;
     pl.MR = M <= 1 ? 1 : M <= 2 ? 2 : 4;
-    int64_t off = 0;
+    int64_t off = 128;                                               // full / empty mbarriers
     pl.off_xs = (int)off; off += L.d.K * 2 * pl.MR;                  // two byte planes per token slot
     pl.off_gtab = (int)off; off += (L.d.K / gs) * pl.MR * 8;
     off = (off + 15) & ~(int64_t)15;
     pl.off_part = (int)off; off += (int64_t)L.gv_max_slots * GV_WARPS * 8 * pl.MR * 8;
     off = (off + 127) & ~(int64_t)127;
-    const int64_t slot = GV_UNIT_BYTES + ((pl.mpu * META_BYTES + 15) & ~15);
-    const int64_t depth = GV_WARPS * 2 * slot;                       // one more iteration (2 units) in flight per warp
+    const int64_t depth = 2 * GV_WARPS * (GV_UNIT_BYTES + pl.mpu * META_BYTES);   // one more stage (32 units) in flight
     // two CTAs per SM (this linear + the next one's prefetch): 228 KB minus 1 KB reserved per CTA, halved
     int64_t D = (GV_SMEM_2CTA - off) / depth;
     if (D < 2) D = (GV_SMEM_FULL_SM - off) / depth;                  // large K x M: one CTA per SM
