@@ -159,27 +159,35 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
                 int E = (int)(mx >> 7);                                  // biased exponent of the group's max |x|
                 E = min(max(E, 14), 254);
                 const float scale = __int_as_float((267 - E) << 23);     // max|x| lands in [2^13, 2^14)
-                int xi[8];
+                // round to integers with the 1.5 * 2^23 trick: the low 16 bits of the sum's pattern are xt (two's
+                // complement), so one PRMT packs a pair; planes and the group sum then work on s16x2 words
+                uint32_t pk[4];
+                int sum = 0;
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    xi[2 * q] = __float2int_rn(__uint_as_float(w4[q] << 16) * scale);
-                    xi[2 * q + 1] = __float2int_rn(__uint_as_float(w4[q] & 0xFFFF0000u) * scale);
+                    const float lo = fmaf(__uint_as_float(w4[q] << 16), scale, 12582912.f);
+                    const float hi = fmaf(__uint_as_float(w4[q] & 0xFFFF0000u), scale, 12582912.f);
+                    pk[q] = __byte_perm(__float_as_uint(lo), __float_as_uint(hi), 0x5410);
+                    sum = __dp2a_lo((int)pk[q], 0x0101, sum);
                 }
-                int sum = ((xi[0] + xi[1]) + (xi[2] + xi[3])) + ((xi[4] + xi[5]) + (xi[6] + xi[7]));
 #pragma unroll
                 for (int o = GL / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
                 if (i < total) {
-                    const int m = i / ppr, c = i - m * ppr;              // token, piece within the row
+                    const int m = MR == 1 ? 0 : (i >= ppr) + (MR > 2 ? (i >= 2 * ppr) + (i >= 3 * ppr) : 0);
+                    const int c = i - m * ppr;                           // token, piece within the row
                     // k = 8c: unit ku = c >> 4, word j = (c & 15) >> 1, IMMA j >> 1 (half j & 1), quads t = 2(c&1), +1
                     const int j = (c & 15) >> 1;
                     uint8_t *dst = xs + ((size_t)(((c >> 4) * 4 + (j >> 1)) * 4 + 2 * (c & 1)) * COLS + 2 * m) * 8 +
                                    (j & 1) * 4;
-                    // byte order (k0, k2, k1, k3): the k order of the bytes of `w & 0x0F0F0F0F`
-                    *reinterpret_cast<uint32_t *>(dst) = gv_pack4(xi[0] >> 7, xi[2] >> 7, xi[1] >> 7, xi[3] >> 7);
-                    *reinterpret_cast<uint32_t *>(dst + 8) = gv_pack4(xi[0] & 127, xi[2] & 127, xi[1] & 127, xi[3] & 127);
-                    *reinterpret_cast<uint32_t *>(dst + COLS * 8) = gv_pack4(xi[4] >> 7, xi[6] >> 7, xi[5] >> 7, xi[7] >> 7);
-                    *reinterpret_cast<uint32_t *>(dst + COLS * 8 + 8) =
-                        gv_pack4(xi[4] & 127, xi[6] & 127, xi[5] & 127, xi[7] & 127);
+                    // xt = 128 hi + lo per 16-bit half; pair (k0,k1) | pair (k2,k3) << 8 gives the byte order
+                    // (k0, k2, k1, k3) of the bytes of `w & 0x0F0F0F0F`
+                    uint32_t hiP[4], loP[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) { hiP[q] = (pk[q] >> 7) & 0x00FF00FFu; loP[q] = pk[q] & 0x007F007Fu; }
+                    *reinterpret_cast<uint32_t *>(dst) = hiP[0] | (hiP[1] << 8);
+                    *reinterpret_cast<uint32_t *>(dst + 8) = loP[0] | (loP[1] << 8);
+                    *reinterpret_cast<uint32_t *>(dst + COLS * 8) = hiP[2] | (hiP[3] << 8);
+                    *reinterpret_cast<uint32_t *>(dst + COLS * 8 + 8) = loP[2] | (loP[3] << 8);
                     if ((c & (GL - 1)) == 0) gtab[(size_t)(c / GL) * MR + m] = make_int2(sum, (E - 13) << 23);
                 }
             }
@@ -204,16 +212,21 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
 #pragma unroll
             for (int ii = 0; ii < IPG; ++ii) {
                 const int i = h * IPG + ii;
-                uint32_t b0, b1;
-                asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(b0), "=r"(b1) : "r"(xk + (uint32_t)(i * 4 * COLS * 8)));
+                uint32_t b0 = 0, b1 = 0;
+                // only the lanes of the COLS data columns need real B values: fewer shared-memory wavefronts
+                if (COLS == 8 || g < COLS)
+                    asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(b0), "=r"(b1) : "r"(xk + (uint32_t)(i * 4 * COLS * 8)));
                 const uint32_t wa = wj[2 * i], wb = wj[2 * i + 1];
-                if (ii & 1) gi_imma(c1, wa & 0x0F0F0F0Fu, wa & 0xF0F0F0F0u, wb & 0x0F0F0F0Fu, wb & 0xF0F0F0F0u, b0, b1);
-                else gi_imma(acc[h], wa & 0x0F0F0F0Fu, wa & 0xF0F0F0F0u, wb & 0x0F0F0F0Fu, wb & 0xF0F0F0F0u, b0, b1);
+                // rows g: the low nibbles; rows g+8: the RAW bytes 16 q[g+8] + q[g] (rows g are subtracted afterwards)
+                if (ii & 1) gi_imma(c1, wa & 0x0F0F0F0Fu, wa, wb & 0x0F0F0F0Fu, wb, b0, b1);
+                else gi_imma(acc[h], wa & 0x0F0F0F0Fu, wa, wb & 0x0F0F0F0Fu, wb, b0, b1);
             }
             if (IPG > 1) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) acc[h][q] += c1[q];
             }
+            acc[h][2] -= acc[h][0];            // 16 * sum(q[g+8] x) = raw - sum(q[g] x)
+            acc[h][3] -= acc[h][1];
         }
     };
     // float part: acc = {row g hi, row g lo, row g+8 hi, row g+8 lo} of token slot t; rows g+8 carry a factor 16
