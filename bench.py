@@ -221,7 +221,7 @@ def run_gpu(args):
     per_launch_bytes = step_bytes / n_lin / max(world, 1)
     per_launch_ms = ms_per_step / n_lin
     achieved = per_launch_bytes / (per_launch_ms * 1e-3) / 1e9
-    out["roofline"] = {"bound": "hbm", "kernel": "decode_kernel<NT=1>", "achieved": round(achieved, 1),
+    out["roofline"] = {"bound": "hbm", "kernel": layers[0][6].kernel_for(M), "achieved": round(achieved, 1),
                        "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": round(achieved / peaks["hbm_gbs"], 4),
                        "traffic": None, "peak_source": peaks["source"],
                        "frac_of_spec_8TBs": round(achieved / 8000.0, 4),

@@ -125,12 +125,7 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
     };
     stamp(0);
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    if (p.fast) {   // one thread waits for the previous kernel; the others park at a hardware barrier (no issue slots)
-        if (tid == 0) asm volatile("griddepcontrol.wait;" ::: "memory");
-        __syncthreads();
-    } else {
-        asm volatile("griddepcontrol.wait;" ::: "memory");
-    }
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     stamp(1);
 
     // ---- stage the activations: per-(group, token) power-of-two scale, two signed-byte planes in B-fragment
@@ -450,7 +445,6 @@ int launch_gemv_imma(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, 
     p.off_xs = pl.off_xs; p.off_gtab = pl.off_gtab; p.off_part = pl.off_part;
     p.off_wring = pl.off_wring; p.off_mring = pl.off_mring;
     p.dbg = gemv_debug_slot();
-    p.fast = gv_env_int("W4A16_GV_WAIT1", 1);
     const bool pdl = gv_env_int("W4A16_NO_PDL", 0) == 0;
     const bool reg = (L.d.K % (32 * GV_UNIT_K)) == 0 && gv_env_int("W4A16_GV_REG", 1);
 #define W4_GI2(MR_, MPU_)                                                              \
