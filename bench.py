@@ -172,10 +172,14 @@ def run_gpu(args):
     with torch.cuda.stream(stream):
         one_step()  # warm-up outside capture (also first-touch of every weight)
         launches_per_step = P.kernel_launches() - launches0
-        if args.graph and world == 1:
-            graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph, stream=stream):
-                one_step()
+        if args.graph:
+            try:  # NCCL all-reduces on the capture stream are captured with the kernels
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph, stream=stream):
+                    one_step()
+            except Exception as e:  # keep measuring with stream launches
+                print(f"[bench] graph capture failed ({e}); stream launches", file=sys.stderr)
+                graph = None
         run = graph.replay if graph is not None else one_step
         for _ in range(args.warmup):
             run()

@@ -149,6 +149,9 @@ class ColumnParallelW4A16Linear(QuantizedLinear):
     def weight_dtype(self):
         return self.inner.weight_dtype()
 
+    def kernel_for(self, m: int) -> str:
+        return self.inner.kernel_for(m)
+
 
 class RowParallelW4A16Linear(QuantizedLinear):
     """RowParallelLinear (parallel_layers.rs:181-324): local GEMM, all_reduce(Sum), + bias."""
@@ -185,3 +188,6 @@ class RowParallelW4A16Linear(QuantizedLinear):
 
     def weight_dtype(self):
         return self.inner.weight_dtype()
+
+    def kernel_for(self, m: int) -> str:
+        return self.inner.kernel_for(m)
