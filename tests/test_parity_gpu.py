@@ -299,3 +299,19 @@ def test_cuda_graph_capture(product):
     graph.replay()
     torch.cuda.synchronize()
     assert (bits_of(y) == want).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M", [17, 64, 100, 256])
+@pytest.mark.parametrize("K,N", [(12288, 4096), (12288, 1024), (4096, 4096)])
+def test_prefill_split_k_few_tiles(product, M, K, N):
+    """Few tokens x few output tiles: the prefill kernel splits K over CTAs (fp32 partials summed in slice order).
+    Same oracle and tolerance as every other GEMM case; run twice to check the self-resetting tickets."""
+    g = 128
+    lin, (qweight, qzeros, scales, _) = make_awq_layer(product, K, N, g, seed=K + N + M)
+    q, z, sb = awq_unpacked(qweight, qzeros, scales)
+    xb = O.make_activations(M, K, seed=M)
+    want = oracle_forward(xb, q, z, sb, g)
+    first = run_forward(lin, xb)
+    assert_close_ref(first, want, f"split-K {K}x{N} M={M}")
+    assert (run_forward(lin, xb) == first).all(), "split-K result is not deterministic across launches"

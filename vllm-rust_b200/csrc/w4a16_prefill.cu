@@ -26,6 +26,7 @@
 //                          (tcgen05.commit), tmem_full / tmem_empty between MMA and epilogue.
 #include <cuda.h>  // CUtensorMap + enums only; the encode entry point is fetched from the runtime, libcuda is not linked
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <mutex>
@@ -51,6 +52,9 @@ struct PrefillParams {
     int M, K, N, KB, G;
     int gs_shift;      // log2(group size), or 31 for per-channel (every k maps to group 0)
     int n_tiles, m_tiles;
+    int ksplit, kblks_tile;   // split-K for few tokens x few output tiles: a tile = (n_tile, m_tile, k slice of kblks_tile blocks)
+    float *part;              // [ksplit][M][N] fp32 partial sums (ksplit > 1)
+    int *tickets;             // [n_tiles * m_tiles] arrival counters, self-resetting
     unsigned long long *dbg;   // W4A16_PF_DEBUG & 4: per-CTA {cycles, ns, wait_full_b, wait_full_a, wait_tmem_empty, tiles}
     int debug;         // timing experiments only (W4A16_PF_DEBUG): 1 = skip x loads after the first k block, 2 = skip dequant
 };
@@ -191,8 +195,9 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
     volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(bars + 2 * S + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int KBLKS = p.K / PF_BLOCK_K;
-    const int ntiles = p.n_tiles * p.m_tiles;
+    const int KBLKS = p.kblks_tile;              // k blocks per tile (all of K unless split)
+    const int nm_tiles = p.n_tiles * p.m_tiles;
+    const int ntiles = nm_tiles * p.ksplit;      // tile = ks * nm_tiles + m_tile * n_tiles + n_tile
 
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < S; ++i) {
@@ -220,7 +225,7 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
         // ===== TMA producer: x tiles [TM tokens][64 k] =====
         int s = 0; uint32_t ph = 0;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-            const int m_tile = tile / p.n_tiles;
+            const int m_tile = (tile % nm_tiles) / p.n_tiles, kb0 = (tile / nm_tiles) * KBLKS;
             for (int kb = 0; kb < KBLKS; ++kb) {
                 mbar_wait(empty + 8 * s, ph ^ 1);
                 if (elect_one()) {
@@ -228,7 +233,7 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
                         mbar_arrive(full + 8 * s);
                     } else {
                         mbar_arrive_expect_tx(full + 8 * s, C::B_STAGE_BYTES);
-                        tma_load_2d(smem_b + s * C::B_STAGE_BYTES, &x_map, kb * PF_BLOCK_K, m_tile * TM, full + 8 * s);
+                        tma_load_2d(smem_b + s * C::B_STAGE_BYTES, &x_map, (kb0 + kb) * PF_BLOCK_K, m_tile * TM, full + 8 * s);
                     }
                 }
                 __syncwarp();
@@ -292,13 +297,14 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
         const int total = my_tiles * KBLKS;
         const int nr = p.N >> 4;
 
-        int pf_tile = blockIdx.x, pf_kb = set;
+        int pf_tile = blockIdx.x, pf_kb = set, pf_k0 = 0;
         const uint4 *pf_w = nullptr;
         const uint8_t *pf_m = nullptr;
         bool pf_valid = false;   // false for the row blocks of a 64-row tail tile that lie beyond N: they dequantise to 0
         auto set_tile = [&](int tile) {
             const int R = (tile % p.n_tiles) * 8 + rloc;
             pf_valid = R < nr;
+            pf_k0 = (tile / nm_tiles) * KBLKS;
             pf_w = p.qw + (size_t)R * p.KB * 32 + lane;
             pf_m = p.meta + (size_t)R * p.G * META_BYTES + 4 * g;
         };
@@ -306,10 +312,10 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
         auto fetch = [&](WEntry<GPS> &e) {
             if (pf_tile >= ntiles) return;
             if (pf_valid) {
-                e.w = ldg_nc_v4(pf_w + pf_kb * 32);
+                e.w = ldg_nc_v4(pf_w + (pf_k0 + pf_kb) * 32);
 #pragma unroll
                 for (int h = 0; h < GPS; ++h) {
-                    const int grp = (pf_kb * PF_BLOCK_K + h * 32) >> p.gs_shift;
+                    const int grp = ((pf_k0 + pf_kb) * PF_BLOCK_K + h * 32) >> p.gs_shift;
                     const uint8_t *m = pf_m + grp * META_BYTES;
                     e.s2[h] = __ldg(reinterpret_cast<const uint32_t *>(m));
                     e.zb[h] = __ldg(m + (META_ZERO_OFF - 3 * g));
@@ -368,11 +374,88 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
         const int et = threadIdx.x - 20 * 32;   // 0..127
         uint32_t ti = 0;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++ti) {
-            const int n_tile = tile % p.n_tiles, m_tile = tile / p.n_tiles;
+            const int rem = tile % nm_tiles, ks = tile / nm_tiles;
+            const int n_tile = rem % p.n_tiles, m_tile = rem / p.n_tiles;
             const int n = n_tile * PF_TILE_N + q * 32 + lane;
             const float bias = p.bias && n < p.N ? __bfloat162float(p.bias[n]) : 0.f;
+            const int rows = min(TM, p.M - m_tile * TM);
             mbar_wait(tmem_full, ti & 1);
             tc_fence_after();
+            if (p.ksplit > 1) {
+                // split-K: fp32 partial of this k slice -> scratch; the last slice to arrive sums all of them in slice order
+                float *pbase = p.part + ((size_t)ks * p.M + (size_t)m_tile * TM) * p.N + n;
+#pragma unroll 1
+                for (int c = 0; c < TM / 32; ++c) {
+                    uint32_t v[32];
+                    tc_ld_32x32b_x32(tmem_base + ((uint32_t)(q * 32) << 16) + c * 32, v);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    if (n < p.N) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            if (c * 32 + i < rows) __stcg(pbase + (size_t)(c * 32 + i) * p.N, __uint_as_float(v[i]));
+                    }
+                }
+                tc_fence_before();
+                if (lane == 0) mbar_arrive(tmem_empty);
+                asm volatile("fence.acq_rel.gpu;" ::: "memory");
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                int *flag = reinterpret_cast<int *>(smem_out);
+                if (et == 0) {
+                    int prev;
+                    asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], 1;" : "=r"(prev) : "l"(p.tickets + rem) : "memory");
+                    const int last = prev == p.ksplit - 1;
+                    if (last) p.tickets[rem] = 0;          // self-reset for the next launch
+                    *flag = last;
+                }
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                const int last = *flag;
+                asm volatile("bar.sync 1, 128;" ::: "memory");   // the flag word is staging memory again
+                if (last) {
+                    asm volatile("fence.acq_rel.gpu;" ::: "memory");
+                    // 128 threads: 32 float4 columns x 4 rows per pass, every slice's loads issued before the sums
+                    const int c4 = et & 31, r0 = et >> 5;
+                    const int nn = n_tile * PF_TILE_N + c4 * 4;
+                    if (nn < p.N) {
+                        float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (p.bias) {
+                            b4.x = __bfloat162float(p.bias[nn]); b4.y = __bfloat162float(p.bias[nn + 1]);
+                            b4.z = __bfloat162float(p.bias[nn + 2]); b4.w = __bfloat162float(p.bias[nn + 3]);
+                        }
+                        const size_t slice = (size_t)p.M * p.N;
+                        // 8 rows per pass: all 8 loads of a slice are in flight before they are added (slice order)
+#pragma unroll 1
+                        for (int row0 = r0; row0 < rows; row0 += 32) {
+                            float4 acc[8];
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                            for (int s2 = 0; s2 < p.ksplit; ++s2) {
+                                float4 v[8];
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) {
+                                    const int row = row0 + 4 * i;
+                                    v[i] = row < rows ? __ldcg(reinterpret_cast<const float4 *>(
+                                                            p.part + (size_t)s2 * slice + (size_t)(m_tile * TM + row) * p.N + nn))
+                                                      : make_float4(0.f, 0.f, 0.f, 0.f);
+                                }
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) { acc[i].x += v[i].x; acc[i].y += v[i].y; acc[i].z += v[i].z; acc[i].w += v[i].w; }
+                            }
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                const int row = row0 + 4 * i;
+                                if (row < rows) {
+                                    __nv_bfloat162 lo = __floats2bfloat162_rn(acc[i].x + b4.x, acc[i].y + b4.y);
+                                    __nv_bfloat162 hi = __floats2bfloat162_rn(acc[i].z + b4.z, acc[i].w + b4.w);
+                                    uint2 out;
+                                    out.x = *reinterpret_cast<uint32_t *>(&lo); out.y = *reinterpret_cast<uint32_t *>(&hi);
+                                    *reinterpret_cast<uint2 *>(p.y + (size_t)(m_tile * TM + row) * p.N + nn) = out;
+                                }
+                            }
+                        }
+                    }
+                }
+                continue;
+            }
 #pragma unroll 1
             for (int c = 0; c < TM / 32; ++c) {
                 uint32_t v[32];
@@ -385,7 +468,6 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
             tc_fence_before();
             if (lane == 0) mbar_arrive(tmem_empty);   // the next tile's MMAs may overwrite the accumulator
             asm volatile("bar.sync 1, 128;" ::: "memory");
-            const int rows = min(TM, p.M - m_tile * TM);
             __nv_bfloat16 *ybase = p.y + (size_t)m_tile * TM * p.N + (size_t)n_tile * PF_TILE_N;
             for (int idx = et; idx < rows * 16; idx += 128) {
                 const int row = idx >> 4, c16 = idx & 15;
@@ -447,6 +529,36 @@ static int launch_pf(const CUtensorMap &map, const PrefillParams &p, int grid, c
 
 int prefill_token_tile(int64_t M) { return M > 128 ? 256 : M > 64 ? 128 : 64; }
 
+// Split-K scratch: one per device, grown on demand outside stream capture (inside a capture that would need a
+// larger one the launch simply runs unsplit).  Calls that split K on one device must be stream-ordered with each
+// other -- the engine drives all forwards from one task (engine/output_pool.rs:40-43).
+constexpr int PF_MAX_SPLIT_TILES = 1024;
+struct SplitScratch { float *part = nullptr; size_t bytes = 0; int *tickets = nullptr; };
+static SplitScratch g_split[64];
+static std::mutex g_split_mu;
+static int splitk_scratch(int device, size_t need, cudaStream_t stream, float **part, int **tickets) {
+    if (device < 0 || device >= 64) return 1;
+    std::lock_guard<std::mutex> lock(g_split_mu);
+    SplitScratch &s = g_split[device];
+    if (s.bytes < need || !s.tickets) {
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(stream, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) { *part = nullptr; return 0; }
+        if (!s.tickets) {
+            if (cudaMalloc(&s.tickets, PF_MAX_SPLIT_TILES * sizeof(int)) != cudaSuccess) { s.tickets = nullptr; return 1; }
+            cudaMemset(s.tickets, 0, PF_MAX_SPLIT_TILES * sizeof(int));
+        }
+        if (s.bytes < need) {
+            cudaDeviceSynchronize();   // nobody may still be reading the old scratch
+            cudaFree(s.part); s.part = nullptr; s.bytes = 0;
+            const size_t want = std::max<size_t>(need, (size_t)32 << 20);
+            if (cudaMalloc(&s.part, want) != cudaSuccess) { cudaGetLastError(); return 1; }
+            s.bytes = want;
+        }
+    }
+    *part = s.part; *tickets = s.tickets;
+    return 0;
+}
+
 int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
                    cudaStream_t stream) {
     if (M < 1) return fail("launch_prefill: M must be >= 1");
@@ -464,6 +576,22 @@ int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
     p.gs_shift = gs == L.d.K && gs != 32 && gs != 64 && gs != 128 ? 31 : (gs == 32 ? 5 : gs == 64 ? 6 : 7);
     p.n_tiles = (int)((L.d.N + PF_TILE_N - 1) / PF_TILE_N);  // N % 64 == 0: the last tile may be half full
     p.m_tiles = (int)((M + TM - 1) / TM);
+    // Few tokens x few output tiles would leave most SMs idle (and the weight stream latency-bound): split K so
+    // that (tiles x slices) fills the machine; partial sums meet in a per-device fp32 scratch, summed in slice order.
+    p.ksplit = 1; p.part = nullptr; p.tickets = nullptr;
+    {
+        const int kblks = (int)(L.d.K / PF_BLOCK_K), nm = p.n_tiles * p.m_tiles, sms = L.scratch->sm_count;
+        int ks = 1;
+        while (ks < 8 && nm * ks * 2 <= sms && kblks % (4 * ks) == 0 && kblks / (2 * ks) >= 48) ks *= 2;   // measured: only long K gains
+        static const bool off = getenv("W4A16_PF_NO_SPLITK") && atoi(getenv("W4A16_PF_NO_SPLITK"));
+        if (ks > 1 && !off && nm <= PF_MAX_SPLIT_TILES) {
+            float *part = nullptr; int *tickets = nullptr;
+            if (splitk_scratch(L.device, (size_t)ks * M * L.d.N * sizeof(float), stream, &part, &tickets) == 0 && part) {
+                p.ksplit = ks; p.part = part; p.tickets = tickets;
+            }
+        }
+        p.kblks_tile = kblks / p.ksplit;
+    }
     { const char *dv = getenv("W4A16_PF_DEBUG"); p.debug = dv ? atoi(dv) : 0; }
     static unsigned long long *dbg_buf = nullptr;
     p.dbg = nullptr;
@@ -483,7 +611,7 @@ int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled(x) failed with CUresult " + std::to_string((int)r));
 
-    const int ntiles = p.n_tiles * p.m_tiles;
+    const int ntiles = p.n_tiles * p.m_tiles * p.ksplit;
     const int grid = std::min(ntiles, L.scratch->sm_count);
     const int gps = gs == 32 ? 2 : 1;
 #define W4_PF(TM_)                                                          \
