@@ -172,14 +172,10 @@ def run_gpu(args):
     with torch.cuda.stream(stream):
         one_step()  # warm-up outside capture (also first-touch of every weight)
         launches_per_step = P.kernel_launches() - launches0
-        if args.graph:
-            try:  # NCCL all-reduces on the capture stream are captured with the kernels
-                graph = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(graph, stream=stream):
-                    one_step()
-            except Exception as e:  # keep measuring with stream launches
-                print(f"[bench] graph capture failed ({e}); stream launches", file=sys.stderr)
-                graph = None
+        if args.graph and world == 1:   # TP: stream launches (replaying a graph with captured NCCL all-reduces hung on this box)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=stream):
+                one_step()
         run = graph.replay if graph is not None else one_step
         for _ in range(args.warmup):
             run()

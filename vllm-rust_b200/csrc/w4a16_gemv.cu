@@ -553,9 +553,11 @@ int gemv_build_table(Linear &L, int sm_count) {
     L.gv_grid = 0;
     if (UT >= (int64_t)1 << 30) return 0;   // the register-ring kernel takes it
     int grid = (int)std::min<int64_t>(UT, (int64_t)sm_count * gv_env_int("W4A16_GEMV_CTAS_PER_SM", 1));
+    const int align = gv_env_int("W4A16_GEMV_ALIGN", 1);   // 1: ranges of whole row blocks (no shared row blocks, coarser balance)
+    // fewer row blocks than SMs but at least half as many: one row block per CTA beats sharing row blocks across CTAs
+    if (align && L.d.NR < grid && 2 * L.d.NR >= grid) grid = (int)L.d.NR;
     const int64_t q = UT / grid, r = UT % grid;
     std::vector<int> start(grid + 1);
-    const int align = gv_env_int("W4A16_GEMV_ALIGN", 1);   // 1: ranges of whole row blocks (no shared row blocks, coarser balance)
     for (int i = 0; i <= grid; ++i)
         start[i] = align && L.d.NR >= grid ? (int)((i * L.d.NR / grid) * UPR) : (int)(i * q + std::min<int64_t>(i, r));
     std::vector<int> rec((size_t)grid * 8, -1);
