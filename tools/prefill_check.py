@@ -11,7 +11,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-SHAPES = {"tiny": (256, 128), "tail": (512, 192), "qkv": (4096, 6144), "o": (4096, 4096),
+SHAPES = {"k4096": (4096, 256), "k4096n1024": (4096, 1024), "k1024": (1024, 256), "k2048": (2048, 512), "n6144": (512, 6144), "tiny": (256, 128), "tail": (512, 192), "qkv": (4096, 6144), "o": (4096, 4096),
           "gate_up": (4096, 24576), "down": (12288, 4096)}
 
 

@@ -109,76 +109,57 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 8 ? 2 : 1) gemv_stream_kerne
     // ---- stage the activations: per-(group, token) power-of-two scale, fp16, fragment order, group sums ----
     // One pass: the SUB_K/8 consecutive lanes that hold a (sub)group agree on its max by shuffles.
     const int ppr = p.K >> 3;  // 16-byte pieces per token row
-    if constexpr (DP) {
-        // Integer path: xt rounded to an integer in [-16383, 16383] (exact for every element within 2^6 of the
-        // group's maximum, |error| <= 2^-14 of that maximum below), split into two signed-byte planes
-        // xt = 128*hi + lo, packed per 4-k quad in the byte order (k0,k2,k1,k3) of the weight nibbles.
-        int *gti = reinterpret_cast<int *>(gtab);                    // [K/SUB_K][MR]{sum_t0..3, 2^e, -, -, -}
-        for (int m = 0; m < p.M; ++m) {
-            for (int c0 = tid - lane; c0 < ppr; c0 += GV_THREADS) {
-                const int c = c0 + lane;
-                const bool live = c < ppr;
-                uint4 v = make_uint4(0, 0, 0, 0);
-                if (live) v = __ldg(reinterpret_cast<const uint4 *>(p.x + (size_t)m * p.K) + c);
-                const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
-                uint32_t mx = 0;
+    // x is [M][K] contiguous: piece i = m * ppr + c.  BATCH loads are in flight per thread before the first
+    // one is consumed (a token-by-token loop pays one L2 round trip per token: 1.45 us each, measured).
+    auto stage_piece = [&](const int i, const uint4 v, const bool live) {
+        const int m = i / ppr, c = i - m * ppr;
+        const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+        uint32_t mx = 0;
 #pragma unroll
-                for (int i = 0; i < 4; ++i) mx = max(mx, max(w4[i] & 0x7FFFu, (w4[i] >> 16) & 0x7FFFu));
+        for (int q = 0; q < 4; ++q) mx = max(mx, max(w4[q] & 0x7FFFu, (w4[q] >> 16) & 0x7FFFu));
 #pragma unroll
-                for (int o = SUB_K / 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-                int E = (int)(mx >> 7);
-                E = min(max(E, 14), 254);
-                const float scale = __int_as_float((267 - E) << 23);
-                int xi[8];
+        for (int o = SUB_K / 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        int E = (int)(mx >> 7);                                  // biased exponent of the group's max |x| (bf16 bits)
+        E = min(max(E, 14), 254);
+        const float scale = __int_as_float((267 - E) << 23);     // 2^(13 - (E-127)): max|x| lands in [2^13, 2^14)
+        if constexpr (DP) {
+            // Integer path: xt rounded to an integer in [-16383, 16383] (exact for every element within 2^6 of the
+            // group's maximum, |error| <= 2^-14 of that maximum below), split into two signed-byte planes
+            // xt = 128*hi + lo, packed per 4-k quad in the byte order (k0,k2,k1,k3) of the weight nibbles.
+            int *gti = reinterpret_cast<int *>(gtab);                    // [K/SUB_K][MR]{sum_t0..3, 2^e, -, -, -}
+            int xi[8];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    xi[2 * i] = __float2int_rn(__uint_as_float(w4[i] << 16) * scale);
-                    xi[2 * i + 1] = __float2int_rn(__uint_as_float(w4[i] & 0xFFFF0000u) * scale);
-                }
-                int sumA = xi[0] + xi[1] + xi[2] + xi[3], sumB = xi[4] + xi[5] + xi[6] + xi[7];
+            for (int q = 0; q < 4; ++q) {
+                xi[2 * q] = __float2int_rn(__uint_as_float(w4[q] << 16) * scale);
+                xi[2 * q + 1] = __float2int_rn(__uint_as_float(w4[q] & 0xFFFF0000u) * scale);
+            }
+            int sumA = xi[0] + xi[1] + xi[2] + xi[3], sumB = xi[4] + xi[5] + xi[6] + xi[7];
 #pragma unroll
-                for (int o = SUB_K / 16; o > 1; o >>= 1) {   // pieces of equal parity share the quad positions t
-                    sumA += __shfl_xor_sync(0xffffffffu, sumA, o);
-                    sumB += __shfl_xor_sync(0xffffffffu, sumB, o);
-                }
-                if (live) {
-                    xs[(size_t)(2 * c) * MR + m] = make_uint2(gv_pack4(xi[0] >> 7, xi[2] >> 7, xi[1] >> 7, xi[3] >> 7),
-                                                              gv_pack4(xi[0] & 127, xi[2] & 127, xi[1] & 127, xi[3] & 127));
-                    xs[(size_t)(2 * c + 1) * MR + m] = make_uint2(gv_pack4(xi[4] >> 7, xi[6] >> 7, xi[5] >> 7, xi[7] >> 7),
-                                                                  gv_pack4(xi[4] & 127, xi[6] & 127, xi[5] & 127, xi[7] & 127));
-                    const int in_grp = c & (SUB_K / 8 - 1);
-                    if (in_grp < 2) {
-                        int *e = gti + ((size_t)(c / (SUB_K / 8)) * MR + m) * 8;
-                        e[2 * in_grp] = sumA;
-                        e[2 * in_grp + 1] = sumB;
-                        if (in_grp == 0) e[4] = (E - 13) << 23;      // bits of 2^e: undoes the scale
-                    }
+            for (int o = SUB_K / 16; o > 1; o >>= 1) {   // pieces of equal parity share the quad positions t
+                sumA += __shfl_xor_sync(0xffffffffu, sumA, o);
+                sumB += __shfl_xor_sync(0xffffffffu, sumB, o);
+            }
+            if (live) {
+                xs[(size_t)(2 * c) * MR + m] = make_uint2(gv_pack4(xi[0] >> 7, xi[2] >> 7, xi[1] >> 7, xi[3] >> 7),
+                                                          gv_pack4(xi[0] & 127, xi[2] & 127, xi[1] & 127, xi[3] & 127));
+                xs[(size_t)(2 * c + 1) * MR + m] = make_uint2(gv_pack4(xi[4] >> 7, xi[6] >> 7, xi[5] >> 7, xi[7] >> 7),
+                                                              gv_pack4(xi[4] & 127, xi[6] & 127, xi[5] & 127, xi[7] & 127));
+                const int in_grp = c & (SUB_K / 8 - 1);
+                if (in_grp < 2) {
+                    int *e = gti + ((size_t)(c / (SUB_K / 8)) * MR + m) * 8;
+                    e[2 * in_grp] = sumA;
+                    e[2 * in_grp + 1] = sumB;
+                    if (in_grp == 0) e[4] = (E - 13) << 23;      // bits of 2^e: undoes the scale
                 }
             }
-        }
-    } else {
-    for (int m = 0; m < p.M; ++m) {
-        for (int c0 = tid - lane; c0 < ppr; c0 += GV_THREADS) {   // warp-uniform trip count: the shuffles need all lanes
-            const int c = c0 + lane;
-            const bool live = c < ppr;
-            uint4 v = make_uint4(0, 0, 0, 0);
-            if (live) v = __ldg(reinterpret_cast<const uint4 *>(p.x + (size_t)m * p.K) + c);
-            const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
-            uint32_t mx = 0;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) mx = max(mx, max(w4[i] & 0x7FFFu, (w4[i] >> 16) & 0x7FFFu));
-#pragma unroll
-            for (int o = SUB_K / 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-            int E = (int)(mx >> 7);                                  // biased exponent of the group's max |x| (bf16 bits)
-            E = min(max(E, 14), 254);
-            const float scale = __int_as_float((267 - E) << 23);     // 2^(13 - (E-127)): max|x| lands in [2^13, 2^14)
+        } else {
             uint32_t h2[4];
             float sum = 0.f;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const float lo = __uint_as_float(w4[i] << 16) * scale, hi = __uint_as_float(w4[i] & 0xFFFF0000u) * scale;
+            for (int q = 0; q < 4; ++q) {
+                const float lo = __uint_as_float(w4[q] << 16) * scale, hi = __uint_as_float(w4[q] & 0xFFFF0000u) * scale;
                 const __half2 hh = __floats2half2_rn(lo, hi);
-                h2[i] = *reinterpret_cast<const uint32_t *>(&hh);
+                h2[q] = *reinterpret_cast<const uint32_t *>(&hh);
                 const float2 back = __half22float2(hh);
                 sum += back.x + back.y;
             }
@@ -194,7 +175,25 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 8 ? 2 : 1) gemv_stream_kerne
                 }
             }
         }
-    }
+    };
+    {
+        const int total = p.M * ppr;
+        const uint4 *x16 = reinterpret_cast<const uint4 *>(p.x);
+        constexpr int BATCH = 4;
+        for (int base = 0; base < total; base += BATCH * GV_THREADS) {   // warp-uniform trip count: the shuffles need all lanes
+            uint4 v[BATCH];
+#pragma unroll
+            for (int r = 0; r < BATCH; ++r) {
+                const int i = base + r * GV_THREADS + tid;
+                v[r] = i < total ? __ldg(x16 + i) : make_uint4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (int r = 0; r < BATCH; ++r) {
+                if (base + r * GV_THREADS >= total) break;               // warp-uniform
+                const int i = base + r * GV_THREADS + tid;
+                stage_piece(min(i, total - 1), v[r], i < total);
+            }
+        }
     }
     __syncthreads();
     stamp(2);

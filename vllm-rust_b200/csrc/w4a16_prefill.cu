@@ -33,6 +33,7 @@
 
 #include "w4a16_dequant.cuh"
 #include "w4a16_internal.cuh"
+#include "w4a16_tc.cuh"
 
 namespace w4 {
 
@@ -42,7 +43,6 @@ constexpr int PF_BLOCK_K = 64;     // k per pipeline stage: one W4T chunk column
 constexpr int PF_A_COL0 = 256;     // TMEM column where the A ring starts (accumulator owns [0, 256))
 constexpr int PF_A_STAGE_COLS = 32;  // 64 k of bf16 = 32 32-bit columns
 constexpr int PF_WPREF = 4;        // weight chunks each dequant warp keeps in flight
-constexpr uint32_t PF_SPIN_LIMIT = 1u << 26;
 
 struct PrefillParams {
     const uint4 *qw;
@@ -58,108 +58,6 @@ struct PrefillParams {
     unsigned long long *dbg;   // W4A16_PF_DEBUG & 4: per-CTA {cycles, ns, wait_full_b, wait_full_a, wait_tmem_empty, tiles}
     int debug;         // timing experiments only (W4A16_PF_DEBUG): 1 = skip x loads after the first k block, 2 = skip dequant
 };
-
-// ---- PTX wrappers ------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
-    uint32_t ok;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity)
-        : "memory");
-    return ok;
-}
-// A wait that cannot hang the GPU: a lost arrival traps (the launch fails loudly) instead of spinning forever.
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t spins = 0;
-    while (!mbar_try_wait(bar, parity))
-        if (++spins > PF_SPIN_LIMIT) __trap();
-}
-// One lane of a converged warp.  Code under `if (elect_one())` is known to run on a single lane, so ptxas keeps
-// descriptor / address operands in uniform registers instead of wrapping every UTCHMMA in a waterfall loop.
-__device__ __forceinline__ uint32_t elect_one() {
-    uint32_t pred;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "elect.sync _|p, 0xffffffff;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(pred));
-    return pred;
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-// D[tmem] (+)= A[tmem] * B[smem descriptor]
-__device__ __forceinline__ void tc_mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
-                                          uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, int c0, int c1, uint32_t bar) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-        ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar)
-        : "memory");
-}
-__device__ __forceinline__ void tc_st_16x256b_x4(uint32_t taddr, const uint32_t (&r)[16]) {
-    asm volatile(
-        "tcgen05.st.sync.aligned.16x256b.x4.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
-        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
-        "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
-        : "memory");
-}
-__device__ __forceinline__ void tc_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)[32]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
-          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
-          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-        : "r"(taddr)
-        : "memory");
-}
-__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
-    uint32_t r;
-    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
-    return r;
-}
-__device__ __forceinline__ uint4 ldg_nc_v4(const uint4 *p) {
-    uint4 r;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-    return r;
-}
-
-// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
-// start address >> 4 in [0,14), LBO [16,30) unused for swizzled K-major, SBO = 1024 B (8 rows x 128 B)
-// in [32,46), descriptor version 1 in [46,48), layout type SWIZZLE_128B = 2 in [61,64).
-__device__ __forceinline__ uint64_t make_b_desc(uint32_t smem_addr) {
-    return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
-}
-// kind::f16 instruction descriptor: D = f32 (bit 4), A = B = bf16 (bits 7, 10), both K-major,
-// N >> 3 in [17,23), M >> 4 in [24,29).
-__host__ __device__ constexpr uint32_t make_idesc(int umma_m, int umma_n) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(umma_n >> 3) << 17) | ((uint32_t)(umma_m >> 4) << 24);
-}
 
 template <int TM> struct PfCfg {
     static constexpr int STAGES = TM == 256 ? 5 : 8;
@@ -495,7 +393,7 @@ static EncodeTiledFn g_encode = nullptr;
 static std::once_flag g_encode_once;
 static std::string g_encode_err;
 
-static int get_encode() {
+int get_encode() {
     std::call_once(g_encode_once, [] {
         void *fn = nullptr;
         cudaDriverEntryPointQueryResult qres;
@@ -510,6 +408,20 @@ static int get_encode() {
 }
 
 bool prefill_available() { return true; }
+
+// x [M][K] bf16 as a 2-D tensor map: boxes of 64 k (one 128-byte swizzle row) x box_rows tokens, rows beyond M zero-filled.
+int encode_x_map(CUtensorMap *map, const __nv_bfloat16 *x, int64_t K, int64_t M, int box_rows) {
+    if (get_encode()) return 1;
+    const cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)M};
+    const cuuint64_t gstride[1] = {(cuuint64_t)K * 2};
+    const cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+    const cuuint32_t estride[2] = {1, 1};
+    CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16 *>(x), gdim, gstride, box,
+                          estride, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled(x) failed with CUresult " + std::to_string((int)r));
+    return 0;
+}
 
 template <int TM, int GPS>
 static int launch_pf(const CUtensorMap &map, const PrefillParams &p, int grid, cudaStream_t stream) {
@@ -532,11 +444,11 @@ int prefill_token_tile(int64_t M) { return M > 128 ? 256 : M > 64 ? 128 : 64; }
 // Split-K scratch: one per device, grown on demand outside stream capture (inside a capture that would need a
 // larger one the launch simply runs unsplit).  Calls that split K on one device must be stream-ordered with each
 // other -- the engine drives all forwards from one task (engine/output_pool.rs:40-43).
-constexpr int PF_MAX_SPLIT_TILES = 1024;
+constexpr int PF_MAX_SPLIT_TILES = SPLITK_MAX_TILES;
 struct SplitScratch { float *part = nullptr; size_t bytes = 0; int *tickets = nullptr; };
 static SplitScratch g_split[64];
 static std::mutex g_split_mu;
-static int splitk_scratch(int device, size_t need, cudaStream_t stream, float **part, int **tickets) {
+int splitk_scratch(int device, size_t need, cudaStream_t stream, float **part, int **tickets) {
     if (device < 0 || device >= 64) return 1;
     std::lock_guard<std::mutex> lock(g_split_mu);
     SplitScratch &s = g_split[device];
@@ -581,8 +493,22 @@ int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
     p.ksplit = 1; p.part = nullptr; p.tickets = nullptr;
     {
         const int kblks = (int)(L.d.K / PF_BLOCK_K), nm = p.n_tiles * p.m_tiles, sms = L.scratch->sm_count;
+        // Cost model in units of one 64-k block of one CTA (~0.35 us: the TS-mode MMA chain): waves x (blocks per
+        // slice + a fixed per-slice cost: pipeline fill, fp32 partial write, ticket, the last slice's re-read).
         int ks = 1;
-        while (ks < 8 && nm * ks * 2 <= sms && kblks % (4 * ks) == 0 && kblks / (2 * ks) >= 48) ks *= 2;   // measured: only long K gains
+        {
+            static const int forced = getenv("W4A16_PF_KSPLIT") ? atoi(getenv("W4A16_PF_KSPLIT")) : 0;
+            static const int c_fix = getenv("W4A16_PF_KSPLIT_FIX") ? atoi(getenv("W4A16_PF_KSPLIT_FIX")) : 10;
+            const int cands[6] = {1, 2, 3, 4, 6, 8};
+            long best = -1;
+            for (int c : cands) {
+                if (kblks % (2 * c) != 0 || kblks / c < 8) continue;      // a slice keeps an even number of k blocks
+                const long waves = ((long)nm * c + sms - 1) / sms;
+                const long cost = waves * (kblks / c + (c > 1 ? c_fix + TM / 16 : 0));
+                if (best < 0 || cost < best) { best = cost; ks = c; }
+            }
+            if (forced > 0 && kblks % (2 * forced) == 0) ks = forced;
+        }
         static const bool off = getenv("W4A16_PF_NO_SPLITK") && atoi(getenv("W4A16_PF_NO_SPLITK"));
         if (ks > 1 && !off && nm <= PF_MAX_SPLIT_TILES) {
             float *part = nullptr; int *tickets = nullptr;
