@@ -99,7 +99,7 @@ class ClockSampler:
 
 
 # -------------------------------------------------------------------------------------
-def build_layers(P, torch, shapes, n_layers, device, comm=None, seed=0):
+def build_layers(P, torch, shapes, n_layers, device, comm=None, seed=0, peers=None):
     """Synthetic random-int4 AWQ checkpoints of the given shapes, generated on the device and
     loaded through the product's loader API (repack included).  With a communicator every rank
     generates the same FULL checkpoint tensor and its Column/RowParallel layer keeps its slice."""
@@ -117,7 +117,7 @@ def build_layers(P, torch, shapes, n_layers, device, comm=None, seed=0):
             if mode == "col":
                 lin = P.ColumnParallelW4A16Linear(cfg, K, N, False, comm, device)
             elif mode == "row":
-                lin = P.RowParallelW4A16Linear(cfg, K, N, False, comm, device)
+                lin = P.RowParallelW4A16Linear(cfg, K, N, False, comm, device, peers=peers)
             else:
                 lin = cfg.create_linear(K, N, False, device)
             lin.load_weights({"qweight": qweight, "qzeros": qzeros, "scales": scales})
@@ -153,7 +153,10 @@ def run_gpu(args):
                     f"TP={world} (col: qkv/gate_up; row+all-reduce: o/down)")
         parallelism = f"tp{world}"
     nccl = P.NcclCommunicator(rank, world, local) if world > 1 else None
-    layers = build_layers(P, torch, shapes, n_layers, dev, nccl)
+    peers = None
+    if world > 1 and args.fused_ar:   # symmetric NVLink buffers: the row-parallel GEMVs all-reduce in their own epilogue
+        peers = P.PeerGroup(rank, world, local, max(sh[2] for sh in shapes if len(sh) > 3 and sh[3] == "row"))
+    layers = build_layers(P, torch, shapes, n_layers, dev, nccl, peers=peers)
 
     xs = {}
     ys = {}
@@ -172,7 +175,9 @@ def run_gpu(args):
     with torch.cuda.stream(stream):
         one_step()  # warm-up outside capture (also first-touch of every weight)
         launches_per_step = P.kernel_launches() - launches0
-        if args.graph and world == 1:   # TP: stream launches (replaying a graph with captured NCCL all-reduces hung on this box)
+        # TP with NCCL all-reduces: stream launches (replaying a graph with captured NCCL hung on this box); with the fused
+        # epilogue there is no NCCL call in the step and the whole TP step is one CUDA graph
+        if args.graph and (world == 1 or peers is not None):
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph, stream=stream):
                 one_step()
@@ -213,7 +218,9 @@ def run_gpu(args):
         "config": {"workload": workload, "group_size": GROUP, "M": M, "parallelism": parallelism,
                    "linears_per_step": n_lin, "weight_bytes_per_step": step_bytes,
                    "l2_policy": "inputs larger than L2: every step streams %.2f GB of distinct weights" % (step_bytes / 1e9 / max(world, 1)),
-                   "launch": "cuda-graph replay" if graph is not None else "stream launches", "pdl": os.environ.get("W4A16_NO_PDL", "0") == "0"},
+                   "launch": "cuda-graph replay" if graph is not None else "stream launches", "pdl": os.environ.get("W4A16_NO_PDL", "0") == "0",
+                   "allreduce": (None if world == 1 else "fused GEMV epilogue over NVLink peer memory (one kernel, no NCCL launch)"
+                                 if peers is not None else "ncclAllReduce after the GEMV")},
         "gpu_launches": int(launches_per_step * args.steps),
         "clocks": clk,
     }
@@ -238,6 +245,10 @@ def run_gpu(args):
     if rank == 0:
         print(json.dumps(out))
     if world > 1:
+        torch.cuda.synchronize()
+        dist.barrier()
+        if peers is not None:
+            peers.destroy()
         if nccl:
             nccl.destroy()
         dist.destroy_process_group()
@@ -420,6 +431,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--layers", type=int, default=0, help="override the number of decoder layers (debug)")
     ap.add_argument("--no-graph", dest="graph", action="store_false")
+    ap.add_argument("--no-fused-ar", dest="fused_ar", action="store_false",
+                    help="TP runs: all-reduce through ncclAllReduce instead of the fused GEMV epilogue over peer memory")
     ap.add_argument("--prefill-m", type=int, nargs="*", default=[64, 256, 1024, 4096])
     ap.add_argument("--quick", action="store_true", help="skip prefill / e2e / cpu legs")
     ap.add_argument("--only-shapes", action="store_true", help="per-shape decode sweep only")

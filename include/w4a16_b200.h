@@ -126,6 +126,29 @@ int w4a16_forward_host(w4a16_handle_t h, const void *x_bf16_host, void *y_bf16_h
 int w4a16_forward_row_allreduce(w4a16_handle_t h, const void *x_bf16, void *y_bf16, int64_t M,
                                 w4a16_comm_t comm, w4a16_stream_t stream);
 
+/* Fused row-parallel forward for decode sizes: replaces the ncclAllReduce of
+ * RowParallelLinear::forward (parallel_layers.rs:295-304, nccl.rs:1338-1364) and the dormant
+ * kernels/custom_allreduce.cu.  Every rank owns one symmetric buffer; the GEMV's epilogue stores
+ * its fp32 partial sums into every peer's buffer over NVLink (P2P stores), publishes a per-CTA
+ * epoch flag, waits for the peers' flags and sums the world's partials in rank order (+ bias).
+ * One kernel, no NCCL launch; results are bit-identical on every rank.
+ *   peer_create : allocate this rank's buffer on the current device (max_partial_floats >=
+ *                 N_out * 4 of the largest row-parallel linear);
+ *   peer_export : 64-byte IPC handle of the buffer (HOST memory), to be all-gathered out of band;
+ *   peer_attach : all_handles = world_size x 64 bytes in rank order; opens every peer's buffer.
+ * forward_row_fused falls back to w4a16_forward_row_allreduce (same result up to the reduction's
+ * rounding) when M > 4, the shape is not eligible, or peer is NULL.  The launch counter the ranks
+ * agree on lives in device memory, so the fused call can be captured into a CUDA graph.
+ * All ranks must make the same sequence of calls (SPMD), like any collective.               */
+typedef struct w4a16_peer *w4a16_peer_t;
+#define W4A16_PEER_HANDLE_BYTES 64
+int w4a16_peer_create(w4a16_peer_t *out, int rank, int world_size, int64_t max_partial_floats);
+int w4a16_peer_export(w4a16_peer_t peer, void *handle_out);
+int w4a16_peer_attach(w4a16_peer_t peer, const void *all_handles);
+int w4a16_peer_destroy(w4a16_peer_t peer);
+int w4a16_forward_row_fused(w4a16_handle_t h, const void *x_bf16, void *y_bf16, int64_t M,
+                            w4a16_peer_t peer, w4a16_comm_t comm, w4a16_stream_t stream);
+
 /* Communicator bootstrap for callers that do not already hold an ncclComm_t
  * (distributed/launcher.rs:132-262: ncclGetUniqueId on rank 0, out-of-band
  * broadcast of the 128-byte id, ncclCommInitRank).  NCCL is dlopen'ed as

@@ -12,6 +12,8 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 SHAPES = {"qkv": (4096, 6144), "o": (4096, 4096), "gate_up": (4096, 24576), "down": (12288, 4096),
+          "l70_tp2_qkv": (8192, 5120), "l70_tp2_o": (4096, 8192), "l70_tp2_gate_up": (8192, 28672), "l70_tp2_down": (14336, 8192),
+          "l70_tp8_qkv": (8192, 1280), "l70_tp8_o": (1024, 8192), "l70_tp8_gate_up": (8192, 7168), "l70_tp8_down": (3584, 8192),
           "q4_qkv": (2560, 6144), "q4_o": (4096, 2560), "q4_gate_up": (2560, 19456), "q4_down": (9728, 2560)}
 G = 128
 

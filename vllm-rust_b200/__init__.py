@@ -12,6 +12,6 @@ from .quantization import (  # noqa: F401
     detect_from_json, create_config, kernel_launches, set_dispatch,
 )
 from .parallel import (  # noqa: F401
-    DeviceCommunicator, MockCommunicator, NcclCommunicator, TorchDistCommunicator,
+    DeviceCommunicator, MockCommunicator, NcclCommunicator, PeerGroup, TorchDistCommunicator,
     ColumnParallelW4A16Linear, RowParallelW4A16Linear, shard_range,
 )

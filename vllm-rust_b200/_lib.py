@@ -48,6 +48,11 @@ SIGNATURES = {
     "w4a16_forward_into": (_i32, [_vp, _vp, _vp, _i64, _vp]),
     "w4a16_forward_host": (_i32, [_vp, _vp, _vp, _i64, _vp]),
     "w4a16_forward_row_allreduce": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp]),
+    "w4a16_peer_create": (_i32, [ctypes.POINTER(_vp), _i32, _i32, _i64]),
+    "w4a16_peer_export": (_i32, [_vp, _vp]),
+    "w4a16_peer_attach": (_i32, [_vp, _vp]),
+    "w4a16_peer_destroy": (_i32, [_vp]),
+    "w4a16_forward_row_fused": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp, _vp]),
     "w4a16_nccl_unique_id": (_i32, [_vp]),
     "w4a16_nccl_comm_init": (_i32, [ctypes.POINTER(_vp), _i32, _vp, _i32]),
     "w4a16_nccl_comm_destroy": (_i32, [_vp]),

@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "w4a16_internal.cuh"
+#include "w4a16_gemv_common.cuh"
 
 namespace w4 {
 
@@ -392,6 +393,120 @@ int w4a16_forward_row_allreduce(w4a16_handle_t h, const void *x_bf16, void *y_bf
         return 1;
     if (L->has_bias) return launch_add_bias(reinterpret_cast<__nv_bfloat16 *>(y_bf16), L->bias, M, L->d.N, s);
     return 0;
+}
+
+// ---- symmetric peer buffers + fused GEMV / all-reduce ------------------------------------------
+// Replaces the NCCL call of RowParallelLinear::forward (parallel_layers.rs:295-304, nccl.rs:1338-1364) and the
+// dormant kernels/custom_allreduce.cu for the decode sizes: the GEMV's epilogue stores its fp32 partials into
+// every peer's buffer over NVLink and sums the world's partials itself (w4a16_gemv_imma.cu).
+__global__ void peer_fill_kernel(uint32_t *p, size_t n, uint32_t v) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+struct PeerCtx {
+    int rank = 0, world = 1, device = 0;
+    uint32_t cap = 0;            // fp32 words per (buffer, source)
+    size_t bytes = 0;
+    float *local = nullptr;
+    float *base[PEER_MAX_WORLD] = {};
+    bool opened[PEER_MAX_WORLD] = {};
+    bool attached = false;
+    uint32_t *epoch_dev = nullptr;   // [0] launch counter, [1] finished-CTA ticket (device, this rank only)
+};
+
+int w4a16_peer_create(w4a16_peer_t *out, int rank, int world_size, int64_t max_partial_floats) {
+    if (!out) return fail("peer_create: null out");
+    if (world_size < 2 || world_size > PEER_MAX_WORLD) return fail("peer_create: world_size must be in 2..8");
+    if (rank < 0 || rank >= world_size) return fail("peer_create: bad rank");
+    if (max_partial_floats < 64 || max_partial_floats > ((int64_t)1 << 26)) return fail("peer_create: bad capacity");
+    PeerCtx *c = new PeerCtx();
+    c->rank = rank; c->world = world_size;
+    W4_CUDA_OK(cudaGetDevice(&c->device));
+    c->cap = (uint32_t)((max_partial_floats + 63) & ~(int64_t)63);
+    c->bytes = (size_t)3 * world_size * c->cap * sizeof(float);
+    if (cudaMalloc(&c->local, c->bytes) != cudaSuccess) { delete c; return fail("peer_create: cudaMalloc failed"); }
+    {   // every word starts as the "empty" sentinel
+        const size_t words = c->bytes / 4;
+        peer_fill_kernel<<<(unsigned)((words + 255) / 256), 256>>>(reinterpret_cast<uint32_t *>(c->local), words, PEER_EMPTY);
+        W4_CUDA_OK(cudaGetLastError());
+    }
+    W4_CUDA_OK(cudaMalloc(&c->epoch_dev, 2 * sizeof(uint32_t)));
+    W4_CUDA_OK(cudaMemset(c->epoch_dev, 0, 2 * sizeof(uint32_t)));
+    W4_CUDA_OK(cudaDeviceSynchronize());
+    c->base[rank] = c->local;
+    *out = reinterpret_cast<w4a16_peer_t>(c);
+    return 0;
+}
+
+int w4a16_peer_export(w4a16_peer_t peer, void *handle_out) {
+    PeerCtx *c = reinterpret_cast<PeerCtx *>(peer);
+    if (!c || !handle_out) return fail("peer_export: null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == W4A16_PEER_HANDLE_BYTES, "IPC handle size");
+    cudaIpcMemHandle_t hnd;
+    W4_CUDA_OK(cudaIpcGetMemHandle(&hnd, c->local));
+    memcpy(handle_out, &hnd, sizeof(hnd));
+    return 0;
+}
+
+int w4a16_peer_attach(w4a16_peer_t peer, const void *all_handles) {
+    PeerCtx *c = reinterpret_cast<PeerCtx *>(peer);
+    if (!c || !all_handles) return fail("peer_attach: null argument");
+    if (c->attached) return fail("peer_attach: already attached");
+    DeviceGuard g(c->device);
+    for (int r = 0; r < c->world; ++r) {
+        if (r == c->rank) continue;
+        cudaIpcMemHandle_t hnd;
+        memcpy(&hnd, reinterpret_cast<const char *>(all_handles) + (size_t)r * sizeof(hnd), sizeof(hnd));
+        void *ptr = nullptr;
+        W4_CUDA_OK(cudaIpcOpenMemHandle(&ptr, hnd, cudaIpcMemLazyEnablePeerAccess));
+        c->base[r] = reinterpret_cast<float *>(ptr);
+        c->opened[r] = true;
+    }
+    c->attached = true;
+    return 0;
+}
+
+int w4a16_peer_destroy(w4a16_peer_t peer) {
+    PeerCtx *c = reinterpret_cast<PeerCtx *>(peer);
+    if (!c) return 0;
+    DeviceGuard g(c->device);
+    cudaDeviceSynchronize();
+    for (int r = 0; r < c->world; ++r)
+        if (c->opened[r]) cudaIpcCloseMemHandle(c->base[r]);
+    cudaFree(c->local);
+    cudaFree(c->epoch_dev);
+    delete c;
+    return 0;
+}
+
+int w4a16_forward_row_fused(w4a16_handle_t h, const void *x_bf16, void *y_bf16, int64_t M, w4a16_peer_t peer,
+                            w4a16_comm_t comm, w4a16_stream_t stream) {
+    Linear *L = reinterpret_cast<Linear *>(h);
+    PeerCtx *c = reinterpret_cast<PeerCtx *>(peer);
+    if (!L) return fail("forward_row_fused: null handle");
+    if (L->tp_size == 1 || L->tp_mode != W4A16_TP_ROW || !c)
+        return w4a16_forward_row_allreduce(h, x_bf16, y_bf16, M, comm, stream);
+    if (!c->attached) return fail("forward_row_fused: peer buffers not attached");
+    if (c->world != L->tp_size || c->rank != L->tp_rank) return fail("forward_row_fused: peer group does not match the shard");
+    DeviceGuard g(L->device);
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    PeerView v{};
+    for (int r = 0; r < c->world; ++r) v.base[r] = c->base[r];
+    v.world = c->world; v.rank = c->rank; v.cap = c->cap;
+    v.epoch_ptr = c->epoch_dev; v.ticket = reinterpret_cast<int *>(c->epoch_dev + 1);
+    // Every rank takes the same branch: the test depends on shape, M and the group only.  The launch counter lives
+    // in device memory, so the fused kernel can be captured into a CUDA graph and replayed.
+    if (M > 4 || !L->loaded || !gemv_imma_peer_usable(*L, M, v) || env_int_api("W4A16_NO_FUSED_AR", 0))
+        return w4a16_forward_row_allreduce(h, x_bf16, y_bf16, M, comm, stream);
+    if (!x_bf16 || !y_bf16) return fail("forward_row_fused: null x or y");
+    const __nv_bfloat16 *x = reinterpret_cast<const __nv_bfloat16 *>(x_bf16);
+    if (L->perm) {
+        if (ensure_gather(L, M)) return 1;
+        if (launch_gather_x(x, L->perm, L->x_gather, M, L->d.K, s)) return 1;
+        x = L->x_gather;
+    }
+    return launch_gemv_imma_peer(*L, x, reinterpret_cast<__nv_bfloat16 *>(y_bf16), M, true, s, &v);
 }
 
 int w4a16_nccl_unique_id(void *unique_id_out) {

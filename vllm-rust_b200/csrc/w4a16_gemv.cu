@@ -665,7 +665,7 @@ int launch_gemv_stream(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y
     if (!pl.ok) return fail("launch_gemv_stream: shape not supported by the stream kernel");
     const int gs = L.d.gs;
     const int mpu = gs == 32 ? 4 : gs == 64 ? 2 : 1;
-    GemvParams p;
+    GemvParams p{};
     p.qw = reinterpret_cast<const uint8_t *>(L.qw);
     p.meta = L.meta;
     p.bias = add_bias && L.has_bias ? L.bias : nullptr;

@@ -19,6 +19,22 @@ constexpr int GV_SMEM_FULL_SM = 220 * 1024;
 constexpr int GV_SMEM_2CTA = (228 * 1024 - 2 * 1024) / 2;   // dynamic bytes per CTA that still let two CTAs share an SM
 constexpr uint32_t GV_SPIN_LIMIT = 1u << 26;
 
+// One rank's view of the symmetric buffers of a tensor-parallel group (w4a16_peer_*, w4a16_api.cu).
+// Every rank owns one allocation  data[3 rotating buffers][world sources][cap fp32 words], every word PEER_EMPTY
+// until a source stores into it, and holds the (IPC-opened) base pointer of every peer's allocation.
+constexpr int PEER_MAX_WORLD = 8;
+constexpr int PEER_TOK = 4;                    // token slots per output row in a peer buffer (the fused path takes M <= 4)
+constexpr uint32_t PEER_EMPTY = 0x80000000u;   // -0.0f: never stored as data (canonicalised to +0.0f)
+struct PeerView {
+    float *base[PEER_MAX_WORLD];   // base[r] = rank r's allocation as mapped into this process (base[rank] = own)
+    int world, rank;
+    uint32_t *epoch_ptr;           // device-resident launch counter of this rank (same value on every rank: SPMD call
+                                   // sequence); a launch uses *epoch_ptr + 1 and its last CTA stores it back, so the
+                                   // kernel is CUDA-graph capturable (nothing launch-specific in the parameters)
+    int *ticket;                   // CTAs of the current launch that have finished (self-resetting)
+    uint32_t cap;                  // fp32 words per (buffer, source)
+};
+
 struct GemvParams {
     const uint8_t *qw;
     const uint8_t *meta;
@@ -38,6 +54,8 @@ struct GemvParams {
     // shared-memory carve-up (bytes from the start of dynamic smem)
     int off_xs, off_gtab, off_flags, off_part, off_wring, off_mring;
     unsigned long long *dbg;    // W4A16_GV_DEBUG: per-CTA globaltimer stamps {start, after wait, staged, streamed, combined, end}
+    // fused row-parallel all-reduce over NVLink peer memory (w4a16_gemv_imma.cu epilogue); world <= 1: off
+    PeerView peer;
 };
 
 __device__ __forceinline__ uint32_t gv_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }

@@ -127,6 +127,10 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
     stamp(1);
+    // fused all-reduce: this launch's epoch (the previous launch's last CTA has stored the counter; read it now so
+    // that the load is off the epilogue's critical path)
+    const bool fused = p.peer.world > 1;
+    const uint32_t epoch = fused ? __ldcg(p.peer.epoch_ptr) + 1u : 0u;
 
     // ---- stage the activations: per-(group, token) power-of-two scale, two signed-byte planes in B-fragment
     //      order, integer group sums.  x is [M][K] contiguous, so 8-element piece i sits at x + 8 i. ----
@@ -342,6 +346,27 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
 
     // ---- combine the 16 warps (fixed tree: deterministic) and write y ----
     // thread (item, q): item = (slot, row g, token), q = quarter of the warps; quarters are adjacent lanes
+    //
+    // Fused row-parallel all-reduce (p.peer.world > 1), "Lamport" style: every rank owns three rotating buffers
+    // [3][world sources][cap] of fp32 words that hold the sentinel -0.0f (PEER_EMPTY) when empty.  Launch e stores
+    // this rank's partial sums (with -0.0f canonicalised to +0.0f) into slot [e % 3][rank] of EVERY rank over NVLink,
+    // polls its own slots [e % 3][0..world) until no word is the sentinel, sums the sources in rank order (the same
+    // order on every rank: bit-identical results everywhere), adds the bias and writes bf16.  The data words are
+    // their own arrival flags: no fence, no flag round trip, no barrier between ranks.  Buffer (e + 1) % 3 -- last
+    // used by launch e - 2, which this CTA itself consumed -- is reset to the sentinel for the next launch.  All
+    // ranks run the same partition, so CTA c owns the same rows everywhere and the exchange is purely per CTA.
+    float *const own = p.peer.base[p.peer.rank & (PEER_MAX_WORLD - 1)];
+    const size_t buf_words = (size_t)p.peer.world * p.peer.cap;
+    const size_t cur_off = (size_t)(epoch % 3u) * buf_words, clr_off = (size_t)((epoch + 1u) % 3u) * buf_words;
+    if (fused) {
+        // word of (row n, token) = n * PEER_TOK + token whatever this launch's MR: consecutive launches may carry
+        // different token counts, and the reset below must cover what ANY earlier launch stored for these rows
+        for (int it = tid; it < n_slots * 16 * PEER_TOK; it += GV_THREADS) {
+            const size_t idx = (size_t)(R_first * 16) * PEER_TOK + it;    // this CTA's rows are contiguous: [16 n_slots][PEER_TOK]
+            for (int r = 0; r < p.peer.world; ++r)
+                reinterpret_cast<uint32_t *>(own + clr_off + (size_t)r * p.peer.cap)[idx] = PEER_EMPTY;
+        }
+    }
     for (int it = tid; it < n_slots * 32 * MR; it += GV_THREADS) {      // multiples of 32: whole warps
         const int q = it & 3, e = (it >> 2) & (8 * MR - 1), slot = it / (32 * MR);
         const float2 *src = part + ((size_t)slot * GV_WARPS + 4 * q) * 8 * MR + e;
@@ -351,11 +376,59 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
         v.x += __shfl_xor_sync(0xffffffffu, v.x, 1); v.y += __shfl_xor_sync(0xffffffffu, v.y, 1);
         v.x += __shfl_xor_sync(0xffffffffu, v.x, 2); v.y += __shfl_xor_sync(0xffffffffu, v.y, 2);
         const int tok = e % MR, n0 = (R_first + slot) * 16 + e / MR;
-        if (q == 0 && tok < p.M) {
+        if (fused) {
+            uint32_t bx = __float_as_uint(v.x), by = __float_as_uint(v.y);
+            if (bx == PEER_EMPTY) bx = 0u;
+            if (by == PEER_EMPTY) by = 0u;
+            for (int r = q; r < p.peer.world; r += 4) {                 // lane q serves peers q, q + 4
+                uint32_t *dst = reinterpret_cast<uint32_t *>(p.peer.base[r] + cur_off + (size_t)p.peer.rank * p.peer.cap);
+                asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(dst + (size_t)n0 * PEER_TOK + tok), "r"(bx) : "memory");
+                asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(dst + (size_t)(n0 + 8) * PEER_TOK + tok), "r"(by) : "memory");
+            }
+        } else if (q == 0 && tok < p.M) {
             const float b0 = p.bias ? __bfloat162float(p.bias[n0]) : 0.f;
             const float b1 = p.bias ? __bfloat162float(p.bias[n0 + 8]) : 0.f;
             p.y[(size_t)tok * p.N + n0] = __float2bfloat16_rn(v.x + b0);
             p.y[(size_t)tok * p.N + n0 + 8] = __float2bfloat16_rn(v.y + b1);
+        }
+    }
+    if (fused) {
+        unsigned long long t0;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        for (int it = tid; it < n_slots * 16 * MR; it += GV_THREADS) {
+            const int tok = it % MR;
+            const int n = R_first * 16 + it / MR;
+            if (tok >= p.M) continue;                                   // padding token slots are never read
+            const uint32_t *srcw = reinterpret_cast<const uint32_t *>(own + cur_off) + (size_t)n * PEER_TOK + tok;
+            float acc = 0.f;
+            for (int r = 0; r < p.peer.world; ++r) {
+                uint32_t w;
+                uint32_t spins = 0;
+                for (;;) {
+                    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(w) : "l"(srcw + (size_t)r * p.peer.cap) : "memory");
+                    if (w != PEER_EMPTY) break;
+                    if ((++spins & 1023u) == 0) {
+                        unsigned long long t1;
+                        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                        if (t1 - t0 > 20000000000ull) __trap();   // 20 s: a peer never arrived -- fail loudly instead of hanging
+                    }
+                }
+                acc += __uint_as_float(w);
+            }
+            const float bsv = p.bias ? __bfloat162float(p.bias[n]) : 0.f;
+            p.y[(size_t)tok * p.N + n] = __float2bfloat16_rn(acc + bsv);
+        }
+        // the last CTA of this launch to finish advances the rank's epoch (every CTA read it right after its
+        // griddepcontrol.wait, before its own ticket; the next launch reads it after ITS griddepcontrol.wait)
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence();
+            const int prev = atomicAdd(p.peer.ticket, 1);
+            if (prev == (int)gridDim.x - 1) {
+                *p.peer.ticket = 0;
+                *p.peer.epoch_ptr = epoch;
+                __threadfence();
+            }
         }
     }
     stamp(4);
@@ -429,6 +502,17 @@ static int gi_launch_t(const GemvParams &p, const ImmaPlan &pl, int grid, cudaSt
 
 int launch_gemv_imma(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
                      cudaStream_t stream) {
+    return launch_gemv_imma_peer(L, x, y, M, add_bias, stream, nullptr);
+}
+
+// peer != null: the epilogue all-reduces the row-parallel partial sums over the peers' symmetric buffers.
+bool gemv_imma_peer_usable(const Linear &L, int64_t M, const PeerView &peer) {
+    const ImmaPlan pl = imma_plan(L, M);
+    return pl.ok && peer.world > 1 && peer.world <= PEER_MAX_WORLD && (uint64_t)L.d.N * PEER_TOK <= peer.cap;
+}
+
+int launch_gemv_imma_peer(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
+                          cudaStream_t stream, const PeerView *peer) {
     const ImmaPlan pl = imma_plan(L, M);
     if (!pl.ok) return fail("launch_gemv_imma: shape not supported by the IMMA stream kernel");
     GemvParams p{};
@@ -445,6 +529,10 @@ int launch_gemv_imma(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, 
     p.off_xs = pl.off_xs; p.off_gtab = pl.off_gtab; p.off_part = pl.off_part;
     p.off_wring = pl.off_wring; p.off_mring = pl.off_mring;
     p.dbg = gemv_debug_slot();
+    if (peer) {
+        if (!gemv_imma_peer_usable(L, M, *peer)) return fail("launch_gemv_imma: shape not supported by the fused all-reduce epilogue");
+        p.peer = *peer;
+    }
     const bool pdl = gv_env_int("W4A16_NO_PDL", 0) == 0;
     const bool reg = (L.d.K % (32 * GV_UNIT_K)) == 0 && gv_env_int("W4A16_GV_REG", 1);
 #define W4_GI2(MR_, MPU_)                                                              \

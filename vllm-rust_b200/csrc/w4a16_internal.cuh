@@ -105,6 +105,10 @@ int launch_gemv_stream(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y
 bool gemv_imma_usable(const Linear &L, int64_t M);
 int launch_gemv_imma(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
                      cudaStream_t stream);
+struct PeerView;   // w4a16_gemv_common.cuh
+bool gemv_imma_peer_usable(const Linear &L, int64_t M, const PeerView &peer);
+int launch_gemv_imma_peer(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
+                          cudaStream_t stream, const PeerView *peer);
 // decode, M <= 4: tcgen05 kernel (w4a16_gemv_umma.cu)
 bool gemv_umma_usable(const Linear &L, int64_t M);
 int gemv_umma_build_table(Linear &L, int sm_count);

@@ -120,6 +120,41 @@ class NcclCommunicator(DeviceCommunicator):
             self._comm = ctypes.c_void_p()
 
 
+class PeerGroup:
+    """Symmetric NVLink peer buffers of a tensor-parallel group (w4a16_peer_*): what the fused GEMV + all-reduce
+    epilogue writes into.  Replaces the reference's dormant custom all-reduce (kernels/custom_allreduce.cu) for
+    the decode sizes.  The 64-byte IPC handles travel over torch.distributed, like the NCCL unique id."""
+
+    HANDLE_BYTES = 64
+
+    def __init__(self, rank: int, world_size: int, device: int, max_out_features: int, group=None):
+        import torch.distributed as dist
+        self._r, self._w = rank, world_size
+        self._peer = ctypes.c_void_p()
+        with torch.cuda.device(device):
+            check(lib().w4a16_peer_create(ctypes.byref(self._peer), rank, world_size, int(max_out_features) * 4))
+            raw = (ctypes.c_char * self.HANDLE_BYTES)()
+            check(lib().w4a16_peer_export(self._peer, ctypes.cast(raw, ctypes.c_void_p)))
+            mine = torch.frombuffer(bytearray(raw.raw), dtype=torch.uint8).clone()
+            on_gpu = dist.get_backend(group) == "nccl"
+            if on_gpu:
+                mine = mine.cuda(device)
+            gathered = [torch.empty_like(mine) for _ in range(world_size)]
+            dist.all_gather(gathered, mine, group=group)
+            blob = b"".join(bytes(t.cpu().tolist()) for t in gathered)
+            buf = (ctypes.c_char * len(blob)).from_buffer_copy(blob)
+            check(lib().w4a16_peer_attach(self._peer, ctypes.cast(buf, ctypes.c_void_p)))
+            dist.barrier(group=group)   # nobody launches before every rank has mapped every buffer
+
+    def ptr(self) -> Optional[int]:
+        return self._peer.value
+
+    def destroy(self):
+        if self._peer:
+            lib().w4a16_peer_destroy(self._peer)
+            self._peer = ctypes.c_void_p()
+
+
 class ColumnParallelW4A16Linear(QuantizedLinear):
     """ColumnParallelLinear (parallel_layers.rs:36-170) over a W4A16 shard; gather_output=false."""
 
@@ -156,8 +191,10 @@ class ColumnParallelW4A16Linear(QuantizedLinear):
 class RowParallelW4A16Linear(QuantizedLinear):
     """RowParallelLinear (parallel_layers.rs:181-324): local GEMM, all_reduce(Sum), + bias."""
 
-    def __init__(self, config, in_features: int, out_features: int, bias: bool, comm: DeviceCommunicator, device):
+    def __init__(self, config, in_features: int, out_features: int, bias: bool, comm: DeviceCommunicator, device,
+                 peers: Optional["PeerGroup"] = None):
         self.comm = comm
+        self.peers = peers   # with a PeerGroup decode-sized calls all-reduce inside the GEMV kernel (no NCCL launch)
         self.inner: B200W4A16Linear = config.create_linear(
             in_features, out_features, bias, device, tp_mode=TP_ROW, tp_rank=comm.rank(), tp_size=comm.world_size())
 
@@ -175,7 +212,10 @@ class RowParallelW4A16Linear(QuantizedLinear):
     def forward_into(self, x2, y):
         if self.comm.world_size() > 1 and self.comm.nccl_comm() is None:
             raise W4A16Error("RowParallelW4A16Linear needs an NcclCommunicator for world_size > 1")
-        self.inner.forward_row_allreduce(x2, y, self.comm.nccl_comm())
+        if self.peers is not None and self.comm.world_size() > 1:
+            self.inner.forward_row_fused(x2, y, self.peers.ptr(), self.comm.nccl_comm())
+        else:
+            self.inner.forward_row_allreduce(x2, y, self.comm.nccl_comm())
 
     def in_features(self):
         return self.inner.in_features()

@@ -255,6 +255,12 @@ class B200W4A16Linear(QuantizedLinear):
         check(lib().w4a16_forward_row_allreduce(self._h, ctypes.c_void_p(x2.data_ptr()), ctypes.c_void_p(y.data_ptr()),
                                                 x2.shape[0], ctypes.c_void_p(comm_ptr or 0), _stream_ptr(x2)))
 
+    def forward_row_fused(self, x2: torch.Tensor, y: torch.Tensor, peer_ptr: Optional[int], comm_ptr: Optional[int]) -> None:
+        with torch.cuda.device(self._device):
+            check(lib().w4a16_forward_row_fused(self._h, ctypes.c_void_p(x2.data_ptr()), ctypes.c_void_p(y.data_ptr()),
+                                                x2.shape[0], ctypes.c_void_p(peer_ptr or 0), ctypes.c_void_p(comm_ptr or 0),
+                                                _stream_ptr(x2)))
+
     def reserve(self, max_tokens: int) -> None:
         with torch.cuda.device(self._device):
             check(lib().w4a16_reserve(self._h, max_tokens))
