@@ -177,7 +177,7 @@ def run_gpu(args):
         launches_per_step = P.kernel_launches() - launches0
         # TP with NCCL all-reduces: stream launches (replaying a graph with captured NCCL hung on this box); with the fused
         # epilogue there is no NCCL call in the step and the whole TP step is one CUDA graph
-        if args.graph and (world == 1 or peers is not None):
+        if args.graph and (world == 1 or (peers is not None and os.environ.get("W4A16_NO_FUSED_AR", "0") == "0")):
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph, stream=stream):
                 one_step()

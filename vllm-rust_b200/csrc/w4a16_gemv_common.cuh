@@ -33,6 +33,7 @@ struct PeerView {
                                    // kernel is CUDA-graph capturable (nothing launch-specific in the parameters)
     int *ticket;                   // CTAs of the current launch that have finished (self-resetting)
     uint32_t cap;                  // fp32 words per (buffer, source)
+    uint32_t flags;                // bit 0: release programmatic dependents early (experiment, W4A16_FUSED_EARLY_PDL)
 };
 
 struct GemvParams {
