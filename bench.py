@@ -57,6 +57,15 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
 
 
+def decode_traffic(world):
+    """dram bytes per launch of the decode kernel from the committed ncu --set full capture (profiles/), averaged
+    over the four Qwen3-8B shapes like `achieved`; None for the TP workload (not captured under ncu)."""
+    p = os.path.join(ROOT, "profiles", "r1_decode_traffic.json")
+    if world != 1 or not os.path.exists(p):
+        return None
+    return json.load(open(p)).get("mean_per_launch")
+
+
 class ClockSampler:
     """nvidia-smi clocks/throttle reasons DURING the timed region (B200_PROFILING.md)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
@@ -230,7 +239,7 @@ def run_gpu(args):
     achieved = per_launch_bytes / (per_launch_ms * 1e-3) / 1e9
     out["roofline"] = {"bound": "hbm", "kernel": layers[0][6].kernel_for(M), "achieved": round(achieved, 1),
                        "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": round(achieved / peaks["hbm_gbs"], 4),
-                       "traffic": None, "peak_source": peaks["source"],
+                       "traffic": decode_traffic(world), "peak_source": peaks["source"],
                        "frac_of_spec_8TBs": round(achieved / 8000.0, 4),
                        "algorithmic_bytes_per_launch": int(per_launch_bytes)}
     if rank == 0 and world == 1:

@@ -40,7 +40,9 @@ __device__ __forceinline__ void gi_imma(int (&c)[4], uint32_t a0, uint32_t a1, u
 // hide the tensor-pipe and shared-memory latencies that 4 warps per scheduler cannot).
 // REG = every row block is a whole number of 32-unit strides (K % 4096 == 0): the two units of an iteration share
 // their row block and every warp visits every row block, so the loop carries no row-block bookkeeping.
-template <int MR, int MPU, int DI, bool REG>
+// FUSED = the epilogue all-reduces row-parallel partial sums over the peers' symmetric buffers (p.peer); a separate
+// instantiation, so the single-GPU kernel carries none of it.
+template <int MR, int MPU, int DI, bool REG, bool FUSED>
 __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvParams p) {
     constexpr int COLS = 2 * MR;               // B columns holding data: (hi, lo) plane of each token slot
     constexpr int IPG = 4 / MPU;               // IMMAs per group
@@ -126,13 +128,14 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
     stamp(0);
     // A launch that ends with the cross-GPU exchange releases its dependents only at exit: with the next linear's
     // CTAs co-resident during the exchange the TP=2 step measured 1.21 ms against 1.02 ms without (bench.py --gpus 2).
-    if (p.peer.world <= 1 || (p.peer.flags & 1)) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (!FUSED || (p.peer.flags & 1)) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
     stamp(1);
     // fused all-reduce: this launch's epoch (the previous launch's last CTA has stored the counter; read it now so
     // that the load is off the epilogue's critical path)
-    const bool fused = p.peer.world > 1;
-    const uint32_t epoch = fused ? __ldcg(p.peer.epoch_ptr) + 1u : 0u;
+    constexpr bool fused = FUSED;
+    uint32_t epoch = 0u;
+    if constexpr (FUSED) epoch = __ldcg(p.peer.epoch_ptr) + 1u;
 
     // ---- stage the activations: per-(group, token) power-of-two scale, two signed-byte planes in B-fragment
     //      order, integer group sums.  x is [M][K] contiguous, so 8-element piece i sits at x + 8 i. ----
@@ -357,10 +360,14 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
     // their own arrival flags: no fence, no flag round trip, no barrier between ranks.  Buffer (e + 1) % 3 -- last
     // used by launch e - 2, which this CTA itself consumed -- is reset to the sentinel for the next launch.  All
     // ranks run the same partition, so CTA c owns the same rows everywhere and the exchange is purely per CTA.
-    float *const own = p.peer.base[p.peer.rank & (PEER_MAX_WORLD - 1)];
-    const size_t buf_words = (size_t)p.peer.world * p.peer.cap;
-    const size_t cur_off = (size_t)(epoch % 3u) * buf_words, clr_off = (size_t)((epoch + 1u) % 3u) * buf_words;
-    if (fused) {
+    float *own = nullptr;
+    size_t cur_off = 0, clr_off = 0;
+    if constexpr (FUSED) {
+        own = p.peer.base[p.peer.rank & (PEER_MAX_WORLD - 1)];
+        const size_t buf_words = (size_t)p.peer.world * p.peer.cap;
+        cur_off = (size_t)(epoch % 3u) * buf_words; clr_off = (size_t)((epoch + 1u) % 3u) * buf_words;
+    }
+    if constexpr (FUSED) {
         // word of (row n, token) = n * PEER_TOK + token whatever this launch's MR: consecutive launches may carry
         // different token counts, and the reset below must cover what ANY earlier launch stored for these rows
         for (int it = tid; it < n_slots * 16 * PEER_TOK; it += GV_THREADS) {
@@ -378,7 +385,7 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
         v.x += __shfl_xor_sync(0xffffffffu, v.x, 1); v.y += __shfl_xor_sync(0xffffffffu, v.y, 1);
         v.x += __shfl_xor_sync(0xffffffffu, v.x, 2); v.y += __shfl_xor_sync(0xffffffffu, v.y, 2);
         const int tok = e % MR, n0 = (R_first + slot) * 16 + e / MR;
-        if (fused) {
+        if constexpr (FUSED) {
             uint32_t bx = __float_as_uint(v.x), by = __float_as_uint(v.y);
             if (bx == PEER_EMPTY) bx = 0u;
             if (by == PEER_EMPTY) by = 0u;
@@ -394,7 +401,7 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
             p.y[(size_t)tok * p.N + n0 + 8] = __float2bfloat16_rn(v.y + b1);
         }
     }
-    if (fused) {
+    if constexpr (FUSED) {
         unsigned long long t0;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
         for (int it = tid; it < n_slots * 16 * MR; it += GV_THREADS) {
@@ -479,11 +486,11 @@ bool gemv_imma_usable(const Linear &L, int64_t M) {
     return imma_plan(L, M).ok;
 }
 
-template <int MR, int MPU, int DI, bool REG>
+template <int MR, int MPU, int DI, bool REG, bool FUSED>
 static int gi_launch_t(const GemvParams &p, const ImmaPlan &pl, int grid, cudaStream_t stream, bool pdl) {
     static bool attr_set = false;   // racing threads only repeat the call
     if (!attr_set) {
-        W4_CUDA_OK(cudaFuncSetAttribute(gemv_imma_kernel<MR, MPU, DI, REG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        W4_CUDA_OK(cudaFuncSetAttribute(gemv_imma_kernel<MR, MPU, DI, REG, FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         GV_SMEM_FULL_SM));
         attr_set = true;
     }
@@ -497,7 +504,7 @@ static int gi_launch_t(const GemvParams &p, const ImmaPlan &pl, int grid, cudaSt
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    W4_CUDA_OK(cudaLaunchKernelEx(&cfg, gemv_imma_kernel<MR, MPU, DI, REG>, p));
+    W4_CUDA_OK(cudaLaunchKernelEx(&cfg, gemv_imma_kernel<MR, MPU, DI, REG, FUSED>, p));
     count_launch();
     return 0;
 }
@@ -538,14 +545,19 @@ int launch_gemv_imma_peer(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16
     // a launch with the fused exchange is not launched programmatically early either (experiment switch: bit 1)
     const bool pdl = gv_env_int("W4A16_NO_PDL", 0) == 0 && (!peer || gv_env_int("W4A16_FUSED_PDL_ATTR", 0));
     const bool reg = (L.d.K % (32 * GV_UNIT_K)) == 0 && gv_env_int("W4A16_GV_REG", 1);
-#define W4_GI2(MR_, MPU_)                                                              \
+#define W4_GI3(MR_, MPU_, FUSED_)                                                      \
     do {                                                                               \
         if (reg) {                                                                     \
-            if (pl.S == 3) return gi_launch_t<MR_, MPU_, 3, true>(p, pl, L.gv_grid, stream, pdl);  \
-            return gi_launch_t<MR_, MPU_, 2, true>(p, pl, L.gv_grid, stream, pdl);     \
+            if (pl.S == 3) return gi_launch_t<MR_, MPU_, 3, true, FUSED_>(p, pl, L.gv_grid, stream, pdl);  \
+            return gi_launch_t<MR_, MPU_, 2, true, FUSED_>(p, pl, L.gv_grid, stream, pdl);     \
         }                                                                              \
-        if (pl.S == 3) return gi_launch_t<MR_, MPU_, 3, false>(p, pl, L.gv_grid, stream, pdl); \
-        return gi_launch_t<MR_, MPU_, 2, false>(p, pl, L.gv_grid, stream, pdl);        \
+        if (pl.S == 3) return gi_launch_t<MR_, MPU_, 3, false, FUSED_>(p, pl, L.gv_grid, stream, pdl); \
+        return gi_launch_t<MR_, MPU_, 2, false, FUSED_>(p, pl, L.gv_grid, stream, pdl);        \
+    } while (0)
+#define W4_GI2(MR_, MPU_)                                                              \
+    do {                                                                               \
+        if (peer) W4_GI3(MR_, MPU_, true);                                             \
+        W4_GI3(MR_, MPU_, false);                                                      \
     } while (0)
 #define W4_GI(MR_)                                                                     \
     do {                                                                               \
@@ -559,6 +571,7 @@ int launch_gemv_imma_peer(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16
         default: W4_GI(4);
     }
 #undef W4_GI2
+#undef W4_GI3
 #undef W4_GI
 }
 
