@@ -180,6 +180,24 @@ def test_skinny_kernel_groups_bias_tail_and_many_tiles(product, g, K, N, M):
     assert (got == again).all()   # split-K partials are summed in slice order: deterministic
 
 
+@pytest.mark.parametrize("M", [5, 8])
+@pytest.mark.parametrize("K,N,g", [(4096, 4096, 128), (2048, 4736, 64), (1024, 2368, 32)])
+def test_imma_two_token_tiles_opt_in(product, M, K, N, g):
+    """The int8 tensor-core GEMV with two token tiles (5..8 tokens), opt-in through W4A16_IMMA8 (read per call)."""
+    import os
+    lin, (qweight, qzeros, scales, _) = make_awq_layer(product, K, N, g, seed=41 + M)
+    q, z, sb = awq_unpacked(qweight, qzeros, scales)
+    xb = O.make_activations(M, K, seed=200 + M)
+    os.environ["W4A16_IMMA8"] = "1"
+    try:
+        assert lin.kernel_for(M) == "gemv_stream_imma"
+        got = run_forward(lin, xb)
+    finally:
+        del os.environ["W4A16_IMMA8"]
+    assert lin.kernel_for(M) != "gemv_stream_imma"
+    assert_close_ref(got, oracle_forward(xb, q, z, sb, g), f"imma8 M={M} {K}x{N} g={g}")
+
+
 def test_rank3_input_and_noncontiguous(product):
     K, N, g = 256, 128, 128
     lin, (qweight, qzeros, scales, _) = make_awq_layer(product, K, N, g, seed=9)

@@ -498,7 +498,7 @@ int w4a16_forward_row_fused(w4a16_handle_t h, const void *x_bf16, void *y_bf16, 
     v.epoch_ptr = c->epoch_dev; v.ticket = reinterpret_cast<int *>(c->epoch_dev + 1);
     // Every rank takes the same branch: the test depends on shape, M and the group only.  The launch counter lives
     // in device memory, so the fused kernel can be captured into a CUDA graph and replayed.
-    if (M > 4 || !L->loaded || !gemv_imma_peer_usable(*L, M, v) || env_int_api("W4A16_NO_FUSED_AR", 0))
+    if (M > PEER_TOK || !L->loaded || !gemv_imma_peer_usable(*L, M, v) || env_int_api("W4A16_NO_FUSED_AR", 0))
         return w4a16_forward_row_allreduce(h, x_bf16, y_bf16, M, comm, stream);
     if (!x_bf16 || !y_bf16) return fail("forward_row_fused: null x or y");
     const __nv_bfloat16 *x = reinterpret_cast<const __nv_bfloat16 *>(x_bf16);

@@ -43,8 +43,9 @@ __device__ __forceinline__ void gi_imma(int (&c)[4], uint32_t a0, uint32_t a1, u
 // FUSED = the epilogue all-reduces row-parallel partial sums over the peers' symmetric buffers (p.peer); a separate
 // instantiation, so the single-GPU kernel carries none of it.
 template <int MR, int MPU, int DI, bool REG, bool FUSED>
-__global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvParams p) {
+__global__ void __launch_bounds__(GV_THREADS, MR <= 4 ? 2 : 1) gemv_imma_kernel(const GemvParams p) {
     constexpr int COLS = 2 * MR;               // B columns holding data: (hi, lo) plane of each token slot
+    constexpr int NT = MR <= 4 ? 1 : MR / 4;   // IMMA token tiles (8 columns = 4 tokens x 2 planes each); lane t of tile nt = token 4 nt + t
     constexpr int IPG = 4 / MPU;               // IMMAs per group
     constexpr int SUB_K = GV_UNIT_K / MPU;     // k per group inside a unit
     constexpr int GL = SUB_K / 8;              // staging lanes (8-element pieces) per group
@@ -177,7 +178,7 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
 #pragma unroll
                 for (int o = GL / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
                 if (i < total) {
-                    const int m = MR == 1 ? 0 : (i >= ppr) + (MR > 2 ? (i >= 2 * ppr) + (i >= 3 * ppr) : 0);
+                    const int m = MR == 1 ? 0 : MR > 4 ? i / ppr : (i >= ppr) + (MR > 2 ? (i >= 2 * ppr) + (i >= 3 * ppr) : 0);
                     const int c = i - m * ppr;                           // token, piece within the row
                     // k = 8c: unit ku = c >> 4, word j = (c & 15) >> 1, IMMA j >> 1 (half j & 1), quads t = 2(c&1), +1
                     const int j = (c & 15) >> 1;
@@ -203,49 +204,63 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
     // ---- main loop: iteration `it` handles this warp's units A = 2 it and B = 2 it + 1 (stream units a + warp + 32 it, + 16) ----
     constexpr uint32_t XU = 4 * 4 * COLS * 8;  // bytes of B fragments per unit
     constexpr uint32_t GU = MPU * MR * 8;      // bytes of group table per unit
-    float y0 = 0.f, y1 = 0.f;                  // rows g / g+8 of the current row block, token slot t
-    const uint32_t xs_l = gv_smem_u32(xs) + (uint32_t)((t * COLS + (g & (COLS - 1))) * 8);
-    const uint32_t gt_l = gv_smem_u32(gtab) + (uint32_t)((t & (MR - 1)) * 8);
+    float y0[NT], y1[NT];                      // rows g / g+8 of the current row block, token slot 4 nt + t
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) { y0[nt] = 0.f; y1[nt] = 0.f; }
+    const uint32_t xs_l = gv_smem_u32(xs) + (uint32_t)((t * COLS + (g & (COLS - 1))) * 8);   // + 64 nt: columns 8 nt + g
+    const uint32_t gt_l = gv_smem_u32(gtab) + (uint32_t)((t & (MR - 1)) * 8);                // + 32 nt: token 4 nt + t
     // integer part of one unit: 4 IMMAs into MPU group accumulators (xk = this lane's B fragments of the unit)
-    auto unit_mma = [&](const uint32_t (&wj)[8], uint32_t xk, int (&acc)[MPU][4]) {
+    auto unit_mma = [&](const uint32_t (&wj)[8], uint32_t xk, int (&acc)[NT][MPU][4]) {
 #pragma unroll
         for (int h = 0; h < MPU; ++h) {
-            int c1[4] = {0, 0, 0, 0};          // second accumulator chain when a group spans several IMMAs
+            int c1[NT][4];                     // second accumulator chain when a group spans several IMMAs
 #pragma unroll
-            for (int q = 0; q < 4; ++q) acc[h][q] = 0;
+            for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) { acc[nt][h][q] = 0; c1[nt][q] = 0; }
 #pragma unroll
             for (int ii = 0; ii < IPG; ++ii) {
                 const int i = h * IPG + ii;
-                uint32_t b0 = 0, b1 = 0;
-                // only the lanes of the COLS data columns need real B values: fewer shared-memory wavefronts
-                if (COLS == 8 || g < COLS)
-                    asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(b0), "=r"(b1) : "r"(xk + (uint32_t)(i * 4 * COLS * 8)));
                 const uint32_t wa = wj[2 * i], wb = wj[2 * i + 1];
                 // rows g: the low nibbles; rows g+8: the RAW bytes 16 q[g+8] + q[g] (rows g are subtracted afterwards)
-                if (ii & 1) gi_imma(c1, wa & 0x0F0F0F0Fu, wa, wb & 0x0F0F0F0Fu, wb, b0, b1);
-                else gi_imma(acc[h], wa & 0x0F0F0F0Fu, wa, wb & 0x0F0F0F0Fu, wb, b0, b1);
-            }
-            if (IPG > 1) {
+                const uint32_t la = wa & 0x0F0F0F0Fu, lb = wb & 0x0F0F0F0Fu;
 #pragma unroll
-                for (int q = 0; q < 4; ++q) acc[h][q] += c1[q];
+                for (int nt = 0; nt < NT; ++nt) {
+                    uint32_t b0 = 0, b1 = 0;
+                    // only the lanes of the COLS data columns need real B values: fewer shared-memory wavefronts
+                    if (COLS >= 8 || g < COLS)
+                        asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(b0), "=r"(b1) : "r"(xk + (uint32_t)(i * 4 * COLS * 8 + nt * 64)));
+                    if (ii & 1) gi_imma(c1[nt], la, wa, lb, wb, b0, b1);
+                    else gi_imma(acc[nt][h], la, wa, lb, wb, b0, b1);
+                }
             }
-            acc[h][2] -= acc[h][0];            // 16 * sum(q[g+8] x) = raw - sum(q[g] x)
-            acc[h][3] -= acc[h][1];
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+                if (IPG > 1) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) acc[nt][h][q] += c1[nt][q];
+                }
+                acc[nt][h][2] -= acc[nt][h][0];    // 16 * sum(q[g+8] x) = raw - sum(q[g] x)
+                acc[nt][h][3] -= acc[nt][h][1];
+            }
         }
     };
     // float part: acc = {row g hi, row g lo, row g+8 hi, row g+8 lo} of token slot t; rows g+8 carry a factor 16
-    auto unit_fin = [&](const int (&acc)[MPU][4], const uint32_t (&s2)[MPU], const uint32_t (&zb)[MPU], uint32_t gk) {
+    auto unit_fin = [&](const int (&acc)[NT][MPU][4], const uint32_t (&s2)[MPU], const uint32_t (&zb)[MPU], uint32_t gk) {
 #pragma unroll
         for (int h = 0; h < MPU; ++h) {
-            int X, e2b;
-            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(X), "=r"(e2b) : "r"(gk + (uint32_t)(h * MR * 8)));
-            const float e2 = __int_as_float(e2b);
-            const int tg = acc[h][0] * 128 + acc[h][1] - (int)(zb[h] & 0x0Fu) * X;
-            const int tg8 = acc[h][2] * 128 + acc[h][3] - (int)(zb[h] & 0xF0u) * X;
-            const float slo = __uint_as_float(s2[h] << 16) * e2;
-            const float shi = __uint_as_float(s2[h] & 0xFFFF0000u) * (e2 * 0.0625f);
-            y0 = fmaf(slo, (float)tg, y0);
-            y1 = fmaf(shi, (float)tg8, y1);
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+                int X, e2b;
+                asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(X), "=r"(e2b) : "r"(gk + (uint32_t)(h * MR * 8 + nt * 32)));
+                const float e2 = __int_as_float(e2b);
+                const int tg = acc[nt][h][0] * 128 + acc[nt][h][1] - (int)(zb[h] & 0x0Fu) * X;
+                const int tg8 = acc[nt][h][2] * 128 + acc[nt][h][3] - (int)(zb[h] & 0xF0u) * X;
+                const float slo = __uint_as_float(s2[h] << 16) * e2;
+                const float shi = __uint_as_float(s2[h] & 0xFFFF0000u) * (e2 * 0.0625f);
+                y0[nt] = fmaf(slo, (float)tg, y0[nt]);
+                y1[nt] = fmaf(shi, (float)tg8, y1[nt]);
+            }
         }
     };
     auto load_unit = [&](uint32_t sw, uint32_t sm, uint32_t (&w)[8], uint32_t (&s2)[MPU], uint32_t (&zb)[MPU]) {
@@ -281,7 +296,7 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
                 load_unit(sb + offW + GV_WARPS * GV_UNIT_BYTES, sb + offM + GV_WARPS * MPU * META_BYTES, wB, s2B, zbB);
                 __syncwarp();                   // every lane has read this warp's units: refill them with stage it + DI
                 refill(sb);
-                int accA[MPU][4], accB[MPU][4];
+                int accA[NT][MPU][4], accB[NT][MPU][4];
                 unit_mma(wA, xk, accA);
                 unit_mma(wB, xk + GV_WARPS * XU, accB);
                 unit_fin(accA, s2A, zbA, gk);
@@ -290,15 +305,21 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
                 sb += STAGE;
                 if (++slot == DI) { slot = 0; sb = ring; }
             }
-            if (t < MR) part[(((size_t)s * GV_WARPS + warp) * 8 + g) * MR + t] = make_float2(y0, y1);
-            y0 = 0.f; y1 = 0.f;
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+                if (t < MR) part[(((size_t)s * GV_WARPS + warp) * 8 + g) * MR + 4 * nt + t] = make_float2(y0[nt], y1[nt]);
+                y0[nt] = 0.f; y1[nt] = 0.f;
+            }
         }
     } else {
     int R_A = (a + warp) / p.UPR, ku_A = (a + warp) - R_A * p.UPR;
     int R_acc = -1;
     auto flush = [&](int R) {
-        if (t < MR) part[(((size_t)(R - R_first) * GV_WARPS + warp) * 8 + g) * MR + t] = make_float2(y0, y1);
-        y0 = 0.f; y1 = 0.f;
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            if (t < MR) part[(((size_t)(R - R_first) * GV_WARPS + warp) * 8 + g) * MR + 4 * nt + t] = make_float2(y0[nt], y1[nt]);
+            y0[nt] = 0.f; y1[nt] = 0.f;
+        }
     };
     int slot = 0;
     for (int it = 0; it < n_st; ++it) {
@@ -332,7 +353,7 @@ __global__ void __launch_bounds__(GV_THREADS, 2) gemv_imma_kernel(const GemvPara
             if (++slot == DI) slot = 0;
             continue;
         }
-        int accA[MPU][4], accB[MPU][4];
+        int accA[NT][MPU][4], accB[NT][MPU][4];
         unit_mma(wA, xs_l + (uint32_t)ku_A * XU, accA);
         unit_mma(wB, xs_l + (uint32_t)ku_B * XU, accB);
         if (R_acc != R_A) { if (R_acc >= 0) flush(R_acc); R_acc = R_A; }
@@ -454,11 +475,15 @@ struct ImmaPlan {
 static ImmaPlan imma_plan(const Linear &L, int64_t M) {
     ImmaPlan pl{};
     pl.ok = false;
-    if (M < 1 || M > 4 || L.gv_grid <= 0 || !L.gv_tab || !L.gv_aligned) return pl;
+    if (M < 1 || M > 8 || L.gv_grid <= 0 || !L.gv_tab || !L.gv_aligned) return pl;
+    // 5..8 tokens (two IMMA token tiles) is parity-tested but opt-in: every CTA quantises all tokens itself (~1 us per
+    // token on the Qwen3-8B shapes: qkv M=8 14.5 us against 8.3 us for the register-ring kernel).  It becomes the
+    // route once the activation quantisation is hoisted into a pre-kernel.
+    if (M > 4 && !gv_env_int("W4A16_IMMA8", 0)) return pl;
     const int gs = L.d.gs;
     if (gs != 32 && gs != 64 && gs != 128) return pl;               // per-channel scales: the f16 stream kernel
     pl.mpu = 128 / gs;
-    pl.MR = M <= 1 ? 1 : M <= 2 ? 2 : 4;
+    pl.MR = M <= 1 ? 1 : M <= 2 ? 2 : M <= 4 ? 4 : 8;   // 8: two IMMA token tiles, one CTA per SM (activations take 2 K x 8 bytes)
     int64_t off = 128;                                               // full / empty mbarriers
     pl.off_xs = (int)off; off += L.d.K * 2 * pl.MR;                  // two byte planes per token slot
     pl.off_gtab = (int)off; off += (L.d.K / gs) * pl.MR * 8;
@@ -470,7 +495,7 @@ static ImmaPlan imma_plan(const Linear &L, int64_t M) {
     int64_t D = (GV_SMEM_2CTA - off) / depth;
     if (D < 2) D = (GV_SMEM_FULL_SM - off) / depth;                  // large K x M: one CTA per SM
     if (D < 2) return pl;
-    D = std::min<int64_t>(D, std::min<int64_t>(3, gv_env_int("W4A16_GEMV_STAGES", 3)));
+    D = std::min<int64_t>(D, std::min<int64_t>(pl.MR > 4 ? 2 : 3, gv_env_int("W4A16_GEMV_STAGES", 3)));
     if (D < 2) D = 2;
     pl.S = (int)D;
     pl.stage_m_bytes = 0;
@@ -517,7 +542,7 @@ int launch_gemv_imma(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, 
 // peer != null: the epilogue all-reduces the row-parallel partial sums over the peers' symmetric buffers.
 bool gemv_imma_peer_usable(const Linear &L, int64_t M, const PeerView &peer) {
     const ImmaPlan pl = imma_plan(L, M);
-    return pl.ok && peer.world > 1 && peer.world <= PEER_MAX_WORLD && (uint64_t)L.d.N * PEER_TOK <= peer.cap;
+    return pl.ok && pl.MR <= 4 && peer.world > 1 && peer.world <= PEER_MAX_WORLD && (uint64_t)L.d.N * PEER_TOK <= peer.cap;
 }
 
 int launch_gemv_imma_peer(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
@@ -565,6 +590,18 @@ int launch_gemv_imma_peer(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16
         if (pl.mpu == 2) W4_GI2(MR_, 2);                                               \
         W4_GI2(MR_, 4);                                                                \
     } while (0)
+    if (pl.MR == 8) {   // no fused instantiation above 4 tokens (gemv_imma_peer_usable), ring of 2
+        if (peer) return fail("launch_gemv_imma: the fused all-reduce epilogue takes M <= 4");
+#define W4_GI8(MPU_)                                                                   \
+    do {                                                                               \
+        if (reg) return gi_launch_t<8, MPU_, 2, true, false>(p, pl, L.gv_grid, stream, pdl);  \
+        return gi_launch_t<8, MPU_, 2, false, false>(p, pl, L.gv_grid, stream, pdl);   \
+    } while (0)
+        if (pl.mpu == 1) W4_GI8(1);
+        if (pl.mpu == 2) W4_GI8(2);
+        W4_GI8(4);
+#undef W4_GI8
+    }
     switch (pl.MR) {
         case 1: W4_GI(1);
         case 2: W4_GI(2);
