@@ -164,7 +164,12 @@ def run_gpu(args):
     nccl = P.NcclCommunicator(rank, world, local) if world > 1 else None
     peers = None
     if world > 1 and args.fused_ar:   # symmetric NVLink buffers: the row-parallel GEMVs all-reduce in their own epilogue
-        peers = P.PeerGroup(rank, world, local, max(sh[2] for sh in shapes if len(sh) > 3 and sh[3] == "row"))
+        try:
+            peers = P.PeerGroup(rank, world, local, max(sh[2] for sh in shapes if len(sh) > 3 and sh[3] == "row"))
+        except P.W4A16Error as e:   # raised on every rank alike: fall back to ncclAllReduce, and say so in `config`
+            if rank == 0:
+                print(f"bench: peer buffers unavailable ({e}); using ncclAllReduce", file=sys.stderr)
+            peers = None
     layers = build_layers(P, torch, shapes, n_layers, dev, nccl, peers=peers)
 
     xs = {}

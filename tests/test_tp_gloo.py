@@ -64,6 +64,13 @@ def _worker(rank, world, port, out_q):
             raise AssertionError("shard_range accepted an indivisible dimension")
         except ValueError:
             pass
+        # the fused all-reduce's peer buffers need a GPU: without one the collective constructor fails on EVERY rank
+        # alike (no hang, no CPU fallback), so a caller can fall back to NCCL consistently
+        try:
+            P.PeerGroup(rank, world, 0, 1024)
+            raise AssertionError("PeerGroup succeeded without a GPU")
+        except P.W4A16Error as e:
+            assert "PeerGroup" in str(e)
         dist.barrier()
         dist.destroy_process_group()
     except Exception:  # noqa: BLE001

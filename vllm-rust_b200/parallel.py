@@ -128,23 +128,45 @@ class PeerGroup:
     HANDLE_BYTES = 64
 
     def __init__(self, rank: int, world_size: int, device: int, max_out_features: int, group=None):
+        """Collective: every rank of the group must call it.  A failure on ANY rank (no peer access, IPC refused)
+        raises W4A16Error on EVERY rank after the exchange, so callers can fall back to NCCL consistently."""
         import torch.distributed as dist
         self._r, self._w = rank, world_size
         self._peer = ctypes.c_void_p()
-        with torch.cuda.device(device):
-            check(lib().w4a16_peer_create(ctypes.byref(self._peer), rank, world_size, int(max_out_features) * 4))
-            raw = (ctypes.c_char * self.HANDLE_BYTES)()
-            check(lib().w4a16_peer_export(self._peer, ctypes.cast(raw, ctypes.c_void_p)))
-            mine = torch.frombuffer(bytearray(raw.raw), dtype=torch.uint8).clone()
-            on_gpu = dist.get_backend(group) == "nccl"
+        on_gpu = dist.get_backend(group) == "nccl"
+
+        def gather(payload: bytes):
+            mine = torch.frombuffer(bytearray(payload), dtype=torch.uint8).clone()
             if on_gpu:
                 mine = mine.cuda(device)
-            gathered = [torch.empty_like(mine) for _ in range(world_size)]
-            dist.all_gather(gathered, mine, group=group)
-            blob = b"".join(bytes(t.cpu().tolist()) for t in gathered)
-            buf = (ctypes.c_char * len(blob)).from_buffer_copy(blob)
-            check(lib().w4a16_peer_attach(self._peer, ctypes.cast(buf, ctypes.c_void_p)))
-            dist.barrier(group=group)   # nobody launches before every rank has mapped every buffer
+            out = [torch.empty_like(mine) for _ in range(world_size)]
+            dist.all_gather(out, mine, group=group)
+            return [bytes(t.cpu().tolist()) for t in out]
+
+        import contextlib
+        with (torch.cuda.device(device) if torch.cuda.is_available() else contextlib.nullcontext()):
+            err = ""
+            raw = (ctypes.c_char * self.HANDLE_BYTES)()
+            try:
+                check(lib().w4a16_peer_create(ctypes.byref(self._peer), rank, world_size, int(max_out_features) * 4))
+                check(lib().w4a16_peer_export(self._peer, ctypes.cast(raw, ctypes.c_void_p)))
+            except W4A16Error as e:
+                err = str(e) or "peer_create failed"
+            got = gather(bytes(raw.raw) + (b"\x01" if err else b"\x00"))
+            if not err and not any(g[-1] for g in got):
+                blob = b"".join(g[:self.HANDLE_BYTES] for g in got)
+                buf = (ctypes.c_char * len(blob)).from_buffer_copy(blob)
+                try:
+                    check(lib().w4a16_peer_attach(self._peer, ctypes.cast(buf, ctypes.c_void_p)))
+                except W4A16Error as e:
+                    err = str(e) or "peer_attach failed"
+            elif not err:
+                err = "a peer rank could not create its buffer"
+            # second exchange doubles as the barrier: nobody launches before every rank has mapped every buffer
+            bad = [i for i, g in enumerate(gather(b"\x01" if err else b"\x00")) if g[0]]
+            if bad:
+                self.destroy()
+                raise W4A16Error(f"PeerGroup: ranks {bad} failed ({err or 'see those ranks'})")
 
     def ptr(self) -> Optional[int]:
         return self._peer.value
