@@ -35,7 +35,7 @@ def _worker(rank, world, port, out_q):
         from oracle import oracle as O
         from helpers import awq_unpacked, oracle_forward, assert_close_ref, t_bf16_from_bits, bits_of, t_i32
         dev = torch.device("cuda", rank)
-        K, N, g = 2048, 4096, 128
+        K, N, g = 4096, 4096, 128   # K / 8 = 512 per rank at world 8: still whole groups
         qweight, qzeros, scales, b = O.make_awq_checkpoint(K, N, g, seed=31, bias=True)   # same on every rank
         q, z, sb = awq_unpacked(qweight, qzeros, scales)
         bias = O.np_bf16_round(b)
@@ -60,7 +60,13 @@ def _worker(rank, world, port, out_q):
             y2 = torch.empty((M, N), dtype=torch.bfloat16, device=dev)
             plain.forward_into(x, y2)
             torch.cuda.synchronize()
-            assert_close_ref(bits_of(y2), want, f"nccl rank {rank} M={M}")
+            # the NCCL path rounds every rank's partial sum to bf16 and reduces in bf16 (the reference's semantics,
+            # nccl.rs:1338-1364): its error grows with the world size, so beyond 2 ranks it is held to 2e-2, not 1e-2
+            if world <= 2:
+                assert_close_ref(bits_of(y2), want, f"nccl rank {rank} M={M}")
+            else:
+                err2 = np.abs(O.np_bf16_bits_to_f32(bits_of(y2)).astype(np.float64) - want).max()
+                assert err2 <= 2e-2 * np.abs(want).max(), f"nccl rank {rank} M={M}: {err2}"
             # every rank holds bit-identical results (sources are summed in rank order everywhere)
             ys = [torch.empty_like(y) for _ in range(world)]
             dist.all_gather(ys, y)
@@ -104,9 +110,14 @@ def _worker(rank, world, port, out_q):
     out_q.put((rank, None))
 
 
-@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs two GPUs")
-def test_fused_row_parallel_allreduce_two_ranks():
-    world = 2
+def _n_gpus():
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_fused_row_parallel_allreduce_real_ranks(world):
+    if _n_gpus() < world:
+        pytest.skip(f"needs {world} GPUs")
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
