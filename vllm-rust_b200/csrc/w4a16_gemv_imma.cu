@@ -189,10 +189,27 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 4 ? 2 : 1) gemv_imma_kernel(
                     uint32_t hiP[4], loP[4];
 #pragma unroll
                     for (int q = 0; q < 4; ++q) { hiP[q] = (pk[q] >> 7) & 0x00FF00FFu; loP[q] = pk[q] & 0x007F007Fu; }
-                    *reinterpret_cast<uint32_t *>(dst) = hiP[0] | (hiP[1] << 8);
-                    *reinterpret_cast<uint32_t *>(dst + 8) = loP[0] | (loP[1] << 8);
-                    *reinterpret_cast<uint32_t *>(dst + COLS * 8) = hiP[2] | (hiP[3] << 8);
-                    *reinterpret_cast<uint32_t *>(dst + COLS * 8 + 8) = loP[2] | (loP[3] << 8);
+                    uint32_t v0 = hiP[0] | (hiP[1] << 8), v1 = loP[0] | (loP[1] << 8);      // -> dst, dst + 8
+                    uint32_t v2 = hiP[2] | (hiP[3] << 8), v3 = loP[2] | (loP[3] << 8);      // -> dst + COLS*8, dst + COLS*8 + 8
+                    if constexpr (MR >= 2) {
+                        // All 32 pieces of a warp land in rows that are multiples of 128 B apart: issued in the same
+                        // order, each of the four stores is a 16-way bank conflict (~2 us per CTA at 4 tokens).  Lanes
+                        // rotate the order of their four stores by (lane >> 2) & 3, which spreads them over 4x the banks.
+                        const int rot = (lane >> 2) & 3;
+                        if (rot & 1) { const uint32_t tv = v0; v0 = v1; v1 = v2; v2 = v3; v3 = tv; }
+                        if (rot & 2) { uint32_t tv = v0; v0 = v2; v2 = tv; tv = v1; v1 = v3; v3 = tv; }
+                        const uint32_t vv[4] = {v0, v1, v2, v3};
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const int idx = (k + rot) & 3;                                  // which of the four slots vv[k] is
+                            *reinterpret_cast<uint32_t *>(dst + (idx & 1) * 8 + (idx >> 1) * (COLS * 8)) = vv[k];
+                        }
+                    } else {
+                        *reinterpret_cast<uint32_t *>(dst) = v0;
+                        *reinterpret_cast<uint32_t *>(dst + 8) = v1;
+                        *reinterpret_cast<uint32_t *>(dst + COLS * 8) = v2;
+                        *reinterpret_cast<uint32_t *>(dst + COLS * 8 + 8) = v3;
+                    }
                     if ((c & (GL - 1)) == 0) gtab[(size_t)(c / GL) * MR + m] = make_int2(sum, (E - 13) << 23);
                 }
             }
