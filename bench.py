@@ -256,6 +256,10 @@ def run_gpu(args):
     elif rank == 0:
         out["e2e"] = {"value": None, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
                       "note": "host-buffer path measured at N=1 only"}
+    if world > 1 and not args.quick:
+        pf = prefill_tp(torch, dist, dev, layers[:len(shapes)], peaks, world)   # every rank takes part (all-reduce inside)
+        if rank == 0:
+            out["prefill_tp"] = pf
     if rank == 0:
         print(json.dumps(out))
     if world > 1:
@@ -352,6 +356,38 @@ def prefill_point(P, torch, dev, peaks, args):
             "M4096_frac_measured_bf16": round(agg / peaks["bf16_tflops"], 4) if agg else None,
             "M4096_frac_spec_2250": round(agg / 2250.0, 4) if agg else None, "peak": peaks["bf16_tflops"],
             "points": rows}
+
+
+def prefill_tp(torch, dist, dev, layer, peaks, world, M=4096, reps=5):
+    """BASELINE config 5 at M=4096: one Llama-3-70B-shaped layer (qkv, o, gate_up, down), tensor-parallel; the
+    row-parallel o / down finish with ncclAllReduce of the [M, 8192] bf16 output (64 MB).  Device time, max over ranks."""
+    bufs = []
+    for name, K, N, Kl, Nl, mode, lin in layer:
+        bufs.append((torch.randn((M, Kl), device=dev).to(torch.bfloat16), torch.empty((M, Nl), device=dev, dtype=torch.bfloat16)))
+    rows = []
+    tot_ms, tot_flops = 0.0, 0.0
+    for (name, K, N, Kl, Nl, mode, lin), (x, y) in zip(layer, bufs):
+        for _ in range(2):
+            lin.forward_into(x, y)
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            lin.forward_into(x, y)
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / reps], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        flops = 2.0 * M * K * N          # whole-job (unsharded) flops
+        tot_ms += ms
+        tot_flops += flops
+        rows.append({"shape": f"{name} {K}->{N}", "mode": mode, "ms": round(ms, 4), "TFLOPS": round(flops / (ms * 1e-3) / 1e12, 1)})
+    agg = tot_flops / (tot_ms * 1e-3) / 1e12
+    return {"M": M, "TFLOPS": round(agg, 1), "TFLOPS_per_gpu": round(agg / world, 1),
+            "frac_measured_bf16_per_gpu": round(agg / world / peaks["bf16_tflops"], 4), "points": rows,
+            "allreduce": "ncclAllReduce (bf16, M x 8192) after the row-parallel GEMMs"}
 
 
 def e2e_host(P, torch, dev, layers, args):
