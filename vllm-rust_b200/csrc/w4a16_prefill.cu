@@ -494,17 +494,23 @@ int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
     {
         const int kblks = (int)(L.d.K / PF_BLOCK_K), nm = p.n_tiles * p.m_tiles, sms = L.scratch->sm_count;
         // Cost model in units of one 64-k block of one CTA (~0.35 us: the TS-mode MMA chain): waves x (blocks per
-        // slice + a fixed per-slice cost: pipeline fill, fp32 partial write, ticket, the last slice's re-read).
+        // slice + a fixed per-slice cost: pipeline fill, fp32 partial write, ticket) + the last slice's re-read of all
+        // partials of its tile, which is latency-bound on 128 threads: ~0.06 units per (slice x token row), fitted to
+        // qkv / o at M = 64 (split wins by 8-11 us), M = 128 (by ~4 us) and M = 256 (split LOSES 9-14 us).
         int ks = 1;
         {
             static const int forced = getenv("W4A16_PF_KSPLIT") ? atoi(getenv("W4A16_PF_KSPLIT")) : 0;
-            static const int c_fix = getenv("W4A16_PF_KSPLIT_FIX") ? atoi(getenv("W4A16_PF_KSPLIT_FIX")) : 10;
+            static const int c_fix = getenv("W4A16_PF_KSPLIT_FIX") ? atoi(getenv("W4A16_PF_KSPLIT_FIX")) : 6;
+            static const double c_row = getenv("W4A16_PF_KSPLIT_ROW") ? atof(getenv("W4A16_PF_KSPLIT_ROW")) : 0.06;
+            const int rows = (int)std::min<int64_t>(M, TM);
             const int cands[6] = {1, 2, 3, 4, 6, 8};
-            long best = -1;
+            double best = -1;
             for (int c : cands) {
                 if (kblks % (2 * c) != 0 || kblks / c < 8) continue;      // a slice keeps an even number of k blocks
                 const long waves = ((long)nm * c + sms - 1) / sms;
-                const long cost = waves * (kblks / c + (c > 1 ? c_fix + TM / 16 : 0));
+                // every split tile writes its fp32 partial (~ rows); the tile that arrives last re-reads c of them
+                const double cost = c == 1 ? (double)waves * kblks
+                                           : (double)waves * (kblks / c + c_fix + c_row * rows) + c_row * c * rows;
                 if (best < 0 || cost < best) { best = cost; ks = c; }
             }
             if (forced > 0 && kblks % (2 * forced) == 0) ks = forced;
