@@ -95,12 +95,22 @@ int w4a16_load_awq(w4a16_handle_t h, const uint32_t *qweight /*[K,N/8]*/,
  * permutation at load plus an activation gather at forward.  (The reference loads
  * g_idx and never uses it: gptq.rs:349-366, marlin_gemm.cu:79-83.)  g_idx must
  * assign exactly group_size rows to every group.  g_idx is read on the HOST side
- * of the call (it synchronises `stream` once, at load).                       */
+ * of the call (it synchronises `stream` once, at load).
+ * ROW shards: the rows are sorted by group over the FULL K and then
+ * sharded, so rank r keeps whole groups; its forward expects x already in that
+ * order (w4a16_row_perm gives it) -- there is no gather inside a ROW shard.   */
 int w4a16_load_gptq(w4a16_handle_t h, const uint32_t *qweight /*[K/8,N]*/,
                     const uint32_t *qzeros /*[G,N/8] or NULL for GPTQ_SYM*/,
                     const void *scales /*[G,N]*/, int scales_dtype,
                     const int32_t *g_idx /*[K] device, or NULL*/, const void *bias, int bias_dtype,
                     w4a16_stream_t stream);
+
+/* Call-order hint: `next` is the linear the caller runs right after `h` (the reference's model code calls its
+ * linears in a fixed order per layer: qkv, o, gate/up, down -- qwen3_quantized.rs:532-551, 704-709).  The decode
+ * kernel of `h` then requests `next`'s weight stream into L2 while it works, so HBM stays busy across the launch
+ * boundary.  A hint only: results never depend on it; NULL clears it; `next` may be destroyed first (the hint is
+ * dropped).  Both handles must live on the same device.                       */
+int w4a16_set_next(w4a16_handle_t h, w4a16_handle_t next);
 
 /* -- forward ----------------------------------------------------------------
  * QuantizedLinear::forward(&Tensor) (config.rs:149) as it is executed by
@@ -110,7 +120,14 @@ int w4a16_load_gptq(w4a16_handle_t h, const uint32_t *qweight /*[K/8,N]*/,
  * x: [M, K_local] bf16, contiguous, 16-byte aligned.  y: [M, N_local] bf16; every
  * element is written, no zero-init needed (marlin_cuda.rs:431-440).  Leading
  * dims are flattened by the caller (awq_marlin.rs:545-571).  M >= 1.
- * For a ROW shard y is the rank's partial sum WITHOUT bias.                   */
+ * For a ROW shard y is the rank's partial sum WITHOUT bias.
+ * Non-finite activations: an Inf or NaN anywhere in a token's row makes that token's
+ * outputs non-finite, as the reference's fp32 FMA chain does (awq_gemv.cu:597-664).
+ * The M <= 4 kernels, which round activations to per-group scaled integers, return NaN
+ * for every output of such a token (the reference may return +-Inf for some of them);
+ * other tokens of the batch are unaffected.  Finite inputs: |x| down to 2^-6 of its
+ * group's largest magnitude is exact, smaller ones carry an absolute error of at most
+ * 2^-14 of that magnitude (tests/test_parity_gpu.py::test_imma_*).            */
 int w4a16_forward_into(w4a16_handle_t h, const void *x_bf16, void *y_bf16, int64_t M,
                        w4a16_stream_t stream);
 
@@ -128,10 +145,12 @@ int w4a16_forward_row_allreduce(w4a16_handle_t h, const void *x_bf16, void *y_bf
 
 /* Fused row-parallel forward for decode sizes: replaces the ncclAllReduce of
  * RowParallelLinear::forward (parallel_layers.rs:295-304, nccl.rs:1338-1364) and the dormant
- * kernels/custom_allreduce.cu.  Every rank owns one symmetric buffer; the GEMV's epilogue stores
- * its fp32 partial sums into every peer's buffer over NVLink (P2P stores), publishes a per-CTA
- * epoch flag, waits for the peers' flags and sums the world's partials in rank order (+ bias).
- * One kernel, no NCCL launch; results are bit-identical on every rank.
+ * kernels/custom_allreduce.cu.  Every rank owns one symmetric buffer of fp32 words that hold a sentinel
+ * (-0.0f) when empty; the GEMV's epilogue stores its fp32 partial sums into every peer's buffer over
+ * NVLink (P2P stores), polls its own buffer until every source's word has arrived (the data words are
+ * their own flags: no fence, no flag round trip), sums the world's partials in rank order (+ bias) and
+ * puts the sentinel back.  One kernel, no NCCL launch; results are bit-identical on every rank.  One
+ * peer group serves row-parallel linears of different N and M (every launch leaves its buffer clean).
  *   peer_create : allocate this rank's buffer on the current device (max_partial_floats >=
  *                 N_out * 4 of the largest row-parallel linear);
  *   peer_export : 64-byte IPC handle of the buffer (HOST memory), to be all-gathered out of band;
@@ -169,6 +188,16 @@ int w4a16_reserve(w4a16_handle_t h, int64_t max_tokens);
  * unpack: q as one byte per nibble [K_local, N_local], z [G_local, N_local].
  * scales: the resident bf16 scales [G_local, N_local].                        */
 int w4a16_dequant_into(w4a16_handle_t h, void *w_bf16, w4a16_stream_t stream);
+/* The reference's other grid ("D1", awq_dequantize_cpu, awq.rs:56-166): f16_rn(f32(q - z) * f32(scale)) with the
+ * checkpoint's ORIGINAL scales (the resident layout keeps only their bf16 rounding, awq_marlin.rs:649-656, so the
+ * checkpoint's [G,N] scales tensor is passed again; device pointer, full/unsharded like at load).  out: dense
+ * [K_local, N_local] f16.  A parity hook: no kernel computes on this grid.   */
+int w4a16_dequant_d1_into(w4a16_handle_t h, const void *scales, int scales_dtype, void *w_f16,
+                          w4a16_stream_t stream);
+/* Checkpoint row held by every local (tiled) row: identity + k_off without act-order.  For an act-order ROW
+ * shard this is the slice of the global sort-by-group permutation the shard was cut from, and the order in which
+ * the caller must present the shard's x columns (x_local[:, i] = x_full[:, perm[i]]).  perm_out: HOST, K_local. */
+int w4a16_row_perm(w4a16_handle_t h, int32_t *perm_out_host);
 int w4a16_unpack_into(w4a16_handle_t h, uint8_t *q, uint8_t *z, w4a16_stream_t stream);
 int w4a16_scales_into(w4a16_handle_t h, void *scales_bf16, w4a16_stream_t stream);
 

@@ -235,15 +235,21 @@ def test_config_1_2_shapes_m1(product, K, N):
     assert_close_ref(run_forward(lin, xb), oracle_forward(xb, q, z, sb, g), f"{K}x{N}")
 
 
-@pytest.mark.parametrize("M", [1, 8, 64, 256])
-@pytest.mark.parametrize("K,N", [(2560, 6144), (4096, 2560), (9728, 2560)])
+_cfg4 = {}
+
+
+@pytest.mark.parametrize("M", [1, 2, 4, 8, 16, 32, 64, 128, 256])
+@pytest.mark.parametrize("K,N", [(2560, 6144), (4096, 2560), (2560, 19456), (9728, 2560)])
 def test_config_4_gptq_act_order(product, M, K, N):
+    """BASELINE config 4: Qwen3-4B GPTQ int4 with act-order g_idx, all four shapes, the whole M list."""
     g = 128
-    qweight, qzeros, scales, g_idx = O.make_gptq_checkpoint(K, N, g, seed=K + M, act_order=True)
-    lin = product.GptqConfig(4, g, desc_act=True).create_linear(K, N, False, DEV)
-    lin.load_weights({"qweight": t_i32(qweight), "qzeros": t_i32(qzeros), "scales": torch.from_numpy(scales),
-                      "g_idx": torch.from_numpy(g_idx)})
-    q, z, sb = gptq_unpacked(qweight, qzeros, scales)
+    if _cfg4.get("key") != (K, N):   # one checkpoint per shape (the shape parameter is the slow axis)
+        qweight, qzeros, scales, g_idx = O.make_gptq_checkpoint(K, N, g, seed=K + N, act_order=True)
+        lin = product.GptqConfig(4, g, desc_act=True).create_linear(K, N, False, DEV)
+        lin.load_weights({"qweight": t_i32(qweight), "qzeros": t_i32(qzeros), "scales": torch.from_numpy(scales),
+                          "g_idx": torch.from_numpy(g_idx)})
+        _cfg4["key"], _cfg4["val"] = (K, N), (lin, gptq_unpacked(qweight, qzeros, scales), g_idx)
+    lin, (q, z, sb), g_idx = _cfg4["val"]
     xb = O.make_activations(M, K, seed=M)
     assert_close_ref(run_forward(lin, xb), oracle_forward(xb, q, z, sb, g, g_idx=g_idx), f"act-order {K}x{N} M={M}")
 
@@ -368,3 +374,110 @@ def test_prefill_split_k_few_tiles(product, M, K, N):
     first = run_forward(lin, xb)
     assert_close_ref(first, want, f"split-K {K}x{N} M={M}")
     assert (run_forward(lin, xb) == first).all(), "split-K result is not deterministic across launches"
+
+
+# ---- the integer-activation decode kernels (M <= 4): where their arithmetic differs from the reference's ----------
+# gemv_imma_kernel rounds activations to 14-bit integers with one power-of-two scale per (group, token)
+# (w4a16_gemv_imma.cu); the reference multiplies exact bf16 activations in fp32 (awq_gemv.cu:597-664).
+def _imma_case(product, K, N, g, xb, what, seed=77):
+    lin, (qweight, qzeros, scales, _) = make_awq_layer(product, K, N, g, seed=seed)
+    q, z, sb = awq_unpacked(qweight, qzeros, scales)
+    M = xb.shape[0]
+    assert lin.kernel_for(M) in ("gemv_stream_imma", "gemv_stream_dp4a", "gemv_stream_nt1"), lin.kernel_for(M)
+    return lin, run_forward(lin, xb), oracle_forward(xb, q, z, sb, g)
+
+
+@pytest.mark.parametrize("M", [1, 4])
+@pytest.mark.parametrize("K,N,g", [(4096, 4096, 128), (2048, 4736, 32)])
+def test_imma_outlier_per_group(product, M, K, N, g):
+    """Every group holds ONE element 2^10 times larger than its 127 (31) small same-sign neighbours: the small ones
+    are rounded to ~4 significant bits by the group's scale -- the worst case of the 2^-14 bound in the header."""
+    rng = np.random.default_rng(K + M)
+    x = np.full((M, K), 0.0123, np.float32) * rng.uniform(0.5, 1.0, size=(M, K)).astype(np.float32)
+    for m in range(M):
+        pos = rng.integers(0, g, size=K // g) + np.arange(K // g) * g
+        x[m, pos] *= 1024.0
+    xb = O.np_f32_to_bf16_bits(x)
+    _, got, want = _imma_case(product, K, N, g, xb, "outlier")
+    assert_close_ref(got, want, f"outlier M={M} g={g}")
+
+
+@pytest.mark.parametrize("M", [1, 3])
+def test_imma_zero_groups_zero_tokens_and_subnormals(product, M):
+    K, N, g = 4096, 4096, 128
+    xb = O.make_activations(M, K, seed=5)
+    xb[:, 256:512] = 0                       # two all-zero groups in every token
+    xb[:, 1024:1152] = 0x8000                # a group of negative zeros
+    xb[:, 2048:2176] = (np.arange(128) % 127 + 1).astype(np.uint16)[None, :]   # a group of bf16 subnormals
+    xb[:, 3000] = 0x0001                     # a subnormal next to normal values
+    if M > 1:
+        xb[M - 1, :] = 0                     # a whole token of zeros -> exactly zero outputs
+    _, got, want = _imma_case(product, K, N, g, xb, "zeros")
+    assert_close_ref(got, want, f"zeros/subnormals M={M}")
+    if M > 1:
+        assert (got[M - 1] & 0x7FFF == 0).all(), "a zero token must give zero outputs"
+
+
+@pytest.mark.parametrize("M", [1, 4, 8, 64])
+def test_non_finite_activations_propagate(product, M):
+    """Policy (include/w4a16_b200.h, w4a16_forward_into): a token holding Inf / NaN gets non-finite outputs, as the
+    reference's fp32 FMA chain gives it; the other tokens of the batch are untouched.  M = 1, 4: the integer-activation
+    kernels (NaN for the whole token); M = 8, 64: the bf16 mma kernels."""
+    K, N, g = 4096, 4096, 128
+    lin, (qweight, qzeros, scales, _) = make_awq_layer(product, K, N, g, seed=31)
+    q, z, sb = awq_unpacked(qweight, qzeros, scales)
+    xb = O.make_activations(M, K, seed=9)
+    clean = xb.copy()
+    bad = {0: 0x7F80} if M == 1 else {1: 0x7F80, 2: 0x7FC0, M - 1: 0xFF80}   # +Inf, NaN, -Inf
+    for m, bits in bad.items():
+        xb[m, 777 + m] = bits
+    got = O.np_bf16_bits_to_f32(run_forward(lin, xb))
+    want_clean = oracle_forward(clean, q, z, sb, g)
+    for m in range(M):
+        if m in bad:
+            assert not np.isfinite(got[m]).any(), f"token {m} holds a non-finite activation: every output must be non-finite"
+        else:
+            err = np.abs(got[m] - want_clean[m]).max()
+            assert err <= 1e-2 * np.abs(want_clean).max(), f"clean token {m} disturbed by a neighbour's Inf/NaN: {err}"
+
+
+# ---- D1: the reference's CPU dequant grid (awq_dequantize_cpu, awq.rs:56-166) ------------------------------------------
+@pytest.mark.parametrize("K,N,g", [(256, 128, 128), (512, 192, 64), (1024, 6144, 128)])
+def test_d1_grid_matches_awq_dequantize_cpu_bit_exact(product, K, N, g):
+    """f16_rn(f32(q - z) * f32(f16 scale)) with the checkpoint's ORIGINAL scales: a different grid from D2 (bf16-rounded
+    scales, bf16 result); SURVEY 8a hazard (i) asks for both to be exposed."""
+    lin, (qweight, qzeros, scales, _) = make_awq_layer(product, K, N, g, seed=K + 3 * N)
+    want = O.C.awq_dequantize_cpu(qweight, np.asarray(scales, np.float32), qzeros, g, K, N)   # f16 bits [K, N]
+    got = lin.dequantize_d1(torch.from_numpy(scales)).cpu().view(torch.int16).numpy().view(np.uint16)
+    want_bits = np.asarray(want).view(np.uint16) if np.asarray(want).dtype != np.uint16 else np.asarray(want)
+    assert (got == want_bits.reshape(K, N)).all(), "D1 grid differs from awq_dequantize_cpu"
+    d2 = O.np_bf16_bits_to_f32(bits_of(lin.dequantize()))
+    d1 = got.view(np.float16).astype(np.float32)
+    assert np.abs(d1 - d2).max() > 0, "D1 and D2 are different grids (f16 vs bf16 scales): they cannot coincide everywhere"
+
+
+# ---- act-order + row-parallel: global K permutation before sharding (SURVEY 8e) ------------------------------------------
+@pytest.mark.parametrize("tp", [2, 4])
+def test_act_order_row_shards_compose(product, tp):
+    K, N, g, M = 2048, 256, 128, 3
+    qweight, qzeros, scales, g_idx = O.make_gptq_checkpoint(K, N, g, seed=tp + 40, act_order=True)
+    w = {"qweight": t_i32(qweight), "qzeros": t_i32(qzeros), "scales": torch.from_numpy(scales), "g_idx": torch.from_numpy(g_idx)}
+    q, z, sb = gptq_unpacked(qweight, qzeros, scales)
+    xb = O.make_activations(M, K, seed=4)
+    x = t_bf16_from_bits(xb).to(DEV)
+    want = oracle_forward(xb, q, z, sb, g, g_idx=g_idx)
+    cfg = product.GptqConfig(4, g, desc_act=True)
+    acc = np.zeros((M, N), np.float64)
+    seen = []
+    for r in range(tp):
+        sh = cfg.create_linear(K, N, False, DEV, tp_mode=2, tp_rank=r, tp_size=tp)
+        sh.load_weights(w)
+        perm = sh.row_perm().numpy()
+        assert perm.shape == (K // tp,)
+        assert (np.sort(g_idx[perm]) == np.repeat(np.arange(r * K // tp // g, (r + 1) * K // tp // g), g)).all(), \
+            "a row shard must hold whole groups of the globally sorted order"
+        seen.append(perm)
+        part = bits_of(sh.forward(x[:, torch.from_numpy(perm.astype(np.int64)).to(DEV)].contiguous()))
+        acc += O.np_bf16_bits_to_f32(part)
+    assert (np.sort(np.concatenate(seen)) == np.arange(K)).all(), "the shards' rows must partition K"
+    assert np.abs(acc - want).max() <= O.reference_tolerance(want)

@@ -92,6 +92,28 @@ def _worker(rank, world, port, out_q):
                 st.synchronize()
                 assert_close_ref(bits_of(y), want, f"graph replay rank {rank}")
         dist.barrier()
+        # ONE PeerGroup shared by row-parallel linears of different N and M, interleaved big, small, small (period 3 =
+        # the buffer rotation: the big linear always lands on the same buffer and only small launches run between
+        # its uses -- stale words of rows [N_small, N_big) would be summed silently if a launch left any behind)
+        Nb = 8192
+        peers2 = P.PeerGroup(rank, world, rank, Nb)
+        qwb, qzb, scb, _ = O.make_awq_checkpoint(K, Nb, g, seed=32)
+        qb_, zb_, sbb = awq_unpacked(qwb, qzb, scb)
+        big = P.RowParallelW4A16Linear(cfg, K, Nb, False, comm, dev, peers=peers2)
+        big.load_weights({"qweight": t_i32(qwb).to(dev), "qzeros": t_i32(qzb).to(dev), "scales": torch.from_numpy(scb).to(dev)})
+        small = P.RowParallelW4A16Linear(cfg, K, N, True, comm, dev, peers=peers2)
+        small.load_weights(w)
+        for it in range(9):
+            for lin, (qq, zz, ss, bb, nn), M in ((big, (qb_, zb_, sbb, None, Nb), 4 if it % 2 else 1),
+                                                 (small, (q, z, sb, bias, N), 2), (small, (q, z, sb, bias, N), 1)):
+                xb = O.make_activations(M, K, seed=300 + 3 * it + M)
+                x = t_bf16_from_bits(np.ascontiguousarray(xb[:, k0:k1])).to(dev)
+                y = torch.full((M, nn), float("nan"), dtype=torch.bfloat16, device=dev)
+                lin.forward_into(x, y)
+                torch.cuda.synchronize()
+                assert_close_ref(bits_of(y), oracle_forward(xb, qq, zz, ss, g, bias_f32=bb), f"shared group it={it} N={nn} M={M}")
+        dist.barrier()
+        peers2.destroy()
         # M > 4 falls back to the NCCL path inside the same entry point
         xb = O.make_activations(8, K, seed=99)
         x = t_bf16_from_bits(np.ascontiguousarray(xb[:, k0:k1])).to(dev)
@@ -125,7 +147,7 @@ def test_fused_row_parallel_allreduce_real_ranks(world):
     for p in procs:
         p.start()
     try:
-        results = [q.get(timeout=150) for _ in range(world)]
+        results = [q.get(timeout=240) for _ in range(world)]
     finally:
         for p in procs:
             p.join(timeout=30)

@@ -9,7 +9,8 @@ from .quantization import (  # noqa: F401
     AwqConfig, AwqMarlinConfig, GptqConfig, MarlinConfig, MarlinScalarType,
     B200W4A16Linear, check_marlin_supports_shape,
     AwqWeightLoader, GptqWeightLoader, create_weight_loader_with_params,
-    detect_from_json, create_config, kernel_launches, set_dispatch,
+    detect_from_json, detect_from_directory, is_supported, create_config, kernel_launches, set_dispatch,
+    DetectedQuantConfig,
 )
 from .parallel import (  # noqa: F401
     DeviceCommunicator, MockCommunicator, NcclCommunicator, PeerGroup, TorchDistCommunicator,

@@ -80,8 +80,24 @@ struct DeviceGuard {
     }
 };
 
+// Live handles: w4a16_set_next stores a raw pointer to another handle, which the caller may destroy first.
+static std::mutex g_live_mu;
+static std::vector<const Linear *> g_live;
+static void live_add(const Linear *L) { std::lock_guard<std::mutex> lk(g_live_mu); g_live.push_back(L); }
+static void live_del(const Linear *L) {
+    std::lock_guard<std::mutex> lk(g_live_mu);
+    g_live.erase(std::remove(g_live.begin(), g_live.end(), L), g_live.end());
+}
+const Linear *linear_next(const Linear *L) {
+    const Linear *n = L->next;
+    if (!n) return nullptr;
+    std::lock_guard<std::mutex> lk(g_live_mu);
+    return std::find(g_live.begin(), g_live.end(), n) != g_live.end() ? n : nullptr;
+}
+
 static void free_linear(Linear *L) {
     if (!L) return;
+    live_del(L);
     DeviceGuard g(L->device);
     cudaFree(L->qw); cudaFree(L->meta); cudaFree(L->bias); cudaFree(L->perm); cudaFree(L->tickets);
     cudaFree(L->splitk_scratch); cudaFree(L->x_gather); cudaFree(L->stage_x); cudaFree(L->stage_y);
@@ -152,7 +168,7 @@ static int ensure_stage(Linear *L, int64_t M) {
     return 0;
 }
 static int ensure_gather(Linear *L, int64_t M) {
-    if (!L->perm || M <= L->x_gather_cap) return 0;
+    if (!L->perm || L->perm_external || M <= L->x_gather_cap) return 0;
     cudaFree(L->x_gather);
     L->x_gather = nullptr; L->x_gather_cap = 0;
     W4_CUDA_OK(cudaMalloc(&L->x_gather, (size_t)M * L->d.K * 2));
@@ -182,7 +198,7 @@ static int forward_local(Linear *L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
     if (!x || !y) return fail("forward: null x or y");
     if ((reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(y) & 15))
         return fail("forward: x and y must be 16-byte aligned");
-    if (L->perm) {  // act-order: tiled row i multiplies x[:, perm[i]]
+    if (L->perm && !L->perm_external) {  // act-order: tiled row i multiplies x[:, perm[i]]
         if (ensure_gather(L, M)) return 1;
         if (launch_gather_x(x, L->perm, L->x_gather, M, L->d.K, stream)) return 1;
         x = L->x_gather;
@@ -259,7 +275,17 @@ int w4a16_create_shard(w4a16_handle_t *out, int64_t in_features, int64_t out_fea
     if (sf > 0) { W4_ALLOC(L->splitk_scratch, (size_t)sf * 4); L->splitk_floats = sf; }
 #undef W4_ALLOC
     if (gemv_build_table(*L, ds->sm_count) || gemv_umma_build_table(*L, ds->sm_count)) { free_linear(L); return 1; }
+    live_add(L);
     *out = reinterpret_cast<w4a16_handle_t>(L);
+    return 0;
+}
+
+int w4a16_set_next(w4a16_handle_t h, w4a16_handle_t next) {
+    Linear *L = reinterpret_cast<Linear *>(h);
+    if (!L) return fail("set_next: null handle");
+    Linear *nx = reinterpret_cast<Linear *>(next);
+    if (nx && nx->device != L->device) return fail("set_next: the next handle lives on another device");
+    L->next = nx;
     return 0;
 }
 
@@ -313,35 +339,41 @@ int w4a16_load_gptq(w4a16_handle_t h, const uint32_t *qweight, const uint32_t *q
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     const int32_t *perm_dev = nullptr, *grp_dev = nullptr;
     if (g_idx) {
-        if (L->tp_mode == W4A16_TP_ROW)
-            return fail("load_gptq: act-order (g_idx) with a ROW shard needs a global K permutation before sharding; not supported");
-        const int64_t K = L->d.K;
+        // g_idx is the FULL [K_full] tensor.  The rows are sorted by group over the whole K (stable), THEN sharded
+        // ("permute at load before sharding"): a ROW shard keeps sorted rows [k_off, k_off + K_local), i.e.
+        // whole groups [k_off / gs, ...), and expects its x columns in that order (perm_external: no gather at
+        // forward; w4a16_row_perm hands the permutation to the caller, who folds it into the producing layer).
+        const int64_t Kf = L->K_full, K = L->d.K;
         const int gs = L->d.gs;
-        const int64_t G = L->d.G;
-        std::vector<int32_t> gi((size_t)K);
-        W4_CUDA_OK(cudaMemcpyAsync(gi.data(), g_idx, (size_t)K * 4, cudaMemcpyDeviceToHost, s));
+        const int64_t Gf = Kf / gs, G = L->d.G;
+        std::vector<int32_t> gi((size_t)Kf);
+        W4_CUDA_OK(cudaMemcpyAsync(gi.data(), g_idx, (size_t)Kf * 4, cudaMemcpyDeviceToHost, s));
         W4_CUDA_OK(cudaStreamSynchronize(s));
         bool trivial = true;
-        for (int64_t k = 0; k < K; ++k) {
-            if (gi[k] < 0 || gi[k] >= G) return fail("load_gptq: g_idx entry out of range");
+        for (int64_t k = 0; k < Kf; ++k) {
+            if (gi[k] < 0 || gi[k] >= Gf) return fail("load_gptq: g_idx entry out of range");
             if (gi[k] != k / gs) trivial = false;
         }
         if (!trivial) {
-            // stable sort of the rows by group: tiled row i <- checkpoint row perm[i]
-            std::vector<int32_t> perm((size_t)K + (size_t)G);
-            std::vector<int64_t> count((size_t)G, 0);
-            for (int64_t k = 0; k < K; ++k) ++count[gi[k]];
-            for (int64_t gg = 0; gg < G; ++gg)
+            std::vector<int32_t> full((size_t)Kf);
+            std::vector<int64_t> count((size_t)Gf, 0);
+            for (int64_t k = 0; k < Kf; ++k) ++count[gi[k]];
+            for (int64_t gg = 0; gg < Gf; ++gg)
                 if (count[gg] != gs) return fail("load_gptq: g_idx must assign exactly group_size rows to every group");
-            std::vector<int64_t> next((size_t)G);
-            for (int64_t gg = 0; gg < G; ++gg) next[gg] = gg * gs;
-            for (int64_t k = 0; k < K; ++k) perm[next[gi[k]]++] = (int32_t)k;
-            for (int64_t gg = 0; gg < G; ++gg) perm[K + gg] = (int32_t)gg;  // sorted block gg is checkpoint group gg
+            std::vector<int64_t> next((size_t)Gf);
+            for (int64_t gg = 0; gg < Gf; ++gg) next[gg] = gg * gs;
+            for (int64_t k = 0; k < Kf; ++k) full[next[gi[k]]++] = (int32_t)k;   // sorted row i <- checkpoint row full[i]
+            // the shard's slice, stored relative to k_off (the repack adds k_off back; a ROW shard's entries may be
+            // negative or beyond K_local: they are checkpoint rows, not local x columns)
+            std::vector<int32_t> perm((size_t)K + (size_t)G);
+            for (int64_t i = 0; i < K; ++i) perm[i] = (int32_t)(full[L->k_off + i] - L->k_off);
+            for (int64_t gg = 0; gg < G; ++gg) perm[K + gg] = (int32_t)(L->k_off / gs + gg);  // sorted block -> checkpoint group
             cudaFree(L->perm); L->perm = nullptr;
             W4_CUDA_OK(cudaMalloc(&L->perm, perm.size() * 4));
             W4_CUDA_OK(cudaMemcpyAsync(L->perm, perm.data(), perm.size() * 4, cudaMemcpyHostToDevice, s));
             W4_CUDA_OK(cudaStreamSynchronize(s));  // perm is a local; the copy must finish before it dies
             perm_dev = L->perm; grp_dev = L->perm + K;
+            L->perm_external = L->tp_mode == W4A16_TP_ROW && L->tp_size > 1;
         }
     }
     if (load_common(L, W4A16_FORMAT_GPTQ_ZP, W4A16_FORMAT_GPTQ_SYM, qweight, qzeros, scales, scales_dtype, perm_dev,
@@ -502,7 +534,7 @@ int w4a16_forward_row_fused(w4a16_handle_t h, const void *x_bf16, void *y_bf16, 
         return w4a16_forward_row_allreduce(h, x_bf16, y_bf16, M, comm, stream);
     if (!x_bf16 || !y_bf16) return fail("forward_row_fused: null x or y");
     const __nv_bfloat16 *x = reinterpret_cast<const __nv_bfloat16 *>(x_bf16);
-    if (L->perm) {
+    if (L->perm && !L->perm_external) {
         if (ensure_gather(L, M)) return 1;
         if (launch_gather_x(x, L->perm, L->x_gather, M, L->d.K, s)) return 1;
         x = L->x_gather;
@@ -545,6 +577,28 @@ int w4a16_dequant_into(w4a16_handle_t h, void *w_bf16, w4a16_stream_t stream) {
     if (!L || !L->loaded) return fail("dequant_into: weights not loaded");
     DeviceGuard g(L->device);
     return launch_dequant(*L, reinterpret_cast<__nv_bfloat16 *>(w_bf16), reinterpret_cast<cudaStream_t>(stream));
+}
+int w4a16_dequant_d1_into(w4a16_handle_t h, const void *scales, int scales_dtype, void *w_f16, w4a16_stream_t stream) {
+    Linear *L = reinterpret_cast<Linear *>(h);
+    if (!L || !L->loaded) return fail("dequant_d1_into: weights not loaded");
+    if (!scales || !w_f16) return fail("dequant_d1_into: null scales or output");
+    if (scales_dtype < W4A16_DTYPE_F16 || scales_dtype > W4A16_DTYPE_F32) return fail("dequant_d1_into: bad scales dtype");
+    DeviceGuard g(L->device);
+    return launch_dequant_d1(*L, scales, scales_dtype, reinterpret_cast<__half *>(w_f16), reinterpret_cast<cudaStream_t>(stream));
+}
+int w4a16_row_perm(w4a16_handle_t h, int32_t *perm_out_host) {
+    Linear *L = reinterpret_cast<Linear *>(h);
+    if (!L || !L->loaded) return fail("row_perm: weights not loaded");
+    if (!perm_out_host) return fail("row_perm: null output");
+    const int64_t K = L->d.K;
+    if (!L->perm) {
+        for (int64_t i = 0; i < K; ++i) perm_out_host[i] = (int32_t)(L->k_off + i);
+        return 0;
+    }
+    DeviceGuard g(L->device);
+    W4_CUDA_OK(cudaMemcpy(perm_out_host, L->perm, (size_t)K * 4, cudaMemcpyDeviceToHost));
+    for (int64_t i = 0; i < K; ++i) perm_out_host[i] += (int32_t)L->k_off;
+    return 0;
 }
 int w4a16_unpack_into(w4a16_handle_t h, uint8_t *q, uint8_t *z, w4a16_stream_t stream) {
     Linear *L = reinterpret_cast<Linear *>(h);

@@ -149,7 +149,8 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 8 ? 2 : 1) gemv_stream_kerne
                     int *e = gti + ((size_t)(c / (SUB_K / 8)) * MR + m) * 8;
                     e[2 * in_grp] = sumA;
                     e[2 * in_grp + 1] = sumB;
-                    if (in_grp == 0) e[4] = (E - 13) << 23;      // bits of 2^e: undoes the scale
+                    // bits of 2^e (undoes the scale); NaN when the (group, token) holds Inf / NaN: non-finite in -> NaN out
+                    if (in_grp == 0) e[4] = mx >= 0x7F80u ? 0x7FC00000 : (E - 13) << 23;
                 }
             }
         } else {

@@ -127,11 +127,29 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 4 ? 2 : 1) gemv_imma_kernel(
         }
     };
     stamp(0);
+    // L2 prefetch of the next linear's stream (immutable weights: independent of every earlier kernel)
+    auto l2_prefetch = [&]() {
+#pragma unroll
+        for (int w = 0; w < 2; ++w) {
+            if (!p.pf_base[w]) continue;
+            const uint32_t lo = (uint32_t)cta * p.pf_slice[w], hi = min(lo + p.pf_slice[w], p.pf_bytes[w]);
+            if (p.pf_flags & 2) {
+                if (tid == 32)
+                    for (uint32_t off = lo; off < hi; off += 32768u)
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.pf_base[w] + off), "r"(min(32768u, hi - off)) : "memory");
+            } else {
+                for (uint32_t off = lo + (uint32_t)tid * 128u; off < hi; off += GV_THREADS * 128u)
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(p.pf_base[w] + off));
+            }
+        }
+    };
+    if (!(p.pf_flags & 1)) l2_prefetch();
     // A launch that ends with the cross-GPU exchange releases its dependents only at exit: with the next linear's
     // CTAs co-resident during the exchange the TP=2 step measured 1.21 ms against 1.02 ms without (bench.py --gpus 2).
     if (!FUSED || (p.peer.flags & 1)) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
     stamp(1);
+    if (p.pf_flags & 1) l2_prefetch();
     // fused all-reduce: this launch's epoch (the previous launch's last CTA has stored the counter; read it now so
     // that the load is off the epilogue's critical path)
     constexpr bool fused = FUSED;
@@ -210,7 +228,10 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 4 ? 2 : 1) gemv_imma_kernel(
                         *reinterpret_cast<uint32_t *>(dst + COLS * 8) = v2;
                         *reinterpret_cast<uint32_t *>(dst + COLS * 8 + 8) = v3;
                     }
-                    if ((c & (GL - 1)) == 0) gtab[(size_t)(c / GL) * MR + m] = make_int2(sum, (E - 13) << 23);
+                    // Inf / NaN anywhere in the (group, token): the scale becomes NaN, so every output of that token is
+                    // NaN (non-finite in -> non-finite out, like the reference's fp32 FMA chain, awq_gemv.cu:597-664)
+                    if ((c & (GL - 1)) == 0)
+                        gtab[(size_t)(c / GL) * MR + m] = make_int2(sum, mx >= 0x7F80u ? 0x7FC00000 : (E - 13) << 23);
                 }
             }
         }
@@ -395,24 +416,18 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 4 ? 2 : 1) gemv_imma_kernel(
     // this rank's partial sums (with -0.0f canonicalised to +0.0f) into slot [e % 3][rank] of EVERY rank over NVLink,
     // polls its own slots [e % 3][0..world) until no word is the sentinel, sums the sources in rank order (the same
     // order on every rank: bit-identical results everywhere), adds the bias and writes bf16.  The data words are
-    // their own arrival flags: no fence, no flag round trip, no barrier between ranks.  Buffer (e + 1) % 3 -- last
-    // used by launch e - 2, which this CTA itself consumed -- is reset to the sentinel for the next launch.  All
-    // ranks run the same partition, so CTA c owns the same rows everywhere and the exchange is purely per CTA.
+    // their own arrival flags: no fence, no flag round trip, no barrier between ranks.  Only the words of real tokens
+    // (tok < M) are stored, every stored word is polled by exactly one thread, and that thread puts the sentinel back
+    // as soon as it has read the word: a launch leaves its buffer clean whatever N and M the neighbouring launches
+    // use (one PeerGroup serves row-parallel linears of different N).  The next store into such a word belongs to
+    // launch e + 3, which a peer issues only after it has seen this rank's launch e + 2 partials -- two kernel
+    // boundaries after the reset.  All ranks run the same partition, so CTA c owns the same rows everywhere and the
+    // exchange is purely per CTA.
     float *own = nullptr;
-    size_t cur_off = 0, clr_off = 0;
+    size_t cur_off = 0;
     if constexpr (FUSED) {
         own = p.peer.base[p.peer.rank & (PEER_MAX_WORLD - 1)];
-        const size_t buf_words = (size_t)p.peer.world * p.peer.cap;
-        cur_off = (size_t)(epoch % 3u) * buf_words; clr_off = (size_t)((epoch + 1u) % 3u) * buf_words;
-    }
-    if constexpr (FUSED) {
-        // word of (row n, token) = n * PEER_TOK + token whatever this launch's MR: consecutive launches may carry
-        // different token counts, and the reset below must cover what ANY earlier launch stored for these rows
-        for (int it = tid; it < n_slots * 16 * PEER_TOK; it += GV_THREADS) {
-            const size_t idx = (size_t)(R_first * 16) * PEER_TOK + it;    // this CTA's rows are contiguous: [16 n_slots][PEER_TOK]
-            for (int r = 0; r < p.peer.world; ++r)
-                reinterpret_cast<uint32_t *>(own + clr_off + (size_t)r * p.peer.cap)[idx] = PEER_EMPTY;
-        }
+        cur_off = (size_t)(epoch % 3u) * ((size_t)p.peer.world * p.peer.cap);
     }
     for (int it = tid; it < n_slots * 32 * MR; it += GV_THREADS) {      // multiples of 32: whole warps
         const int q = it & 3, e = (it >> 2) & (8 * MR - 1), slot = it / (32 * MR);
@@ -427,7 +442,7 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 4 ? 2 : 1) gemv_imma_kernel(
             uint32_t bx = __float_as_uint(v.x), by = __float_as_uint(v.y);
             if (bx == PEER_EMPTY) bx = 0u;
             if (by == PEER_EMPTY) by = 0u;
-            for (int r = q; r < p.peer.world; r += 4) {                 // lane q serves peers q, q + 4
+            for (int r = q; r < p.peer.world && tok < p.M; r += 4) {    // lane q serves peers q, q + 4; real tokens only
                 uint32_t *dst = reinterpret_cast<uint32_t *>(p.peer.base[r] + cur_off + (size_t)p.peer.rank * p.peer.cap);
                 asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(dst + (size_t)n0 * PEER_TOK + tok), "r"(bx) : "memory");
                 asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(dst + (size_t)(n0 + 8) * PEER_TOK + tok), "r"(by) : "memory");
@@ -447,20 +462,34 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 4 ? 2 : 1) gemv_imma_kernel(
             const int n = R_first * 16 + it / MR;
             if (tok >= p.M) continue;                                   // padding token slots are never read
             const uint32_t *srcw = reinterpret_cast<const uint32_t *>(own + cur_off) + (size_t)n * PEER_TOK + tok;
-            float acc = 0.f;
-            for (int r = 0; r < p.peer.world; ++r) {
-                uint32_t w;
-                uint32_t spins = 0;
-                for (;;) {
-                    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(w) : "l"(srcw + (size_t)r * p.peer.cap) : "memory");
-                    if (w != PEER_EMPTY) break;
-                    if ((++spins & 1023u) == 0) {
-                        unsigned long long t1;
-                        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-                        if (t1 - t0 > 20000000000ull) __trap();   // 20 s: a peer never arrived -- fail loudly instead of hanging
-                    }
+            // all sources' words are requested together and re-read until none is the sentinel (one NVLink latency,
+            // not `world` of them in sequence)
+            uint32_t w[PEER_MAX_WORLD];
+            uint32_t spins = 0;
+            for (;;) {
+                bool all = true;
+#pragma unroll
+                for (int r = 0; r < PEER_MAX_WORLD; ++r) {
+                    w[r] = 0u;
+                    if (r < p.peer.world)
+                        asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(w[r]) : "l"(srcw + (size_t)r * p.peer.cap) : "memory");
                 }
-                acc += __uint_as_float(w);
+#pragma unroll
+                for (int r = 0; r < PEER_MAX_WORLD; ++r) all = all && w[r] != PEER_EMPTY;
+                if (all) break;
+                if ((++spins & 1023u) == 0) {
+                    unsigned long long t1;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                    if (t1 - t0 > 20000000000ull) __trap();   // 20 s: a peer never arrived -- fail loudly instead of hanging
+                }
+            }
+            float acc = 0.f;
+#pragma unroll
+            for (int r = 0; r < PEER_MAX_WORLD; ++r) {
+                if (r < p.peer.world) {
+                    acc += __uint_as_float(w[r]);               // rank order: bit-identical on every rank
+                    const_cast<uint32_t *>(srcw)[(size_t)r * p.peer.cap] = PEER_EMPTY;   // consumed: empty again for launch e + 3
+                }
             }
             const float bsv = p.bias ? __bfloat162float(p.bias[n]) : 0.f;
             p.y[(size_t)tok * p.N + n] = __float2bfloat16_rn(acc + bsv);
@@ -580,6 +609,23 @@ int launch_gemv_imma_peer(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16
     p.off_xs = pl.off_xs; p.off_gtab = pl.off_gtab; p.off_part = pl.off_part;
     p.off_wring = pl.off_wring; p.off_mring = pl.off_mring;
     p.dbg = gemv_debug_slot();
+    {   // w4a16_set_next: this launch requests the next linear's stream into L2
+        static const int pf_mode = gv_env_int("W4A16_L2PF", 1);   // 0 off | 1 before the wait | 2 after the wait; +4: bulk prefetch
+        static const int pf_hops = gv_env_int("W4A16_L2PF_HOPS", 1);
+        const Linear *nx = linear_next(&L);
+        for (int hop = 1; nx && hop < pf_hops; ++hop) nx = linear_next(nx);
+        if (pf_mode & 3 && nx && nx->loaded && nx->device == L.device) {
+            const int64_t bytes[2] = {qw_bytes(nx->d), meta_bytes(nx->d)};
+            const void *base[2] = {nx->qw, nx->meta};
+            for (int w = 0; w < 2; ++w) {
+                if (bytes[w] >= ((int64_t)1 << 32)) continue;
+                p.pf_base[w] = reinterpret_cast<const uint8_t *>(base[w]);
+                p.pf_bytes[w] = (uint32_t)bytes[w];
+                p.pf_slice[w] = (uint32_t)((((bytes[w] + L.gv_grid - 1) / L.gv_grid) + 127) & ~(int64_t)127);
+            }
+            p.pf_flags = ((pf_mode & 3) == 2 ? 1 : 0) | (pf_mode & 4 ? 2 : 0);
+        }
+    }
     if (peer) {
         if (!gemv_imma_peer_usable(L, M, *peer)) return fail("launch_gemv_imma: shape not supported by the fused all-reduce epilogue");
         p.peer = *peer;

@@ -50,6 +50,8 @@ struct Linear {
     uint8_t *meta = nullptr;       // [NR][G][48]
     __nv_bfloat16 *bias = nullptr; // [N] or null
     int32_t *perm = nullptr;       // act-order: tiled row i holds checkpoint row perm[i]; null otherwise
+    bool perm_external = false;    // act-order ROW shard: the rows were sorted over the FULL K before sharding; x arrives
+                                   // already in that order (no gather at forward), hooks answer in tiled row order
     int32_t *tickets = nullptr;    // [NR] split-K arrival counters (self-resetting)
     float *splitk_scratch = nullptr;  // [SC][32][N] fp32 partials when the decode kernel splits K over CTAs
     int64_t splitk_floats = 0;
@@ -66,7 +68,10 @@ struct Linear {
     int *gu_rb_start = nullptr;   // tcgen05 decode kernel: first row block of every CTA (device)
     int gu_grid = 0, gu_max_rb = 0;
     DeviceScratch *scratch = nullptr;
+    Linear *next = nullptr;       // w4a16_set_next: the linear the caller runs after this one (L2 prefetch hint)
 };
+// `L->next` if that handle is still alive (a destroyed handle is dropped from the registry), else null
+const Linear *linear_next(const Linear *L);
 
 // ---- kernels (defined in the .cu files) ----------------------------------------
 struct RepackSrc {
@@ -85,6 +90,7 @@ int launch_repack(const Linear &L, const RepackSrc &src, cudaStream_t stream);
 int launch_unpack(const Linear &L, uint8_t *q, uint8_t *z, cudaStream_t stream);
 int launch_dequant(const Linear &L, __nv_bfloat16 *w, cudaStream_t stream);
 int launch_scales_out(const Linear &L, __nv_bfloat16 *s, cudaStream_t stream);
+int launch_dequant_d1(const Linear &L, const void *scales, int scales_dtype, __half *w, cudaStream_t stream);
 int launch_convert_bias(const void *src, int dtype, __nv_bfloat16 *dst, int64_t n, cudaStream_t stream);
 int launch_gather_x(const __nv_bfloat16 *x, const int32_t *perm, __nv_bfloat16 *xg, int64_t M, int64_t K,
                     cudaStream_t stream);

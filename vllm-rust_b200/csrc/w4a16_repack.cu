@@ -198,8 +198,9 @@ static int grid_for(int64_t n) {
 // grp_map for the hooks lives next to perm on the handle (Linear::perm + K entries).
 static HookParams hook_params(const Linear &L) {
     HookParams p;
-    p.d = L.d; p.qw = L.qw; p.meta = L.meta; p.perm = L.perm;
-    p.grp_map = L.perm ? L.perm + L.d.K : nullptr;
+    p.d = L.d; p.qw = L.qw; p.meta = L.meta;
+    p.perm = L.perm_external ? nullptr : L.perm;   // an externally permuted ROW shard answers in tiled row order
+    p.grp_map = p.perm ? L.perm + L.d.K : nullptr;
     return p;
 }
 
@@ -222,6 +223,42 @@ int launch_scales_out(const Linear &L, __nv_bfloat16 *s, cudaStream_t stream) {
 int launch_dequant(const Linear &L, __nv_bfloat16 *w, cudaStream_t stream) {
     HookParams p = hook_params(L);
     dequant_dense_kernel<<<grid_for(L.d.NR * L.d.KB * CHUNK_WORDS), 256, 0, stream>>>(p, w);
+    count_launch();
+    W4_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+// The reference's OTHER dequant grid ("D1", SURVEY 8a hazard i): awq_dequantize_cpu (awq.rs:56-166) multiplies
+// (q - z) as f32 by the checkpoint's ORIGINAL scale (f16 in AWQ checkpoints, not the bf16-rounded resident copy) and
+// casts the matrix to F16 (awq.rs:163-165).  The resident layout keeps only bf16 scales (S1), so the hook takes the
+// checkpoint's scales tensor again; q and z come from the resident layout.  Parity hook only: no kernel consumes D1.
+__global__ void dequant_d1_kernel(HookParams p, const void *scales, int dtype, int64_t N_full, int64_t n_off,
+                                  int64_t k_off, int gs_ckpt, __half *w) {
+    int64_t total = p.d.K * p.d.N;
+    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        int64_t k = idx / p.d.N, n = idx - k * p.d.N;        // k = tiled row
+        NibblePos np = nibble_pos(p.d, k, n);
+        int q = (int)((p.qw[np.word] >> np.shift) & 0xFu);
+        int64_t grp = k / p.d.gs;
+        int r = (int)(n & 15);
+        const uint8_t *m = p.meta + meta_offset(p.d, n >> 4, grp);
+        int z = (m[META_ZERO_OFF + (r & 7)] >> (4 * (r >> 3))) & 0xF;
+        int64_t cg = p.grp_map ? (int64_t)p.grp_map[grp] : (k_off + grp * p.d.gs) / gs_ckpt;
+        int64_t si = cg * N_full + n_off + n;
+        float sc = dtype == 0 ? __half2float(reinterpret_cast<const __half *>(scales)[si])
+                 : dtype == 1 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16 *>(scales)[si])
+                              : reinterpret_cast<const float *>(scales)[si];
+        int64_t ko = p.perm ? (int64_t)p.perm[k] : k;
+        w[ko * p.d.N + n] = __float2half_rn((float)(q - z) * sc);
+    }
+}
+
+int launch_dequant_d1(const Linear &L, const void *scales, int scales_dtype, __half *w, cudaStream_t stream) {
+    HookParams p = hook_params(L);
+    const int gs_ckpt = L.group_size_cfg > 0 ? L.group_size_cfg : (int)L.K_full;
+    dequant_d1_kernel<<<grid_for(L.d.K * L.d.N), 256, 0, stream>>>(p, scales, scales_dtype, L.N_full, L.n_off, L.k_off,
+                                                                  gs_ckpt, w);
     count_launch();
     W4_CUDA_OK(cudaGetLastError());
     return 0;

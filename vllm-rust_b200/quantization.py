@@ -44,6 +44,9 @@ class QuantizationMethod(enum.Enum):  # quantization/config.rs QuantizationMetho
     GPTQ = "gptq"
     MARLIN = "marlin"  # "gptq_marlin" routes here (detection.rs:258)
 
+    def __str__(self) -> str:  # Display impl (config.rs): the lower-case method name
+        return self.value
+
 
 class MarlinScalarType(enum.Enum):  # marlin.rs:52-84
     UINT4B8 = "uint4b8"  # symmetric, W = (q - 8) * s
@@ -135,7 +138,9 @@ class B200W4A16Linear(QuantizedLinear):
                                        int(bias), self._device.index, tp_mode, tp_rank, tp_size))
         self._full = (in_features, out_features)
         self._fmt = fmt
+        self._group_size = group_size
         self._loaded = False
+        self._next = None
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -192,7 +197,7 @@ class B200W4A16Linear(QuantizedLinear):
         bias = dev(weights.get("bias"))
         if bias is not None and bias.dtype not in DTYPE_CODE:
             raise W4A16Error(f"bias dtype {bias.dtype} not supported")
-        g = scales.shape[0]
+        g = 1 if self._group_size <= 0 else kf // self._group_size   # marlin.rs:308-341: K % group_size == 0
         exp_qw = (kf, nf // 8) if self._fmt == FORMAT_AWQ else (kf // 8, nf)
         if tuple(qweight.shape) != exp_qw:
             raise W4A16Error(f"qweight shape {tuple(qweight.shape)} != expected {exp_qw}")
@@ -209,7 +214,11 @@ class B200W4A16Linear(QuantizedLinear):
                 check(lib().w4a16_load_awq(self._h, ptr(qweight), ptr(qzeros), ptr(scales), DTYPE_CODE[scales.dtype],
                                            ptr(bias), DTYPE_CODE[bias.dtype] if bias is not None else 1, s))
             else:
-                g_idx = dev(weights.get("g_idx"), torch.int32)
+                g_idx = weights.get("g_idx")
+                if g_idx is not None:
+                    if g_idx.dtype.is_floating_point or g_idx.numel() != kf:
+                        raise W4A16Error(f"g_idx must hold {kf} integer entries, got {g_idx.numel()} of {g_idx.dtype}")
+                    g_idx = g_idx.to(self._device, torch.int32).contiguous()
                 check(lib().w4a16_load_gptq(self._h, ptr(qweight), ptr(qzeros), ptr(scales),
                                             DTYPE_CODE[scales.dtype], ptr(g_idx), ptr(bias),
                                             DTYPE_CODE[bias.dtype] if bias is not None else 1, s))
@@ -289,17 +298,37 @@ class B200W4A16Linear(QuantizedLinear):
             check(lib().w4a16_scales_into(self._h, ctypes.c_void_p(s.data_ptr()), _stream_ptr(s)))
         return s
 
+    def dequantize_d1(self, scales: torch.Tensor) -> torch.Tensor:
+        """Dense [K, N] f16 on the D1 grid of awq_dequantize_cpu (awq.rs:56-166): f32(q - z) * f32(original scale),
+        cast to F16.  `scales` is the checkpoint's [G, N] tensor (the resident copy is bf16-rounded)."""
+        sc = scales.to(self._device).contiguous()
+        if sc.dtype not in DTYPE_CODE:
+            raise W4A16Error(f"scales dtype {sc.dtype} not supported")
+        w = torch.empty((self.in_features(), self.out_features()), dtype=torch.float16, device=self._device)
+        with torch.cuda.device(self._device):
+            check(lib().w4a16_dequant_d1_into(self._h, ctypes.c_void_p(sc.data_ptr()), DTYPE_CODE[sc.dtype],
+                                              ctypes.c_void_p(w.data_ptr()), _stream_ptr(w)))
+            torch.cuda.current_stream().synchronize()   # `sc` is a local
+        return w
+
+    def row_perm(self) -> torch.Tensor:
+        """Checkpoint row of every local row (w4a16_row_perm); for an act-order ROW shard: the x column order."""
+        out = torch.empty((self.in_features(),), dtype=torch.int32)
+        check(lib().w4a16_row_perm(self._h, ctypes.c_void_p(out.data_ptr())))
+        return out
+
+    def set_next(self, nxt: "Optional[B200W4A16Linear]") -> None:
+        """Call-order hint (w4a16_set_next): the decode kernel of this linear prefetches `nxt`'s weights into L2."""
+        check(lib().w4a16_set_next(self._h, nxt._h if nxt is not None else None))
+        self._next = nxt
+
     def weight_groups(self) -> int:
         gs = self._group_size
         return 1 if gs <= 0 else self.in_features() // gs
 
-    _group_size = 128
-
 
 def _make_linear(in_features, out_features, bias, group_size, fmt, device, **tp) -> B200W4A16Linear:
-    lin = B200W4A16Linear(in_features, out_features, bias, group_size, fmt, device, **tp)
-    lin._group_size = group_size
-    return lin
+    return B200W4A16Linear(in_features, out_features, bias, group_size, fmt, device, **tp)
 
 
 @dataclass
@@ -450,6 +479,42 @@ def detect_from_json(config: Mapping) -> DetectedQuantConfig:
         return DetectedQuantConfig()
     m = _METHODS.get(qc.get("quant_method"), QuantizationMethod.NONE)
     return DetectedQuantConfig(m, qc.get("bits"), qc.get("group_size"), qc.get("desc_act"), dict(qc))
+
+
+def detect_from_directory(model_dir) -> DetectedQuantConfig:
+    """detection.rs:70-218: config.json's `quantization_config` first, then quantize_config.json (GPTQ layout
+    {bits, group_size, desc_act}; AWQ layout {w_bit, q_group_size}); anything else (missing directory, no
+    quantization section, unknown method) is QuantizationMethod.NONE."""
+    import json
+    import os
+    d = str(model_dir)
+    try:
+        with open(os.path.join(d, "config.json")) as f:
+            det = detect_from_json(json.load(f))
+        if det.method is not QuantizationMethod.NONE:
+            return det
+    except (OSError, ValueError):
+        pass
+    try:
+        with open(os.path.join(d, "quantize_config.json")) as f:
+            qc = json.load(f)
+    except (OSError, ValueError):
+        return DetectedQuantConfig()
+    if not isinstance(qc, Mapping):
+        return DetectedQuantConfig()
+    if qc.get("bits") is not None and qc.get("group_size") is not None:   # GPTQ layout (detection.rs:180-201)
+        m = QuantizationMethod.MARLIN if qc.get("quant_method") == "gptq_marlin" else QuantizationMethod.GPTQ
+        return DetectedQuantConfig(m, qc.get("bits"), qc.get("group_size"), qc.get("desc_act"), dict(qc))
+    if qc.get("w_bit") is not None:                                        # AWQ layout (detection.rs:203-216)
+        return DetectedQuantConfig(QuantizationMethod.AWQ, qc.get("w_bit"), qc.get("q_group_size"), None, dict(qc))
+    return DetectedQuantConfig()
+
+
+def is_supported(capability: int, method: QuantizationMethod) -> bool:
+    """quantization/mod.rs:237-264 for the W4A16 members (the reference's minimum capabilities; this build itself
+    runs on capability 100 only -- QuantizationConfig.min_capability())."""
+    return capability >= {QuantizationMethod.NONE: 0, QuantizationMethod.GPTQ: 70, QuantizationMethod.AWQ: 70,
+                          QuantizationMethod.MARLIN: 80, QuantizationMethod.AWQ_MARLIN: 80}[method]
 
 
 def create_config(detected: DetectedQuantConfig) -> QuantizationConfig:
