@@ -189,14 +189,6 @@ def build_layers(P, torch, shapes, n_layers, device, comm=None, seed=0, peers=No
     return layers
 
 
-def chain_next(layers):
-    """w4a16_set_next in call order (the reference's model code runs its linears in a fixed order per layer,
-    qwen3_quantized.rs:532-551, 704-709); the last linear of a step is followed by the first of the next step."""
-    inner = [getattr(t[6], "inner", t[6]) for t in layers]
-    for a, b in zip(inner, inner[1:] + inner[:1]):
-        a.set_next(b)
-
-
 def timed_steps(torch, dist, dev, run, stream, args, world, rank, local):
     for _ in range(args.warmup):
         run()
@@ -265,8 +257,6 @@ def run_gpu(args):
             print(json.dumps({"metric": METRIC, "n_gpus": world, "tp_check": tp_chk, "error": "tp_check failed"}))
         raise SystemExit(3)
     layers = build_layers(P, torch, shapes, n_layers, dev, nccl, peers=peers)
-    if args.next_hint:
-        chain_next(layers)
 
     xs = {}
     ys = {}
@@ -305,7 +295,6 @@ def run_gpu(args):
                    "linears_per_step": n_lin, "weight_bytes_per_step": step_bytes,
                    "l2_policy": "inputs larger than L2: every step streams %.2f GB of distinct weights" % (step_bytes / 1e9 / max(world, 1)),
                    "launch": "cuda-graph replay" if graph is not None else "stream launches", "pdl": os.environ.get("W4A16_NO_PDL", "0") == "0",
-                   "next_hint": bool(args.next_hint),
                    "allreduce": (None if world == 1 else "fused GEMV epilogue over NVLink peer memory (one kernel, no NCCL launch)"
                                  if peers is not None else "ncclAllReduce after the GEMV")},
         "gpu_launches": int(launches_per_step * args.steps),
@@ -414,8 +403,6 @@ def tp_check(P, torch, dist, dev, nccl, peers, rank, world):
 def same_workload_1gpu(P, torch, dev, shapes, n_layers, args):
     """The TP workload UNSHARDED on this one GPU (7.1 GB of weights for the 16-layer Llama-3-70B step): ms per step."""
     layers = build_layers(P, torch, [sh[:3] for sh in shapes], n_layers, dev)
-    if args.next_hint:
-        chain_next(layers)
     xs = {K: torch.randn((1, K), device=dev).to(torch.bfloat16) for _, K, *_ in layers}
     ys = {N: torch.empty((1, N), device=dev, dtype=torch.bfloat16) for _, _, N, *_ in layers}
 
@@ -441,9 +428,6 @@ def shape_sweep(P, torch, dev, peaks, args):
             lin = cfg.create_linear(K, N, False, dev)
             lin.load_weights(rand_awq(torch, K, N, dev))
             lins.append(lin)
-        for a, b in zip(lins, lins[1:] + lins[:1]):
-            if args.next_hint:
-                a.set_next(b)
         for M in ms_list:
             use = lins if M < 512 else lins[:2]
             x = torch.randn((M, K), device=dev).to(torch.bfloat16)
@@ -532,8 +516,6 @@ def config1(P, torch, dev, peaks):
         lin = cfg.create_linear(K, N, False, dev)
         lin.load_weights(rand_awq(torch, K, N, dev))
         lins.append(lin)
-    for a, b in zip(lins, lins[1:] + lins[:1]):
-        a.set_next(b)
     x = torch.randn((1, K), device=dev).to(torch.bfloat16)
     y = torch.empty((1, N), device=dev, dtype=torch.bfloat16)
 
@@ -561,8 +543,6 @@ def gptq_act_order(P, torch, dev, peaks):
             lin.load_weights(rand_gptq_act_order(torch, K, N, dev))
             lin.reserve(max(GPTQ_M))
             lins.append(lin)
-        for a, b in zip(lins, lins[1:] + lins[:1]):
-            a.set_next(b)
         for M in GPTQ_M:
             x = torch.randn((M, K), device=dev).to(torch.bfloat16)
             y = torch.empty((M, N), device=dev, dtype=torch.bfloat16)
@@ -751,8 +731,6 @@ def main():
     ap.add_argument("--no-graph", dest="graph", action="store_false")
     ap.add_argument("--no-fused-ar", dest="fused_ar", action="store_false",
                     help="TP runs: all-reduce through ncclAllReduce instead of the fused GEMV epilogue over peer memory")
-    ap.add_argument("--no-next-hint", dest="next_hint", action="store_false",
-                    help="do not chain the linears with w4a16_set_next (no L2 prefetch of the next linear's weights)")
     ap.add_argument("--quick", action="store_true", help="decode step + short sweep only (no prefill / e2e / cpu legs)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":

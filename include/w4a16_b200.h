@@ -105,13 +105,6 @@ int w4a16_load_gptq(w4a16_handle_t h, const uint32_t *qweight /*[K/8,N]*/,
                     const int32_t *g_idx /*[K] device, or NULL*/, const void *bias, int bias_dtype,
                     w4a16_stream_t stream);
 
-/* Call-order hint: `next` is the linear the caller runs right after `h` (the reference's model code calls its
- * linears in a fixed order per layer: qkv, o, gate/up, down -- qwen3_quantized.rs:532-551, 704-709).  The decode
- * kernel of `h` then requests `next`'s weight stream into L2 while it works, so HBM stays busy across the launch
- * boundary.  A hint only: results never depend on it; NULL clears it; `next` may be destroyed first (the hint is
- * dropped).  Both handles must live on the same device.                       */
-int w4a16_set_next(w4a16_handle_t h, w4a16_handle_t next);
-
 /* -- forward ----------------------------------------------------------------
  * QuantizedLinear::forward(&Tensor) (config.rs:149) as it is executed by
  * MarlinLinear::forward -> marlin_gemm_pooled / marlin_gemm (marlin.rs:741-754,

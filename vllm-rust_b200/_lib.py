@@ -57,7 +57,6 @@ SIGNATURES = {
     "w4a16_nccl_comm_init": (_i32, [ctypes.POINTER(_vp), _i32, _vp, _i32]),
     "w4a16_nccl_comm_destroy": (_i32, [_vp]),
     "w4a16_reserve": (_i32, [_vp, _i64]),
-    "w4a16_set_next": (_i32, [_vp, _vp]),
     "w4a16_dequant_into": (_i32, [_vp, _vp, _vp]),
     "w4a16_dequant_d1_into": (_i32, [_vp, _vp, _i32, _vp, _vp]),
     "w4a16_row_perm": (_i32, [_vp, _vp]),

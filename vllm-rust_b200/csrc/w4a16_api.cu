@@ -80,28 +80,12 @@ struct DeviceGuard {
     }
 };
 
-// Live handles: w4a16_set_next stores a raw pointer to another handle, which the caller may destroy first.
-static std::mutex g_live_mu;
-static std::vector<const Linear *> g_live;
-static void live_add(const Linear *L) { std::lock_guard<std::mutex> lk(g_live_mu); g_live.push_back(L); }
-static void live_del(const Linear *L) {
-    std::lock_guard<std::mutex> lk(g_live_mu);
-    g_live.erase(std::remove(g_live.begin(), g_live.end(), L), g_live.end());
-}
-const Linear *linear_next(const Linear *L) {
-    const Linear *n = L->next;
-    if (!n) return nullptr;
-    std::lock_guard<std::mutex> lk(g_live_mu);
-    return std::find(g_live.begin(), g_live.end(), n) != g_live.end() ? n : nullptr;
-}
-
 static void free_linear(Linear *L) {
     if (!L) return;
-    live_del(L);
     DeviceGuard g(L->device);
     cudaFree(L->qw); cudaFree(L->meta); cudaFree(L->bias); cudaFree(L->perm); cudaFree(L->tickets);
     cudaFree(L->splitk_scratch); cudaFree(L->x_gather); cudaFree(L->stage_x); cudaFree(L->stage_y);
-    cudaFree(L->rowpar_f32); cudaFree(L->gv_tab); cudaFree(L->gu_rb_start);
+    cudaFree(L->rowpar_f32); cudaFree(L->gv_tab);
     delete L;
 }
 
@@ -274,18 +258,8 @@ int w4a16_create_shard(w4a16_handle_t *out, int64_t in_features, int64_t out_fea
     if (cudaMemset(L->tickets, 0, (size_t)nt * 4) != cudaSuccess) return bail("cudaMemset(tickets) failed");
     if (sf > 0) { W4_ALLOC(L->splitk_scratch, (size_t)sf * 4); L->splitk_floats = sf; }
 #undef W4_ALLOC
-    if (gemv_build_table(*L, ds->sm_count) || gemv_umma_build_table(*L, ds->sm_count)) { free_linear(L); return 1; }
-    live_add(L);
+    if (gemv_build_table(*L, ds->sm_count)) { free_linear(L); return 1; }
     *out = reinterpret_cast<w4a16_handle_t>(L);
-    return 0;
-}
-
-int w4a16_set_next(w4a16_handle_t h, w4a16_handle_t next) {
-    Linear *L = reinterpret_cast<Linear *>(h);
-    if (!L) return fail("set_next: null handle");
-    Linear *nx = reinterpret_cast<Linear *>(next);
-    if (nx && nx->device != L->device) return fail("set_next: the next handle lives on another device");
-    L->next = nx;
     return 0;
 }
 

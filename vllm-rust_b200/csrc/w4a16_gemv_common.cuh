@@ -57,13 +57,6 @@ struct GemvParams {
     unsigned long long *dbg;    // W4A16_GV_DEBUG: per-CTA globaltimer stamps {start, after wait, staged, streamed, combined, end}
     // fused row-parallel all-reduce over NVLink peer memory (w4a16_gemv_imma.cu epilogue); world <= 1: off
     PeerView peer;
-    // L2 prefetch of the NEXT linear's weight stream (w4a16_set_next): every CTA requests its 1/grid slice of the two
-    // ranges, so HBM keeps working through this launch's dependency wait, activation staging, tail and hand-over
-    const uint8_t *pf_base[2];  // next handle's qw / meta (null: off)
-    uint32_t pf_slice[2];       // bytes per CTA (multiple of 128)
-    uint32_t pf_bytes[2];       // total bytes
-    int pf_flags;               // bit 0: issue after the dependency wait (default: before); bit 1: cp.async.bulk.prefetch.L2
-                                // by one thread (default: prefetch.global.L2 by all threads)
 };
 
 __device__ __forceinline__ uint32_t gv_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }

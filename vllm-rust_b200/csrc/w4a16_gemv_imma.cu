@@ -127,29 +127,11 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 4 ? 2 : 1) gemv_imma_kernel(
         }
     };
     stamp(0);
-    // L2 prefetch of the next linear's stream (immutable weights: independent of every earlier kernel)
-    auto l2_prefetch = [&]() {
-#pragma unroll
-        for (int w = 0; w < 2; ++w) {
-            if (!p.pf_base[w]) continue;
-            const uint32_t lo = (uint32_t)cta * p.pf_slice[w], hi = min(lo + p.pf_slice[w], p.pf_bytes[w]);
-            if (p.pf_flags & 2) {
-                if (tid == 32)
-                    for (uint32_t off = lo; off < hi; off += 32768u)
-                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.pf_base[w] + off), "r"(min(32768u, hi - off)) : "memory");
-            } else {
-                for (uint32_t off = lo + (uint32_t)tid * 128u; off < hi; off += GV_THREADS * 128u)
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(p.pf_base[w] + off));
-            }
-        }
-    };
-    if (!(p.pf_flags & 1)) l2_prefetch();
     // A launch that ends with the cross-GPU exchange releases its dependents only at exit: with the next linear's
     // CTAs co-resident during the exchange the TP=2 step measured 1.21 ms against 1.02 ms without (bench.py --gpus 2).
     if (!FUSED || (p.peer.flags & 1)) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
     stamp(1);
-    if (p.pf_flags & 1) l2_prefetch();
     // fused all-reduce: this launch's epoch (the previous launch's last CTA has stored the counter; read it now so
     // that the load is off the epilogue's critical path)
     constexpr bool fused = FUSED;
@@ -609,23 +591,6 @@ int launch_gemv_imma_peer(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16
     p.off_xs = pl.off_xs; p.off_gtab = pl.off_gtab; p.off_part = pl.off_part;
     p.off_wring = pl.off_wring; p.off_mring = pl.off_mring;
     p.dbg = gemv_debug_slot();
-    {   // w4a16_set_next: this launch requests the next linear's stream into L2
-        static const int pf_mode = gv_env_int("W4A16_L2PF", 1);   // 0 off | 1 before the wait | 2 after the wait; +4: bulk prefetch
-        static const int pf_hops = gv_env_int("W4A16_L2PF_HOPS", 1);
-        const Linear *nx = linear_next(&L);
-        for (int hop = 1; nx && hop < pf_hops; ++hop) nx = linear_next(nx);
-        if (pf_mode & 3 && nx && nx->loaded && nx->device == L.device) {
-            const int64_t bytes[2] = {qw_bytes(nx->d), meta_bytes(nx->d)};
-            const void *base[2] = {nx->qw, nx->meta};
-            for (int w = 0; w < 2; ++w) {
-                if (bytes[w] >= ((int64_t)1 << 32)) continue;
-                p.pf_base[w] = reinterpret_cast<const uint8_t *>(base[w]);
-                p.pf_bytes[w] = (uint32_t)bytes[w];
-                p.pf_slice[w] = (uint32_t)((((bytes[w] + L.gv_grid - 1) / L.gv_grid) + 127) & ~(int64_t)127);
-            }
-            p.pf_flags = ((pf_mode & 3) == 2 ? 1 : 0) | (pf_mode & 4 ? 2 : 0);
-        }
-    }
     if (peer) {
         if (!gemv_imma_peer_usable(L, M, *peer)) return fail("launch_gemv_imma: shape not supported by the fused all-reduce epilogue");
         p.peer = *peer;

@@ -65,13 +65,8 @@ struct Linear {
     int *gv_tab = nullptr;        // decode stream kernel: per-CTA unit range + row-block sharing table (device)
     int gv_grid = 0, gv_max_slots = 0;
     bool gv_aligned = false;      // every CTA range is a whole number of row blocks
-    int *gu_rb_start = nullptr;   // tcgen05 decode kernel: first row block of every CTA (device)
-    int gu_grid = 0, gu_max_rb = 0;
     DeviceScratch *scratch = nullptr;
-    Linear *next = nullptr;       // w4a16_set_next: the linear the caller runs after this one (L2 prefetch hint)
 };
-// `L->next` if that handle is still alive (a destroyed handle is dropped from the registry), else null
-const Linear *linear_next(const Linear *L);
 
 // ---- kernels (defined in the .cu files) ----------------------------------------
 struct RepackSrc {
@@ -115,11 +110,6 @@ struct PeerView;   // w4a16_gemv_common.cuh
 bool gemv_imma_peer_usable(const Linear &L, int64_t M, const PeerView &peer);
 int launch_gemv_imma_peer(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
                           cudaStream_t stream, const PeerView *peer);
-// decode, M <= 4: tcgen05 kernel (w4a16_gemv_umma.cu)
-bool gemv_umma_usable(const Linear &L, int64_t M);
-int gemv_umma_build_table(Linear &L, int sm_count);
-int launch_gemv_umma(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
-                     cudaStream_t stream);
 int gemv_debug_read(unsigned long long *out, int64_t words, unsigned long long *launches);
 // prefill (tcgen05): any M
 int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,

@@ -140,7 +140,6 @@ class B200W4A16Linear(QuantizedLinear):
         self._fmt = fmt
         self._group_size = group_size
         self._loaded = False
-        self._next = None
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -316,11 +315,6 @@ class B200W4A16Linear(QuantizedLinear):
         out = torch.empty((self.in_features(),), dtype=torch.int32)
         check(lib().w4a16_row_perm(self._h, ctypes.c_void_p(out.data_ptr())))
         return out
-
-    def set_next(self, nxt: "Optional[B200W4A16Linear]") -> None:
-        """Call-order hint (w4a16_set_next): the decode kernel of this linear prefetches `nxt`'s weights into L2."""
-        check(lib().w4a16_set_next(self._h, nxt._h if nxt is not None else None))
-        self._next = nxt
 
     def weight_groups(self) -> int:
         gs = self._group_size
