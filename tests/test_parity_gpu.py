@@ -383,7 +383,7 @@ def _imma_case(product, K, N, g, xb, what, seed=77):
     lin, (qweight, qzeros, scales, _) = make_awq_layer(product, K, N, g, seed=seed)
     q, z, sb = awq_unpacked(qweight, qzeros, scales)
     M = xb.shape[0]
-    assert lin.kernel_for(M) in ("gemv_stream_imma", "gemv_stream_dp4a", "gemv_stream_nt1"), lin.kernel_for(M)
+    assert lin.kernel_for(M) in ("gemv_stream_imma2", "gemv_stream_imma", "gemv_stream_dp4a", "gemv_stream_nt1"), lin.kernel_for(M)
     return lin, run_forward(lin, xb), oracle_forward(xb, q, z, sb, g)
 
 
@@ -481,3 +481,19 @@ def test_act_order_row_shards_compose(product, tp):
         acc += O.np_bf16_bits_to_f32(part)
     assert (np.sort(np.concatenate(seen)) == np.arange(K)).all(), "the shards' rows must partition K"
     assert np.abs(acc - want).max() <= O.reference_tolerance(want)
+
+
+@pytest.mark.parametrize("M", [1, 2, 3, 4])
+@pytest.mark.parametrize("g", [32, 64, 128])
+def test_imma2_k4096_all_group_sizes(product, M, g):
+    """The second-generation int8 tensor-core GEMV (K = 4096): hoisted B fragments at g = 128, the shared-memory path
+    at g = 32 / 64; bias; a row-block count that is not a multiple of the grid (uneven slots per CTA)."""
+    K, N = 4096, 4736
+    lin, (qweight, qzeros, scales, bias) = make_awq_layer(product, K, N, g, seed=61 + g + M, bias=True)
+    assert lin.kernel_for(M) == "gemv_stream_imma2"
+    q, z, sb = awq_unpacked(qweight, qzeros, scales)
+    xb = O.make_activations(M, K, seed=300 + M)
+    y = torch.full((M, N), float("nan"), dtype=torch.bfloat16, device=DEV)
+    lin.forward_into(t_bf16_from_bits(xb).to(DEV), y)
+    torch.cuda.synchronize()
+    assert_close_ref(bits_of(y), oracle_forward(xb, q, z, sb, g, bias_f32=bias), f"imma2 M={M} g={g}")

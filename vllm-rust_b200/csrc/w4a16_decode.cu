@@ -338,6 +338,7 @@ static int launch_t(const DecodeParams &p, dim3 grid, cudaStream_t stream, bool 
 }
 
 const char *decode_kernel_name(const Linear &L, int64_t M) {
+    if (gemv_imma2_usable(L, M)) return "gemv_stream_imma2";
     if (gemv_imma_usable(L, M)) return "gemv_stream_imma";
     if (M <= 4 && gemv_stream_usable(L, M)) return M <= 2 ? "gemv_stream_dp4a" : "gemv_stream_nt1";
     return M <= 8 ? "decode_mma_nt1" : M <= 16 ? "decode_mma_nt2" : "decode_mma_nt4";
@@ -346,6 +347,7 @@ const char *decode_kernel_name(const Linear &L, int64_t M) {
 int launch_decode(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
                   cudaStream_t stream) {
     if (M < 1 || M > 32) return fail("launch_decode: M must be in 1..32");
+    if (gemv_imma2_usable(L, M)) return launch_gemv_imma2(L, x, y, M, add_bias, stream);
     if (gemv_imma_usable(L, M)) return launch_gemv_imma(L, x, y, M, add_bias, stream);
     // measured: above 4 tokens the register-ring kernel below beats the stream kernel (its per-token staging dominates)
     if (M <= 4 && gemv_stream_usable(L, M)) return launch_gemv_stream(L, x, y, M, add_bias, stream);

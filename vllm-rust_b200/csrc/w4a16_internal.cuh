@@ -106,6 +106,10 @@ int launch_gemv_stream(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y
 bool gemv_imma_usable(const Linear &L, int64_t M);
 int launch_gemv_imma(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
                      cudaStream_t stream);
+// decode, M <= 4, K % 4096 == 0: second-generation int8 tensor-core stream kernel (w4a16_gemv_imma2.cu)
+bool gemv_imma2_usable(const Linear &L, int64_t M);
+int launch_gemv_imma2(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
+                      cudaStream_t stream);
 struct PeerView;   // w4a16_gemv_common.cuh
 bool gemv_imma_peer_usable(const Linear &L, int64_t M, const PeerView &peer);
 int launch_gemv_imma_peer(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
