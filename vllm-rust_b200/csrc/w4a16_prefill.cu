@@ -78,7 +78,12 @@ template <int GPS> struct WEntry {
 };
 
 // TM = tokens per tile (UMMA N): 256, 128 or 64.  GPS = groups per 64-k stage: 1 (g >= 64), 2 (g = 32).
-template <int TM, int GPS>
+// CL2 = launched as clusters of two CTAs that work on the two n-tiles of a pair in lockstep (same m-tile, same k blocks):
+// every x tile is fetched from L2 ONCE per pair -- each CTA loads half of the token rows and multicasts them into both
+// shared memories.  Measured with the kernel's own switches (W4A16_PF_DEBUG), skipping the x loads after the first
+// k block gained 6-12 % at M = 4096: the activation tiles (32 KB per 680 cycles per SM, 10 TB/s chip-wide) sit at the
+// L2's bandwidth limit.
+template <int TM, int GPS, bool CL2>
 __global__ void __launch_bounds__(PF_THREADS, 1)
 prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p) {
     using C = PfCfg<TM>;
@@ -100,7 +105,7 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < S; ++i) {
             mbar_init(full + 8 * i, 9);     // the producer's arrive.expect_tx (TMA completes the bytes) + 8 dequant warps
-            mbar_init(empty + 8 * i, 1);    // tcgen05.commit
+            mbar_init(empty + 8 * i, CL2 ? 2 : 1);    // tcgen05.commit (CL2: of both CTAs of the pair)
         }
         mbar_init(tmem_full, 1);            // tcgen05.commit after the last k block of a tile
         mbar_init(tmem_empty, 4);           // one arrival per epilogue warp
@@ -116,8 +121,10 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
         asm volatile("prefetch.tensormap [%0];" ::"l"(&x_map) : "memory");
     tc_fence_before();
     __syncthreads();
+    if constexpr (CL2) cluster_sync_all();   // the peer's barriers exist before anything is multicast into this CTA
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    const uint32_t crank = CL2 ? cluster_ctarank() : 0u;
 
     if (warp == 0) {
         // ===== TMA producer: x tiles [TM tokens][64 k] =====
@@ -127,7 +134,12 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
             for (int kb = 0; kb < KBLKS; ++kb) {
                 mbar_wait(empty + 8 * s, ph ^ 1);
                 if (elect_one()) {
-                    if ((p.debug & 1) && kb >= S) {
+                    if constexpr (CL2) {
+                        // both halves of the tile land in THIS CTA's stage (own load + the peer's multicast): 32 KB expected
+                        mbar_arrive_expect_tx(full + 8 * s, C::B_STAGE_BYTES);
+                        tma_load_2d_mc(smem_b + s * C::B_STAGE_BYTES + crank * (C::B_STAGE_BYTES / 2), &x_map, (kb0 + kb) * PF_BLOCK_K,
+                                       m_tile * TM + (int)crank * (TM / 2), full + 8 * s, (uint16_t)3);
+                    } else if ((p.debug & 1) && kb >= S) {
                         mbar_arrive(full + 8 * s);
                     } else {
                         mbar_arrive_expect_tx(full + 8 * s, C::B_STAGE_BYTES);
@@ -163,7 +175,8 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
                     for (int k = 0; k < PF_BLOCK_K / 16; ++k)   // +32 bytes of k inside the swizzle atom = +2 in the address field
                         tc_mma_ts(tmem_base, a_tmem + k * 8, bdesc + 2 * k, idesc, (uint32_t)((kb | k) != 0));
                     if (prof) { long long c1 = clock64(); w_m += c1 - c0; c0 = c1; }
-                    tc_commit(empty + 8 * s);                   // frees the A columns and the B tile of this stage
+                    if constexpr (CL2) tc_commit_mc(empty + 8 * s, (uint16_t)3);   // ... in both CTAs: the peer multicasts into this stage too
+                    else tc_commit(empty + 8 * s);              // frees the A columns and the B tile of this stage
                     if (kb == KBLKS - 1) tc_commit(tmem_full);  // accumulator complete
                     if (prof) w_c += clock64() - c0;
                 }
@@ -379,6 +392,7 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
 
     tc_fence_before();
     __syncthreads();
+    if constexpr (CL2) cluster_sync_all();   // the peer may still signal this CTA's barriers
     if (warp == 2) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
@@ -423,18 +437,52 @@ int encode_x_map(CUtensorMap *map, const __nv_bfloat16 *x, int64_t K, int64_t M,
     return 0;
 }
 
-template <int TM, int GPS>
-static int launch_pf(const CUtensorMap &map, const PrefillParams &p, int grid, cudaStream_t stream) {
+template <int TM, int GPS, bool CL2>
+static int launch_pf(const CUtensorMap &map, const PrefillParams &p, int grid, int device, cudaStream_t stream) {
     using C = PfCfg<TM>;
-    static std::once_flag once;
-    static cudaError_t attr_err = cudaSuccess;
-    std::call_once(once, [] {
-        attr_err = cudaFuncSetAttribute(prefill_kernel<TM, GPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
-    });
-    if (attr_err != cudaSuccess)
-        return fail(std::string("cudaFuncSetAttribute(prefill_kernel smem): ") + cudaGetErrorString(attr_err));
-    prefill_kernel<TM, GPS><<<grid, PF_THREADS, C::SMEM_BYTES, stream>>>(map, p);
-    W4_CUDA_OK(cudaGetLastError());
+    static cudaError_t attr_err[64];
+    static int max_clusters[64];
+    static bool attr_done[64] = {};
+    static std::mutex mu;
+    if (device < 0 || device >= 64) return fail("launch_prefill: device index out of range");
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (!attr_done[device]) {   // per device
+            attr_err[device] = cudaFuncSetAttribute(prefill_kernel<TM, GPS, CL2>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
+            max_clusters[device] = 0;
+            if (CL2 && attr_err[device] == cudaSuccess) {
+                cudaLaunchConfig_t q{};
+                q.gridDim = dim3(2); q.blockDim = dim3(PF_THREADS); q.dynamicSmemBytes = C::SMEM_BYTES;
+                cudaLaunchAttribute qa[1];
+                qa[0].id = cudaLaunchAttributeClusterDimension;
+                qa[0].val.clusterDim.x = 2; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
+                q.attrs = qa; q.numAttrs = 1;
+                int n = 0;
+                if (cudaOccupancyMaxActiveClusters(&n, prefill_kernel<TM, GPS, CL2>, &q) != cudaSuccess) { cudaGetLastError(); n = 0; }
+                max_clusters[device] = n;
+            }
+            attr_done[device] = true;
+        }
+    }
+    if (attr_err[device] != cudaSuccess)
+        return fail(std::string("cudaFuncSetAttribute(prefill_kernel smem): ") + cudaGetErrorString(attr_err[device]));
+    if (!CL2) {
+        prefill_kernel<TM, GPS, CL2><<<grid, PF_THREADS, C::SMEM_BYTES, stream>>>(map, p);
+        W4_CUDA_OK(cudaGetLastError());
+        count_launch();
+        return 0;
+    }
+    if (max_clusters[device] < 1) return 2;   // clusters of two cannot be scheduled here: the caller falls back
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)std::min(grid & ~1, 2 * max_clusters[device]));
+    cfg.blockDim = dim3(PF_THREADS);
+    cfg.dynamicSmemBytes = C::SMEM_BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    W4_CUDA_OK(cudaLaunchKernelEx(&cfg, prefill_kernel<TM, GPS, CL2>, map, p));
     count_launch();
     return 0;
 }
@@ -533,29 +581,39 @@ int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
         p.dbg = dbg_buf;
     }
 
-    CUtensorMap map;
-    const cuuint64_t gdim[2] = {(cuuint64_t)L.d.K, (cuuint64_t)M};
-    const cuuint64_t gstride[1] = {(cuuint64_t)L.d.K * 2};
-    const cuuint32_t box[2] = {(cuuint32_t)PF_BLOCK_K, (cuuint32_t)TM};
-    const cuuint32_t estride[2] = {1, 1};
-    CUresult r = g_encode(&map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16 *>(x), gdim, gstride, box,
-                          estride, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                          CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled(x) failed with CUresult " + std::to_string((int)r));
-
     const int ntiles = p.n_tiles * p.m_tiles * p.ksplit;
     const int grid = std::min(ntiles, L.scratch->sm_count);
     const int gps = gs == 32 ? 2 : 1;
-#define W4_PF(TM_)                                                          \
-    do {                                                                    \
-        if (gps == 1) return launch_pf<TM_, 1>(map, p, grid, stream);       \
-        return launch_pf<TM_, 2>(map, p, grid, stream);                     \
+    // pairs of CTAs share every x tile (TMA multicast) when the two n-tiles of a pair exist for every m-tile
+    static const bool no_cl2 = getenv("W4A16_PF_NO_CLUSTER") && atoi(getenv("W4A16_PF_NO_CLUSTER"));
+    bool cl2 = TM == 256 && p.ksplit == 1 && (p.n_tiles % 2) == 0 && grid >= 2 && !no_cl2 && !(p.debug & 3);
+
+    int rc = 2;
+    for (int attempt = 0; attempt < 2 && rc == 2; ++attempt) {
+        CUtensorMap map;
+        const cuuint64_t gdim[2] = {(cuuint64_t)L.d.K, (cuuint64_t)M};
+        const cuuint64_t gstride[1] = {(cuuint64_t)L.d.K * 2};
+        const cuuint32_t box[2] = {(cuuint32_t)PF_BLOCK_K, (cuuint32_t)(cl2 ? TM / 2 : TM)};
+        const cuuint32_t estride[2] = {1, 1};
+        CUresult r = g_encode(&map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16 *>(x), gdim, gstride, box,
+                              estride, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled(x) failed with CUresult " + std::to_string((int)r));
+        if (cl2) {
+            rc = gps == 1 ? launch_pf<256, 1, true>(map, p, grid, L.device, stream) : launch_pf<256, 2, true>(map, p, grid, L.device, stream);
+            if (rc == 2) cl2 = false;   // no room for clusters of two on this device: plain launch
+            continue;
+        }
+#define W4_PF(TM_)                                                                          \
+    do {                                                                                    \
+        if (gps == 1) return launch_pf<TM_, 1, false>(map, p, grid, L.device, stream);      \
+        return launch_pf<TM_, 2, false>(map, p, grid, L.device, stream);                    \
     } while (0)
-    int rc;
-    if (TM == 256) rc = [&] { W4_PF(256); }();
-    else if (TM == 128) rc = [&] { W4_PF(128); }();
-    else rc = [&] { W4_PF(64); }();
+        if (TM == 256) rc = [&] { W4_PF(256); }();
+        else if (TM == 128) rc = [&] { W4_PF(128); }();
+        else rc = [&] { W4_PF(64); }();
 #undef W4_PF
+    }
     if (rc == 0 && (p.debug & 4)) {
         static unsigned long long h[256 * 8];
         W4_CUDA_OK(cudaStreamSynchronize(stream));
