@@ -105,6 +105,53 @@ int w4a16_load_gptq(w4a16_handle_t h, const uint32_t *qweight /*[K/8,N]*/,
                     const int32_t *g_idx /*[K] device, or NULL*/, const void *bias, int bias_dtype,
                     w4a16_stream_t stream);
 
+/* -- fused sibling projections and the SwiGLU epilogue -------
+ * The reference runs the sibling projections of one input as separate quantized linears:
+ * q_proj / k_proj / v_proj (qwen3_quantized.rs:84-96 create them one by one, :179-181 run
+ * them), gate_proj / up_proj followed by fused_swiglu or silu * mul
+ * (qwen3_quantized.rs:532-551, swiglu.cu:14-46).  One handle of width sum(n_part) loaded
+ * from the siblings' separate checkpoints replaces the 2-3 launches by one: part p fills
+ * output columns [n_begin, n_begin + n_part) from a checkpoint that is n_part columns wide
+ * (the same tensors w4a16_load_awq / _gptq take for a linear of that width).  n_begin and
+ * n_part are multiples of 16; the handle is unsharded (W4A16_TP_NONE; sharded siblings are
+ * sharded by the caller: each rank loads its column slice of every sibling as a part of a
+ * local handle).  The handle counts as loaded once the parts cover every column exactly
+ * once; loading the same part again overwrites it in place.  GPTQ parts must bring the same
+ * g_idx (they share x, so one gather serves all).  bias: the part's own [n_part] vector.
+ * The result is bit-identical to one linear loaded from the column-wise concatenated
+ * checkpoint (tests/test_fused_gpu.py).                                        */
+int w4a16_load_awq_part(w4a16_handle_t h, int64_t n_begin, int64_t n_part, const uint32_t *qweight,
+                        const uint32_t *qzeros, const void *scales, int scales_dtype, const void *bias,
+                        int bias_dtype, w4a16_stream_t stream);
+int w4a16_load_gptq_part(w4a16_handle_t h, int64_t n_begin, int64_t n_part, const uint32_t *qweight,
+                         const uint32_t *qzeros, const void *scales, int scales_dtype,
+                         const int32_t *g_idx, const void *bias, int bias_dtype, w4a16_stream_t stream);
+/* W4A16_EPILOGUE_SWIGLU: the handle holds gate_proj (part at n_begin = 0) and up_proj (part at
+ * n_begin = I) of one MLP, I = out_features / 2 at creation, I % 8 == 0, and its forward
+ * writes y[M, I] = bf16( silu_f32(gate) * f32(up) ), gate and up being the two projections
+ * ROUNDED TO BF16 first (with their bias, if any) -- the tensors the reference hands to
+ * fused_swiglu_bf16 (swiglu.cu:40-45: silu(x) = x / (1 + expf(-x)) in fp32, one bf16
+ * rounding of the product).  The resident layout interleaves the two projections (gate
+ * column c and up column c share a 16-row block), so the pair meets in one thread's
+ * registers and the [M, 2I] intermediate never exists.  Call before any load; loads go
+ * through w4a16_load_*_part only.  w4a16_out_features then reports I, w4a16_weight_rows
+ * 2I; the parity hooks answer in [gate | up] column order.  Forward: w4a16_forward_into
+ * only (no ROW/fused all-reduce: the handle is unsharded).                    */
+enum w4a16_epilogue { W4A16_EPILOGUE_NONE = 0, W4A16_EPILOGUE_SWIGLU = 1 };
+int w4a16_set_epilogue(w4a16_handle_t h, int epilogue);
+
+/* -- cache of the resident layout -----------------------------
+ * The reference repacks at every start (AwqMarlinLinear::load_weights,
+ * awq_marlin.rs:580-667).  save_tiled writes a loaded handle's resident bytes (header +
+ * qw | meta | bias | perm, checksummed; written to path.tmp and renamed) and load_tiled
+ * reads them into a handle created with the SAME geometry, format, bias flag, shard and
+ * epilogue: every header field is compared and a mismatch is an error naming the field.
+ * fingerprint: the caller's identity of the source checkpoint (e.g. a hash of the
+ * safetensors header); 0 on load skips that one check.  After load_tiled the handle is
+ * bit-identical to a freshly repacked one (tests/test_cache_gpu.py).           */
+int w4a16_save_tiled(w4a16_handle_t h, const char *path, uint64_t fingerprint);
+int w4a16_load_tiled(w4a16_handle_t h, const char *path, uint64_t fingerprint, w4a16_stream_t stream);
+
 /* -- forward ----------------------------------------------------------------
  * QuantizedLinear::forward(&Tensor) (config.rs:149) as it is executed by
  * MarlinLinear::forward -> marlin_gemm_pooled / marlin_gemm (marlin.rs:741-754,
@@ -196,7 +243,8 @@ int w4a16_scales_into(w4a16_handle_t h, void *scales_bf16, w4a16_stream_t stream
 
 /* -- introspection ----------------------------------------------------------- */
 int64_t w4a16_in_features(w4a16_handle_t h);   /* local K */
-int64_t w4a16_out_features(w4a16_handle_t h);  /* local N */
+int64_t w4a16_out_features(w4a16_handle_t h);  /* local N: the width of y (I for a SwiGLU handle) */
+int64_t w4a16_weight_rows(w4a16_handle_t h);   /* columns of W held (2I for a SwiGLU handle, else = out_features) */
 int w4a16_has_bias(w4a16_handle_t h);
 int64_t w4a16_weight_bytes(w4a16_handle_t h);  /* resident bytes of the repacked layout */
 /* Kernels launched by this library in this process so far (bench.py's gpu_launches). */

@@ -292,6 +292,21 @@ def np_gemm_ref(x_f32, q, z, scales_f32, group_size, g_idx=None, bias_f32=None, 
     return y
 
 
+def np_swiglu_bf16(gate_bits: np.ndarray, up_bits: np.ndarray) -> np.ndarray:
+    """silu(gate) * up on bf16 tensors, fp32 inside, one rounding to bf16: fused_swiglu_bf16 (swiglu.cu:17-19, 40-45)
+    == silu_and_mul_separate_bf16 (activations.cu:34-36, 148-164), the kernel QuantizedSwiGluMlp::forward launches
+    between gate_proj / up_proj and down_proj (qwen3_quantized.rs:532-551).  silu(x) = x / (1 + expf(-x)).
+    The reference builds its kernels with --use_fast_math (build.rs:335-339: ex2.approx / rcp.approx), so the GPU
+    result may differ from this exact-libm restatement in the last fp32 bits: after the bf16 rounding that is at most
+    one bf16 ulp on a small fraction of elements (tests/test_fused_gpu.py pins the product bit-for-bit against the
+    reference kernel itself and against this function within one ulp)."""
+    g = np_bf16_bits_to_f32(gate_bits).astype(np.float32)
+    u = np_bf16_bits_to_f32(up_bits).astype(np.float32)
+    with np.errstate(over="ignore"):
+        s = (g / (np.float32(1.0) + np.exp(-g, dtype=np.float32))).astype(np.float32)
+    return np_f32_to_bf16_bits((s * u).astype(np.float32))
+
+
 def reference_tolerance(expected: np.ndarray) -> float:
     """max(0.01 * max|expected|, 5e-2): marlin_cuda.rs:2168-2183, 2598-2611."""
     return max(0.01 * float(np.max(np.abs(expected))), 5e-2)

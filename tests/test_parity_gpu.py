@@ -490,7 +490,8 @@ def test_imma2_k4096_all_group_sizes(product, M, g):
     at g = 32 / 64; bias; a row-block count that is not a multiple of the grid (uneven slots per CTA)."""
     K, N = 4096, 4736
     lin, (qweight, qzeros, scales, bias) = make_awq_layer(product, K, N, g, seed=61 + g + M, bias=True)
-    assert lin.kernel_for(M) == "gemv_stream_imma2"
+    # g = 32 / 64 with 3-4 tokens: the staging no longer fits twice per SM and the plan hands the shape to the first kernel
+    assert lin.kernel_for(M) in (("gemv_stream_imma2",) if g == 128 or M <= 2 else ("gemv_stream_imma2", "gemv_stream_imma"))
     q, z, sb = awq_unpacked(qweight, qzeros, scales)
     xb = O.make_activations(M, K, seed=300 + M)
     y = torch.full((M, N), float("nan"), dtype=torch.bfloat16, device=DEV)

@@ -10,8 +10,9 @@ from .quantization import (  # noqa: F401
     B200W4A16Linear, check_marlin_supports_shape,
     AwqWeightLoader, GptqWeightLoader, create_weight_loader_with_params,
     detect_from_json, detect_from_directory, is_supported, create_config, kernel_launches, set_dispatch,
-    DetectedQuantConfig,
+    DetectedQuantConfig, EPILOGUE_NONE, EPILOGUE_SWIGLU,
 )
+from .checkpoint import SafetensorsCheckpoint, load_decoder_linears, save_safetensors, save_sharded  # noqa: F401
 from .parallel import (  # noqa: F401
     DeviceCommunicator, MockCommunicator, NcclCommunicator, PeerGroup, TorchDistCommunicator,
     ColumnParallelW4A16Linear, RowParallelW4A16Linear, shard_range,

@@ -45,6 +45,11 @@ SIGNATURES = {
     "w4a16_destroy": (_i32, [_vp]),
     "w4a16_load_awq": (_i32, [_vp, _vp, _vp, _vp, _i32, _vp, _i32, _vp]),
     "w4a16_load_gptq": (_i32, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _vp]),
+    "w4a16_load_awq_part": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp, _i32, _vp, _i32, _vp]),
+    "w4a16_load_gptq_part": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _vp]),
+    "w4a16_set_epilogue": (_i32, [_vp, _i32]),
+    "w4a16_save_tiled": (_i32, [_vp, ctypes.c_char_p, _u64]),
+    "w4a16_load_tiled": (_i32, [_vp, ctypes.c_char_p, _u64, _vp]),
     "w4a16_forward_into": (_i32, [_vp, _vp, _vp, _i64, _vp]),
     "w4a16_forward_host": (_i32, [_vp, _vp, _vp, _i64, _vp]),
     "w4a16_forward_row_allreduce": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp]),
@@ -64,6 +69,7 @@ SIGNATURES = {
     "w4a16_scales_into": (_i32, [_vp, _vp, _vp]),
     "w4a16_in_features": (_i64, [_vp]),
     "w4a16_out_features": (_i64, [_vp]),
+    "w4a16_weight_rows": (_i64, [_vp]),
     "w4a16_has_bias": (_i32, [_vp]),
     "w4a16_weight_bytes": (_i64, [_vp]),
     "w4a16_kernel_launches": (_u64, []),

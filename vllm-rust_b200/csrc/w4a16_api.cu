@@ -89,15 +89,57 @@ static void free_linear(Linear *L) {
     delete L;
 }
 
-static int finish_load(Linear *L, const void *bias, int bias_dtype, cudaStream_t stream) {
+// One column part of a fused handle (w4a16_load_*_part): destination columns [n_begin, n_begin + n_part) from a
+// checkpoint of width n_part.  whole(): the ordinary single-checkpoint load.
+struct Part {
+    int64_t n_begin = 0, n_part = 0;
+    bool is_part = false;
+};
+
+static int finish_load(Linear *L, const void *bias, int bias_dtype, cudaStream_t stream, const Part &pt = Part()) {
+    const bool swiglu = L->epilogue == W4A16_EPILOGUE_SWIGLU;
     if (L->has_bias) {
         if (!bias) return fail("load_weights: layer was created with bias but none was given");
         // bias is per output feature: a COLUMN shard keeps its slice, a ROW shard keeps all of it
         size_t esz = bias_dtype == W4A16_DTYPE_F32 ? 4 : 2;
-        const char *src = reinterpret_cast<const char *>(bias) + (size_t)L->n_off * esz;
-        if (launch_convert_bias(src, bias_dtype, L->bias, L->d.N, stream)) return 1;
+        if (!pt.is_part) {
+            const char *src = reinterpret_cast<const char *>(bias) + (size_t)L->n_off * esz;
+            if (launch_convert_bias(src, bias_dtype, L->bias, L->d.N, stream)) return 1;
+        } else if (swiglu) {
+            if (launch_convert_bias(bias, bias_dtype, L->bias, pt.n_part, stream, pt.n_begin ? 1 : 0)) return 1;
+        } else {
+            if (launch_convert_bias(bias, bias_dtype, L->bias + pt.n_begin, pt.n_part, stream)) return 1;
+        }
     }
-    L->loaded = true;
+    if (!pt.is_part) { L->loaded = true; return 0; }
+    // a part: the handle is loaded once the parts cover every column exactly once
+    for (int i = 0; i < L->n_parts_loaded; ++i)
+        if (L->part_cols[i][0] == pt.n_begin && L->part_cols[i][1] == pt.n_part) return 0;   // reloaded in place
+    L->part_cols[L->n_parts_loaded][0] = pt.n_begin; L->part_cols[L->n_parts_loaded][1] = pt.n_part;
+    ++L->n_parts_loaded;
+    int64_t covered = 0;
+    for (int i = 0; i < L->n_parts_loaded; ++i) covered += L->part_cols[i][1];
+    L->loaded = covered == L->d.N;
+    return 0;
+}
+
+static int check_part(Linear *L, int64_t n_begin, int64_t n_part, Part *pt) {
+    if (L->tp_mode != W4A16_TP_NONE) return fail("load_part: fused sibling parts need an unsharded handle");
+    if (n_begin < 0 || n_part <= 0 || n_begin + n_part > L->d.N) return fail("load_part: columns out of range");
+    if (L->epilogue == W4A16_EPILOGUE_SWIGLU) {
+        if (n_part * 2 != L->d.N || (n_begin != 0 && n_begin != n_part))
+            return fail("load_part: a SwiGLU handle takes exactly two parts of out_features / 2 columns: gate at 0, up at out_features / 2");
+    } else if (n_begin % CHUNK_N || n_part % CHUNK_N) {
+        return fail("load_part: part boundaries must be multiples of 16 columns");
+    }
+    bool again = false;   // checked BEFORE the repack writes anything
+    for (int i = 0; i < L->n_parts_loaded; ++i) {
+        if (L->part_cols[i][0] == n_begin && L->part_cols[i][1] == n_part) { again = true; continue; }
+        if (n_begin < L->part_cols[i][0] + L->part_cols[i][1] && L->part_cols[i][0] < n_begin + n_part)
+            return fail("load_part: the part overlaps columns that another part has filled");
+    }
+    if (!again && L->n_parts_loaded >= 8) return fail("load_part: more than 8 parts");
+    pt->n_begin = n_begin; pt->n_part = n_part; pt->is_part = true;
     return 0;
 }
 
@@ -175,6 +217,8 @@ static int pick_route(const Linear &L, int64_t M) {
     return M > decode_max ? ROUTE_PREFILL : ROUTE_DECODE;
 }
 
+static inline int64_t out_width(const Linear &L) { return L.epilogue == W4A16_EPILOGUE_SWIGLU ? L.d.N / 2 : L.d.N; }
+
 static int forward_local(Linear *L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
                          cudaStream_t stream) {
     if (!L->loaded) return fail("forward: weights not loaded (call load_weights first)");
@@ -192,7 +236,7 @@ static int forward_local(Linear *L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
     if (route == ROUTE_PREFILL) return launch_prefill(*L, x, y, M, add_bias, stream);
     for (int64_t m0 = 0; m0 < M; m0 += DECODE_MAX_M) {
         int64_t mm = std::min<int64_t>(DECODE_MAX_M, M - m0);
-        if (launch_decode(*L, x + m0 * L->d.K, y + m0 * L->d.N, mm, add_bias, stream)) return 1;
+        if (launch_decode(*L, x + m0 * L->d.K, y + m0 * out_width(*L), mm, add_bias, stream)) return 1;
     }
     return 0;
 }
@@ -276,7 +320,7 @@ int w4a16_destroy(w4a16_handle_t h) {
 
 static int load_common(Linear *L, int format_expected_min, int format_expected_max, const uint32_t *qweight,
                        const uint32_t *qzeros, const void *scales, int scales_dtype, const int32_t *perm_dev,
-                       const int32_t *grp_dev, cudaStream_t stream) {
+                       const int32_t *grp_dev, cudaStream_t stream, const Part &pt = Part()) {
     if (L->format < format_expected_min || L->format > format_expected_max)
         return fail("load_weights: handle was created for a different checkpoint format");
     if (!qweight) return fail("load_weights: missing 'qweight'");
@@ -290,28 +334,56 @@ static int load_common(Linear *L, int format_expected_min, int format_expected_m
     src.G_full = L->K_full / src.gs;
     src.k_off = L->k_off; src.n_off = L->n_off;
     src.perm = perm_dev; src.row_group = grp_dev;
+    if (pt.is_part) {   // the part's checkpoint is n_part wide and starts at its own column 0
+        src.N_full = pt.n_part; src.n_off = 0;
+        if (L->epilogue == W4A16_EPILOGUE_SWIGLU) { src.half = pt.n_begin ? 1 : 0; src.dst_R0 = 0; src.NR_part = L->d.NR; }
+        else { src.dst_R0 = pt.n_begin / CHUNK_N; src.NR_part = pt.n_part / CHUNK_N; }
+    } else if (L->epilogue != W4A16_EPILOGUE_NONE) {
+        return fail("load_weights: a SwiGLU handle is loaded through w4a16_load_*_part (gate, then up)");
+    }
     return launch_repack(*L, src, stream);
+}
+
+static int load_awq_impl(Linear *L, const Part &pt, const uint32_t *qweight, const uint32_t *qzeros, const void *scales,
+                         int scales_dtype, const void *bias, int bias_dtype, cudaStream_t s) {
+    DeviceGuard g(L->device);
+    if (load_common(L, W4A16_FORMAT_AWQ, W4A16_FORMAT_AWQ, qweight, qzeros, scales, scales_dtype, nullptr, nullptr, s, pt))
+        return 1;
+    return finish_load(L, bias, bias_dtype, s, pt);
 }
 
 int w4a16_load_awq(w4a16_handle_t h, const uint32_t *qweight, const uint32_t *qzeros, const void *scales,
                    int scales_dtype, const void *bias, int bias_dtype, w4a16_stream_t stream) {
     Linear *L = reinterpret_cast<Linear *>(h);
     if (!L) return fail("load_awq: null handle");
-    DeviceGuard g(L->device);
-    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-    if (load_common(L, W4A16_FORMAT_AWQ, W4A16_FORMAT_AWQ, qweight, qzeros, scales, scales_dtype, nullptr, nullptr, s))
-        return 1;
-    return finish_load(L, bias, bias_dtype, s);
+    return load_awq_impl(L, Part(), qweight, qzeros, scales, scales_dtype, bias, bias_dtype, reinterpret_cast<cudaStream_t>(stream));
 }
 
-int w4a16_load_gptq(w4a16_handle_t h, const uint32_t *qweight, const uint32_t *qzeros, const void *scales,
-                    int scales_dtype, const int32_t *g_idx, const void *bias, int bias_dtype,
-                    w4a16_stream_t stream) {
+int w4a16_load_awq_part(w4a16_handle_t h, int64_t n_begin, int64_t n_part, const uint32_t *qweight, const uint32_t *qzeros,
+                        const void *scales, int scales_dtype, const void *bias, int bias_dtype, w4a16_stream_t stream) {
     Linear *L = reinterpret_cast<Linear *>(h);
-    if (!L) return fail("load_gptq: null handle");
+    if (!L) return fail("load_awq_part: null handle");
+    Part pt;
+    if (check_part(L, n_begin, n_part, &pt)) return 1;
+    return load_awq_impl(L, pt, qweight, qzeros, scales, scales_dtype, bias, bias_dtype, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int w4a16_set_epilogue(w4a16_handle_t h, int epilogue) {
+    Linear *L = reinterpret_cast<Linear *>(h);
+    if (!L) return fail("set_epilogue: null handle");
+    if (epilogue != W4A16_EPILOGUE_NONE && epilogue != W4A16_EPILOGUE_SWIGLU) return fail("set_epilogue: unknown epilogue");
+    if (L->loaded || L->n_parts_loaded) return fail("set_epilogue: must be called before any weights are loaded");
+    if (epilogue == W4A16_EPILOGUE_SWIGLU && L->tp_mode != W4A16_TP_NONE) return fail("set_epilogue: a SwiGLU handle must be unsharded");
+    L->epilogue = epilogue;
+    return 0;
+}
+
+static int load_gptq_impl(Linear *L, const Part &pt, const uint32_t *qweight, const uint32_t *qzeros, const void *scales,
+                          int scales_dtype, const int32_t *g_idx, const void *bias, int bias_dtype, cudaStream_t s) {
     DeviceGuard g(L->device);
-    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     const int32_t *perm_dev = nullptr, *grp_dev = nullptr;
+    if (pt.is_part && L->n_parts_loaded > 0 && (g_idx != nullptr) != !L->part_g_idx.empty())
+        return fail("load_gptq_part: every part of a fused handle must bring the same g_idx (one has it, another does not)");
     if (g_idx) {
         // g_idx is the FULL [K_full] tensor.  The rows are sorted by group over the whole K (stable), THEN sharded
         // ("permute at load before sharding"): a ROW shard keeps sorted rows [k_off, k_off + K_local), i.e.
@@ -328,7 +400,14 @@ int w4a16_load_gptq(w4a16_handle_t h, const uint32_t *qweight, const uint32_t *q
             if (gi[k] < 0 || gi[k] >= Gf) return fail("load_gptq: g_idx entry out of range");
             if (gi[k] != k / gs) trivial = false;
         }
-        if (!trivial) {
+        if (pt.is_part) {   // sibling projections share their input: one permutation of x serves all parts
+            if (L->n_parts_loaded > 0 && L->part_g_idx != gi)
+                return fail("load_gptq_part: every part of a fused handle must bring the same g_idx");
+            L->part_g_idx = gi;
+        }
+        if (!trivial && pt.is_part && L->perm) {
+            perm_dev = L->perm; grp_dev = L->perm + L->d.K;   // built by the first part
+        } else if (!trivial) {
             std::vector<int32_t> full((size_t)Kf);
             std::vector<int64_t> count((size_t)Gf, 0);
             for (int64_t k = 0; k < Kf; ++k) ++count[gi[k]];
@@ -351,9 +430,27 @@ int w4a16_load_gptq(w4a16_handle_t h, const uint32_t *qweight, const uint32_t *q
         }
     }
     if (load_common(L, W4A16_FORMAT_GPTQ_ZP, W4A16_FORMAT_GPTQ_SYM, qweight, qzeros, scales, scales_dtype, perm_dev,
-                    grp_dev, s))
+                    grp_dev, s, pt))
         return 1;
-    return finish_load(L, bias, bias_dtype, s);
+    return finish_load(L, bias, bias_dtype, s, pt);
+}
+
+int w4a16_load_gptq(w4a16_handle_t h, const uint32_t *qweight, const uint32_t *qzeros, const void *scales,
+                    int scales_dtype, const int32_t *g_idx, const void *bias, int bias_dtype,
+                    w4a16_stream_t stream) {
+    Linear *L = reinterpret_cast<Linear *>(h);
+    if (!L) return fail("load_gptq: null handle");
+    return load_gptq_impl(L, Part(), qweight, qzeros, scales, scales_dtype, g_idx, bias, bias_dtype, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int w4a16_load_gptq_part(w4a16_handle_t h, int64_t n_begin, int64_t n_part, const uint32_t *qweight, const uint32_t *qzeros,
+                         const void *scales, int scales_dtype, const int32_t *g_idx, const void *bias, int bias_dtype,
+                         w4a16_stream_t stream) {
+    Linear *L = reinterpret_cast<Linear *>(h);
+    if (!L) return fail("load_gptq_part: null handle");
+    Part pt;
+    if (check_part(L, n_begin, n_part, &pt)) return 1;
+    return load_gptq_impl(L, pt, qweight, qzeros, scales, scales_dtype, g_idx, bias, bias_dtype, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int w4a16_forward_into(w4a16_handle_t h, const void *x_bf16, void *y_bf16, int64_t M, w4a16_stream_t stream) {
@@ -375,7 +472,7 @@ int w4a16_forward_host(w4a16_handle_t h, const void *x_host, void *y_host, int64
     if (ensure_stage(L, M)) return 1;
     W4_CUDA_OK(cudaMemcpyAsync(L->stage_x, x_host, (size_t)M * L->d.K * 2, cudaMemcpyHostToDevice, s));
     if (w4a16_forward_into(h, L->stage_x, L->stage_y, M, stream)) return 1;
-    W4_CUDA_OK(cudaMemcpyAsync(y_host, L->stage_y, (size_t)M * L->d.N * 2, cudaMemcpyDeviceToHost, s));
+    W4_CUDA_OK(cudaMemcpyAsync(y_host, L->stage_y, (size_t)M * out_width(*L) * 2, cudaMemcpyDeviceToHost, s));
     W4_CUDA_OK(cudaStreamSynchronize(s));
     return 0;
 }
@@ -557,6 +654,7 @@ int w4a16_dequant_d1_into(w4a16_handle_t h, const void *scales, int scales_dtype
     if (!L || !L->loaded) return fail("dequant_d1_into: weights not loaded");
     if (!scales || !w_f16) return fail("dequant_d1_into: null scales or output");
     if (scales_dtype < W4A16_DTYPE_F16 || scales_dtype > W4A16_DTYPE_F32) return fail("dequant_d1_into: bad scales dtype");
+    if (L->n_parts_loaded) return fail("dequant_d1_into: a fused handle has one scales tensor per part; use the per-sibling handles");
     DeviceGuard g(L->device);
     return launch_dequant_d1(*L, scales, scales_dtype, reinterpret_cast<__half *>(w_f16), reinterpret_cast<cudaStream_t>(stream));
 }
@@ -588,7 +686,12 @@ int w4a16_scales_into(w4a16_handle_t h, void *scales_bf16, w4a16_stream_t stream
 }
 
 int64_t w4a16_in_features(w4a16_handle_t h) { return h ? reinterpret_cast<Linear *>(h)->d.K : -1; }
-int64_t w4a16_out_features(w4a16_handle_t h) { return h ? reinterpret_cast<Linear *>(h)->d.N : -1; }
+int64_t w4a16_out_features(w4a16_handle_t h) {   /* a SwiGLU handle writes silu(gate) * up: half as wide as its weights */
+    if (!h) return -1;
+    const Linear *L = reinterpret_cast<Linear *>(h);
+    return L->epilogue == W4A16_EPILOGUE_SWIGLU ? L->d.N / 2 : L->d.N;
+}
+int64_t w4a16_weight_rows(w4a16_handle_t h) { return h ? reinterpret_cast<Linear *>(h)->d.N : -1; }
 int w4a16_has_bias(w4a16_handle_t h) { return h ? (int)reinterpret_cast<Linear *>(h)->has_bias : 0; }
 int64_t w4a16_weight_bytes(w4a16_handle_t h) {
     if (!h) return -1;

@@ -46,6 +46,7 @@ struct DecodeParams {
     int wk_shift;          // log2(warps along K inside a CTA)
     int sc;                // CTAs along K
     int ups;               // units per slice
+    int swiglu;            // SwiGLU handle: rows g / g+8 are (gate, up), y is [M, N/2] (w4a16_epilogue.cuh)
 };
 
 __device__ __forceinline__ uint4 ldg_stream(const uint4 *p) {
@@ -152,6 +153,16 @@ __device__ __forceinline__ void store_fragment(const DecodeParams &p, int R, int
     const int n0 = R * 16 + g;
     const float b0 = p.bias ? __bfloat162float(p.bias[n0]) : 0.f;
     const float b1 = p.bias ? __bfloat162float(p.bias[n0 + 8]) : 0.f;
+    if (p.swiglu) {
+        const size_t I = (size_t)(p.N >> 1), c = (size_t)R * 8 + g;
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            const int tok = nt * 8 + 2 * t;
+            if (tok < p.M) p.y[(size_t)tok * I + c] = swiglu_bf16(v[nt].x + b0, v[nt].z + b1);
+            if (tok + 1 < p.M) p.y[(size_t)(tok + 1) * I + c] = swiglu_bf16(v[nt].y + b0, v[nt].w + b1);
+        }
+        return;
+    }
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
         const int tok = nt * 8 + 2 * t;
@@ -360,6 +371,7 @@ int launch_decode(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int
     p.x = x; p.y = y;
     p.scratch = reinterpret_cast<float4 *>(L.splitk_scratch); p.tickets = L.tickets;
     p.M = (int)M; p.K = (int)L.d.K; p.N = (int)L.d.N; p.KB = (int)L.d.KB; p.G = (int)L.d.G;
+    p.swiglu = L.epilogue == W4A16_EPILOGUE_SWIGLU;
     if (gs != 32 && gs != 64 && gs != 128 && gs != L.d.K) return fail("launch_decode: unsupported group size");
     const int mpu = gs == 32 ? 4 : gs == 64 ? 2 : 1;
     p.meta_unit_stride = gs == L.d.K && gs != 128 ? 0 : mpu * META_BYTES;  // per-channel: one group for all of K

@@ -456,6 +456,12 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 8 ? 2 : 1) gemv_stream_kerne
         const int tok = 2 * pp;
         const float b0 = p.bias ? __bfloat162float(p.bias[n0]) : 0.f;
         const float b1 = p.bias ? __bfloat162float(p.bias[n0 + 8]) : 0.f;
+        if (p.swiglu) {   // rows g / g+8 are (gate, up) of output column 8 R + gg
+            const size_t I = (size_t)(p.N >> 1), c = (size_t)R * 8 + gg;
+            if (tok < p.M) p.y[(size_t)tok * I + c] = swiglu_bf16(v.x + b0, v.z + b1);
+            if (tok + 1 < p.M) p.y[(size_t)(tok + 1) * I + c] = swiglu_bf16(v.y + b0, v.w + b1);
+            return;
+        }
         if (tok < p.M) {
             p.y[(size_t)tok * p.N + n0] = __float2bfloat16_rn(v.x + b0);
             p.y[(size_t)tok * p.N + n0 + 8] = __float2bfloat16_rn(v.z + b1);
@@ -675,6 +681,7 @@ int launch_gemv_stream(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y
     p.tickets = L.tickets;
     p.tab = reinterpret_cast<const int4 *>(L.gv_tab);
     p.M = (int)M; p.K = (int)L.d.K; p.N = (int)L.d.N;
+    p.swiglu = L.epilogue == W4A16_EPILOGUE_SWIGLU;
     p.UPR = (int)(L.d.K / GV_UNIT_K);
     p.meta_stride = pl.stage_m_bytes ? mpu * META_BYTES : 0;
     p.P = pl.P;

@@ -1,6 +1,7 @@
 // w4a16_gemv_common.cuh -- parameters and PTX helpers shared by the decode stream kernels
 // (w4a16_gemv.cu: dp4a / mma.sync f16 path; w4a16_gemv_imma.cu: int8 tensor-core path for M <= 4).
 #pragma once
+#include "w4a16_epilogue.cuh"
 #include <stdlib.h>
 
 #include "w4a16_internal.cuh"
@@ -46,6 +47,7 @@ struct GemvParams {
     int32_t *tickets;           // [NR]
     const int4 *tab;            // [grid][2]: {a, b, first_lo, first_hi}, {last_lo, last_hi, -, -}
     int M, K, N;
+    int swiglu;                 // SwiGLU handle: rows g / g+8 are (gate, up); y is [M, N/2] (w4a16_epilogue.cuh)
     int UPR;                    // units per row block = K / 128
     int meta_stride;            // bytes of meta per unit (MPU*48), 0 for per-channel scales
     int P;                      // ceil(M/2): fragment column pairs that hold real tokens

@@ -432,8 +432,12 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 4 ? 2 : 1) gemv_imma_kernel(
         } else if (q == 0 && tok < p.M) {
             const float b0 = p.bias ? __bfloat162float(p.bias[n0]) : 0.f;
             const float b1 = p.bias ? __bfloat162float(p.bias[n0 + 8]) : 0.f;
-            p.y[(size_t)tok * p.N + n0] = __float2bfloat16_rn(v.x + b0);
-            p.y[(size_t)tok * p.N + n0 + 8] = __float2bfloat16_rn(v.y + b1);
+            if (p.swiglu) {   // rows g / g+8 are (gate, up) of output column 8 R + g
+                p.y[(size_t)tok * (p.N >> 1) + (n0 >> 4) * 8 + (n0 & 7)] = swiglu_bf16(v.x + b0, v.y + b1);
+            } else {
+                p.y[(size_t)tok * p.N + n0] = __float2bfloat16_rn(v.x + b0);
+                p.y[(size_t)tok * p.N + n0 + 8] = __float2bfloat16_rn(v.y + b1);
+            }
         }
     }
     if constexpr (FUSED) {
@@ -584,6 +588,7 @@ int launch_gemv_imma_peer(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16
     p.x = x; p.y = y;
     p.tab = reinterpret_cast<const int4 *>(L.gv_tab);
     p.M = (int)M; p.K = (int)L.d.K; p.N = (int)L.d.N;
+    p.swiglu = L.epilogue == W4A16_EPILOGUE_SWIGLU;
     p.UPR = (int)(L.d.K / GV_UNIT_K);
     p.meta_stride = pl.mpu * META_BYTES;
     p.n_stages_ring = pl.S;

@@ -8,7 +8,10 @@
 
 #include <atomic>
 #include <string>
+#include <vector>
 
+#include "../../include/w4a16_b200.h"
+#include "w4a16_epilogue.cuh"
 #include "w4a16_layout.cuh"
 
 namespace w4 {
@@ -56,6 +59,12 @@ struct Linear {
     float *splitk_scratch = nullptr;  // [SC][32][N] fp32 partials when the decode kernel splits K over CTAs
     int64_t splitk_floats = 0;
     bool loaded = false;
+    // fused sibling projections (w4a16_load_*_part): column intervals filled so far; epilogue 1 = SwiGLU pair (the handle
+    // holds gate rows in the g half and up rows in the g+8 half of every row block and writes silu(gate) * up, N / 2 wide)
+    int epilogue = 0;
+    int64_t part_cols[8][2] = {};
+    int n_parts_loaded = 0;
+    std::vector<int32_t> part_g_idx;   // act-order: every part must bring the same g_idx
     // scratch that scales with M
     __nv_bfloat16 *x_gather = nullptr;  // act-order gathered activations [cap, K]
     int64_t x_gather_cap = 0;
@@ -80,13 +89,15 @@ struct RepackSrc {
     int gs;                   // effective group size
     const int32_t *perm;      // device, local row i -> checkpoint row (already includes k_off) or null
     const int32_t *row_group; // device, local row i -> checkpoint group index (act-order) or null
+    int64_t dst_R0 = 0, NR_part = 0;   // column part: destination row blocks [dst_R0, dst_R0 + NR_part); 0 = the whole handle
+    int half = -1;                     // SwiGLU pair: 0 = gate rows (g), 1 = up rows (g + 8); -1 = plain
 };
 int launch_repack(const Linear &L, const RepackSrc &src, cudaStream_t stream);
 int launch_unpack(const Linear &L, uint8_t *q, uint8_t *z, cudaStream_t stream);
 int launch_dequant(const Linear &L, __nv_bfloat16 *w, cudaStream_t stream);
 int launch_scales_out(const Linear &L, __nv_bfloat16 *s, cudaStream_t stream);
 int launch_dequant_d1(const Linear &L, const void *scales, int scales_dtype, __half *w, cudaStream_t stream);
-int launch_convert_bias(const void *src, int dtype, __nv_bfloat16 *dst, int64_t n, cudaStream_t stream);
+int launch_convert_bias(const void *src, int dtype, __nv_bfloat16 *dst, int64_t n, cudaStream_t stream, int half = -1);
 int launch_gather_x(const __nv_bfloat16 *x, const int32_t *perm, __nv_bfloat16 *xg, int64_t M, int64_t K,
                     cudaStream_t stream);
 int launch_add_bias(__nv_bfloat16 *y, const __nv_bfloat16 *bias, int64_t M, int64_t N, cudaStream_t stream);

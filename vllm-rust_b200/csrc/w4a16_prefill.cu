@@ -32,6 +32,7 @@
 #include <mutex>
 
 #include "w4a16_dequant.cuh"
+#include "w4a16_epilogue.cuh"
 #include "w4a16_internal.cuh"
 #include "w4a16_tc.cuh"
 
@@ -56,6 +57,7 @@ struct PrefillParams {
     float *part;              // [ksplit][M][N] fp32 partial sums (ksplit > 1)
     int *tickets;             // [n_tiles * m_tiles] arrival counters, self-resetting
     unsigned long long *dbg;   // W4A16_PF_DEBUG & 4: per-CTA {cycles, ns, wait_full_b, wait_full_a, wait_tmem_empty, tiles}
+    int swiglu;        // SwiGLU handle: TMEM lanes l / l^8 are (gate, up); y is [M, N/2], 64 output columns per n-tile
     int debug;         // timing experiments only (W4A16_PF_DEBUG): 1 = skip x loads after the first k block, 2 = skip dequant
 };
 
@@ -326,6 +328,7 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
                     // 128 threads: 32 float4 columns x 4 rows per pass, every slice's loads issued before the sums
                     const int c4 = et & 31, r0 = et >> 5;
                     const int nn = n_tile * PF_TILE_N + c4 * 4;
+                    const unsigned act = __ballot_sync(0xffffffffu, nn < p.N);   // a half-full last tile: lanes 0..15
                     if (nn < p.N) {
                         float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
                         if (p.bias) {
@@ -351,6 +354,25 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
 #pragma unroll
                                 for (int i = 0; i < 8; ++i) { acc[i].x += v[i].x; acc[i].y += v[i].y; acc[i].z += v[i].z; acc[i].w += v[i].w; }
                             }
+                            if (p.swiglu) {   // columns nn.. (gate) and nn+8.. (up) sit two lanes apart
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) {
+                                    const int row = row0 + 4 * i;      // warp-uniform
+                                    if (row >= rows) continue;
+                                    const float4 a = make_float4(acc[i].x + b4.x, acc[i].y + b4.y, acc[i].z + b4.z, acc[i].w + b4.w);
+                                    float4 o;
+                                    o.x = __shfl_xor_sync(act, a.x, 2); o.y = __shfl_xor_sync(act, a.y, 2);
+                                    o.z = __shfl_xor_sync(act, a.z, 2); o.w = __shfl_xor_sync(act, a.w, 2);
+                                    if (!(c4 & 2)) {
+                                        __nv_bfloat162 lo = __halves2bfloat162(swiglu_bf16(a.x, o.x), swiglu_bf16(a.y, o.y));
+                                        __nv_bfloat162 hi = __halves2bfloat162(swiglu_bf16(a.z, o.z), swiglu_bf16(a.w, o.w));
+                                        uint2 out;
+                                        out.x = *reinterpret_cast<uint32_t *>(&lo); out.y = *reinterpret_cast<uint32_t *>(&hi);
+                                        *reinterpret_cast<uint2 *>(p.y + (size_t)(m_tile * TM + row) * (p.N >> 1) + (nn >> 4) * 8 + (nn & 7)) = out;
+                                    }
+                                }
+                                continue;
+                            }
 #pragma unroll
                             for (int i = 0; i < 8; ++i) {
                                 const int row = row0 + 4 * i;
@@ -365,6 +387,37 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
                         }
                     }
                 }
+                continue;
+            }
+            if (p.swiglu) {
+                // TMEM lane l holds gate column 8 (l / 16) + l % 8 when l & 8 == 0, lane l ^ 8 the matching up column.
+                // The pair splits the token rows: the gate lane finishes even rows, the up lane odd rows.
+                const bool up_lane = (lane & 8) != 0;
+                const int oc = (q * 2 + (lane >> 4)) * 8 + (lane & 7);
+#pragma unroll 1
+                for (int c = 0; c < TM / 32; ++c) {
+                    uint32_t v[32];
+                    tc_ld_32x32b_x32(tmem_base + ((uint32_t)(q * 32) << 16) + c * 32, v);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                    for (int i = 0; i < 32; i += 2) {
+                        const float a = __uint_as_float(v[i]) + bias, b = __uint_as_float(v[i + 1]) + bias;
+                        const float recv = __shfl_xor_sync(0xffffffffu, up_lane ? a : b, 8);
+                        smem_out[(c * 32 + i + (up_lane ? 1 : 0)) * PF_TILE_N + oc] = up_lane ? swiglu_bf16(recv, b) : swiglu_bf16(a, recv);
+                    }
+                }
+                tc_fence_before();
+                if (lane == 0) mbar_arrive(tmem_empty);
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                const int I = p.N >> 1;
+                __nv_bfloat16 *yb = p.y + (size_t)m_tile * TM * I + (size_t)n_tile * (PF_TILE_N / 2);
+                for (int idx = et; idx < rows * 8; idx += 128) {
+                    const int row = idx >> 3, c8 = idx & 7;
+                    if (n_tile * (PF_TILE_N / 2) + c8 * 8 < I)
+                        *reinterpret_cast<uint4 *>(yb + (size_t)row * I + c8 * 8) =
+                        *reinterpret_cast<const uint4 *>(smem_out + row * PF_TILE_N + c8 * 8);
+                }
+                asm volatile("bar.sync 1, 128;" ::: "memory");
                 continue;
             }
 #pragma unroll 1
@@ -533,6 +586,7 @@ int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
     p.bias = add_bias && L.has_bias ? L.bias : nullptr;
     p.y = y;
     p.M = (int)M; p.K = (int)L.d.K; p.N = (int)L.d.N; p.KB = (int)L.d.KB; p.G = (int)L.d.G;
+    p.swiglu = L.epilogue == W4A16_EPILOGUE_SWIGLU;
     p.gs_shift = gs == L.d.K && gs != 32 && gs != 64 && gs != 128 ? 31 : (gs == 32 ? 5 : gs == 64 ? 6 : 7);
     p.n_tiles = (int)((L.d.N + PF_TILE_N - 1) / PF_TILE_N);  // N % 64 == 0: the last tile may be half full
     p.m_tiles = (int)((M + TM - 1) / TM);

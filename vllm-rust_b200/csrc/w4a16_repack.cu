@@ -29,6 +29,12 @@ struct RepackParams {
     Dims d;
     uint32_t *qw;
     uint8_t *meta;
+    // column parts (fused sibling projections): this launch fills destination row blocks
+    // [dst_R0, dst_R0 + NR_part) from a checkpoint of its own (n_off = 0, N_full = the part's width).
+    // half = 0 / 1 (gate / up of a SwiGLU pair): the part's column c becomes row 16 (c / 8) + 8 half + c % 8, i.e. it fills
+    // one half (rows g or rows g+8) of EVERY row block, read-modify-write on the words both halves share; -1 = plain.
+    int64_t dst_R0, NR_part;
+    int half;
 };
 
 __device__ __forceinline__ uint32_t src_nibble(const RepackParams &p, int64_t k_local, int64_t n_local) {
@@ -43,21 +49,24 @@ __device__ __forceinline__ uint32_t src_nibble(const RepackParams &p, int64_t k_
 }
 
 __global__ void repack_qweight_kernel(RepackParams p) {
-    int64_t total = p.d.NR * p.d.KB * CHUNK_WORDS;
+    int64_t total = p.NR_part * p.d.KB * CHUNK_WORDS;
     for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
          idx += (int64_t)gridDim.x * blockDim.x) {
         int64_t chunk = idx >> 7;
         int wi = (int)(idx & 127);
         int lane = wi >> 2, j = wi & 3;
-        int64_t R = chunk / p.d.KB, kb = chunk - R * p.d.KB;
+        int64_t R = chunk / p.d.KB, kb = chunk - R * p.d.KB;   // R: row block within the part
         uint32_t out = 0;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             int kk, nn;
             nibble_coord(lane, j, i, kk, nn);
-            out |= src_nibble(p, kb * CHUNK_K + kk, R * CHUNK_N + nn) << (4 * i);
+            if (p.half < 0) out |= src_nibble(p, kb * CHUNK_K + kk, R * CHUNK_N + nn) << (4 * i);
+            else if ((i & 1) == p.half) out |= src_nibble(p, kb * CHUNK_K + kk, R * 8 + (nn & 7)) << (4 * i);
         }
-        p.qw[idx] = out;
+        uint32_t *dst = p.qw + ((p.dst_R0 + R) * p.d.KB + kb) * CHUNK_WORDS + wi;
+        if (p.half < 0) *dst = out;
+        else *dst = (*dst & (p.half ? 0x0F0F0F0Fu : 0xF0F0F0F0u)) | out;
     }
 }
 
@@ -70,19 +79,24 @@ __device__ __forceinline__ uint16_t load_scale_bf16(const void *s, int dtype, in
 }
 
 __global__ void repack_meta_kernel(RepackParams p) {
-    int64_t total = p.d.NR * p.d.G * 8;
+    int64_t total = p.NR_part * p.d.G * 8;
     for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
          idx += (int64_t)gridDim.x * blockDim.x) {
         int g = (int)(idx & 7);
         int64_t blk = idx >> 3;
         int64_t R = blk / p.d.G, grp = blk - R * p.d.G;
         int64_t cg = p.grp_map ? (int64_t)p.grp_map[grp] : (p.k_off + grp * p.gs) / p.gs_ckpt;
-        uint8_t *m = p.meta + blk * META_BYTES;
+        uint8_t *m = p.meta + ((p.dst_R0 + R) * p.d.G + grp) * META_BYTES;
         uint32_t zz[2];
         uint16_t ss[2];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-            int64_t col = p.n_off + R * CHUNK_N + g + 8 * h;
+            if (p.half >= 0 && h != p.half) {   // the other half of the pair keeps what it holds
+                ss[h] = (uint16_t)(reinterpret_cast<uint32_t *>(m)[g] >> (16 * h));
+                zz[h] = (m[META_ZERO_OFF + g] >> (4 * h)) & 0xFu;
+                continue;
+            }
+            int64_t col = p.half < 0 ? p.n_off + R * CHUNK_N + g + 8 * h : R * 8 + g;
             ss[h] = load_scale_bf16(p.scales, p.scales_dtype, cg * p.N_full + col);
             if (p.format == 2) {
                 zz[h] = 8u;  // symmetric: W = (q - 8) * s  (marlin_gemm.cu:43-48)
@@ -106,11 +120,12 @@ int launch_repack(const Linear &L, const RepackSrc &src, cudaStream_t stream) {
     p.gs = L.d.gs; p.gs_ckpt = src.gs;
     p.perm = src.perm; p.grp_map = src.row_group;
     p.d = L.d; p.qw = L.qw; p.meta = L.meta;
-    int64_t words = L.d.NR * L.d.KB * CHUNK_WORDS;
+    p.dst_R0 = src.dst_R0; p.NR_part = src.NR_part > 0 ? src.NR_part : L.d.NR; p.half = src.half;
+    int64_t words = p.NR_part * L.d.KB * CHUNK_WORDS;
     int blocks = (int)((words + 255) / 256 < 148 * 16 ? (words + 255) / 256 : 148 * 16);
     repack_qweight_kernel<<<blocks, 256, 0, stream>>>(p);
     count_launch();
-    int64_t metas = L.d.NR * L.d.G * 8;
+    int64_t metas = p.NR_part * L.d.G * 8;
     int mblocks = (int)((metas + 255) / 256 < 148 * 8 ? (metas + 255) / 256 : 148 * 8);
     repack_meta_kernel<<<mblocks, 256, 0, stream>>>(p);
     count_launch();
@@ -127,14 +142,26 @@ struct HookParams {
     const uint8_t *meta;
     const int32_t *perm;     // local tiled row -> local checkpoint row, or null
     const int32_t *grp_map;  // local group -> output group row, or null (identity)
+    int pair;                // SwiGLU handle: the hooks answer in [gate | up] column order (col_of_row / row_of_col)
 };
+
+// SwiGLU pair layout: gate column c sits in tiled row 16 (c / 8) + c % 8, up column c eight rows further.
+__device__ __forceinline__ int64_t row_of_col(const HookParams &p, int64_t n) {
+    if (!p.pair) return n;
+    const int64_t I = p.d.N >> 1, c = n >= I ? n - I : n;
+    return 16 * (c >> 3) + (n >= I ? 8 : 0) + (c & 7);
+}
+__device__ __forceinline__ int64_t col_of_row(const HookParams &p, int64_t r) {
+    if (!p.pair) return r;
+    return ((r >> 4) << 3) + (r & 7) + ((r & 8) ? (p.d.N >> 1) : 0);
+}
 
 __global__ void unpack_q_kernel(HookParams p, uint8_t *q) {
     int64_t total = p.d.K * p.d.N;
     for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
          idx += (int64_t)gridDim.x * blockDim.x) {
         int64_t k = idx / p.d.N, n = idx - k * p.d.N;
-        NibblePos np = nibble_pos(p.d, k, n);
+        NibblePos np = nibble_pos(p.d, k, row_of_col(p, n));
         int64_t ko = p.perm ? (int64_t)p.perm[k] : k;
         q[ko * p.d.N + n] = (uint8_t)((p.qw[np.word] >> np.shift) & 0xFu);
     }
@@ -145,8 +172,9 @@ __global__ void unpack_z_kernel(HookParams p, uint8_t *z, __nv_bfloat16 *s) {
     for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
          idx += (int64_t)gridDim.x * blockDim.x) {
         int64_t grp = idx / p.d.N, n = idx - grp * p.d.N;
-        int64_t R = n >> 4;
-        int r = (int)(n & 15), g = r & 7, h = r >> 3;
+        const int64_t nt = row_of_col(p, n);
+        int64_t R = nt >> 4;
+        int r = (int)(nt & 15), g = r & 7, h = r >> 3;
         const uint8_t *m = p.meta + meta_offset(p.d, R, grp);
         int64_t go = p.grp_map ? (int64_t)p.grp_map[grp] : grp;
         if (z) z[go * p.d.N + n] = (uint8_t)((m[META_ZERO_OFF + g] >> (4 * h)) & 0xF);
@@ -181,7 +209,7 @@ __global__ void dequant_dense_kernel(HookParams p, __nv_bfloat16 *w) {
             uint32_t s16 = h ? (pr >> 16) : (pr & 0xFFFFu);
             uint32_t z4 = (m[META_ZERO_OFF + g] >> (4 * h)) & 0xFu;
             uint32_t v = dequant_pair(word >> (4 * r), zero_magic(z4), s16 | (s16 << 16));
-            int64_t n = R * CHUNK_N + nn;
+            int64_t n = col_of_row(p, R * CHUNK_N + nn);
             int64_t k0 = p.perm ? (int64_t)p.perm[k] : k;
             int64_t k1 = p.perm ? (int64_t)p.perm[k + 1] : k + 1;
             w[k0 * p.d.N + n] = __ushort_as_bfloat16((unsigned short)(v & 0xFFFFu));
@@ -201,6 +229,7 @@ static HookParams hook_params(const Linear &L) {
     p.d = L.d; p.qw = L.qw; p.meta = L.meta;
     p.perm = L.perm_external ? nullptr : L.perm;   // an externally permuted ROW shard answers in tiled row order
     p.grp_map = p.perm ? L.perm + L.d.K : nullptr;
+    p.pair = L.epilogue == W4A16_EPILOGUE_SWIGLU;
     return p;
 }
 
@@ -238,11 +267,12 @@ __global__ void dequant_d1_kernel(HookParams p, const void *scales, int dtype, i
     for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
          idx += (int64_t)gridDim.x * blockDim.x) {
         int64_t k = idx / p.d.N, n = idx - k * p.d.N;        // k = tiled row
-        NibblePos np = nibble_pos(p.d, k, n);
+        const int64_t nt = row_of_col(p, n);
+        NibblePos np = nibble_pos(p.d, k, nt);
         int q = (int)((p.qw[np.word] >> np.shift) & 0xFu);
         int64_t grp = k / p.d.gs;
-        int r = (int)(n & 15);
-        const uint8_t *m = p.meta + meta_offset(p.d, n >> 4, grp);
+        int r = (int)(nt & 15);
+        const uint8_t *m = p.meta + meta_offset(p.d, nt >> 4, grp);
         int z = (m[META_ZERO_OFF + (r & 7)] >> (4 * (r >> 3))) & 0xF;
         int64_t cg = p.grp_map ? (int64_t)p.grp_map[grp] : (k_off + grp * p.d.gs) / gs_ckpt;
         int64_t si = cg * N_full + n_off + n;
@@ -267,14 +297,16 @@ int launch_dequant_d1(const Linear &L, const void *scales, int scales_dtype, __h
 // ---------------------------------------------------------------------------
 // small helpers around the forward
 // ---------------------------------------------------------------------------
-__global__ void convert_bias_kernel(const void *src, int dtype, __nv_bfloat16 *dst, int64_t n) {
+// half < 0: dst[i] = src[i]; half = 0 / 1: source element i lands at row 16 (i / 8) + 8 half + i % 8 (SwiGLU pair layout)
+__global__ void convert_bias_kernel(const void *src, int dtype, __nv_bfloat16 *dst, int64_t n, int half) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
-    dst[i] = __ushort_as_bfloat16(load_scale_bf16(src, dtype, i));
+    const int64_t o = half < 0 ? i : 16 * (i >> 3) + 8 * half + (i & 7);
+    dst[o] = __ushort_as_bfloat16(load_scale_bf16(src, dtype, i));
 }
 
-int launch_convert_bias(const void *src, int dtype, __nv_bfloat16 *dst, int64_t n, cudaStream_t stream) {
-    convert_bias_kernel<<<(int)((n + 255) / 256), 256, 0, stream>>>(src, dtype, dst, n);
+int launch_convert_bias(const void *src, int dtype, __nv_bfloat16 *dst, int64_t n, cudaStream_t stream, int half) {
+    convert_bias_kernel<<<(int)((n + 255) / 256), 256, 0, stream>>>(src, dtype, dst, n, half);
     count_launch();
     W4_CUDA_OK(cudaGetLastError());
     return 0;

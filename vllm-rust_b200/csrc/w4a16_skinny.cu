@@ -442,6 +442,7 @@ static int sk_env_int(const char *name, int dflt) {
 }
 
 bool skinny_usable(const Linear &L, int64_t M) {
+    if (L.epilogue != W4A16_EPILOGUE_NONE) return false;   // no SwiGLU epilogue in the opt-in kernel
     if (sk_env_int("W4A16_NO_SKINNY", 0)) return false;
     if (M < 1 || M > SK_TM) return false;
     const int gs = L.d.gs;

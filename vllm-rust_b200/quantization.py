@@ -21,6 +21,8 @@ from __future__ import annotations
 
 import ctypes
 import enum
+import hashlib
+import os
 from dataclasses import dataclass, field
 from typing import Dict, Mapping, Optional, Sequence
 
@@ -35,6 +37,9 @@ MARLIN_SUPPORTED_GROUP_SIZES = (-1, 32, 64, 128)  # marlin.rs:48
 FORMAT_AWQ, FORMAT_GPTQ_ZP, FORMAT_GPTQ_SYM = 0, 1, 2
 DTYPE_CODE = {torch.float16: 0, torch.bfloat16: 1, torch.float32: 2}
 TP_NONE, TP_COLUMN, TP_ROW = 0, 1, 2
+
+
+EPILOGUE_NONE, EPILOGUE_SWIGLU = 0, 1   # enum w4a16_epilogue (include/w4a16_b200.h)
 
 
 class QuantizationMethod(enum.Enum):  # quantization/config.rs QuantizationMethod (the W4A16 members)
@@ -172,6 +177,23 @@ class B200W4A16Linear(QuantizedLinear):
     def load_weights(self, weights: Mapping[str, torch.Tensor]) -> None:
         """Keys "qweight", "qzeros", "scales", "bias", "g_idx" in CHECKPOINT layout
         (awq_marlin.rs:592-664, gptq.rs:435-454); the repack runs inside."""
+        self._load(weights, None, self._full[1])
+
+    def load_part(self, n_begin: int, weights: Mapping[str, torch.Tensor]) -> None:
+        """One sibling projection of a fused handle (w4a16_load_*_part): `weights` is that projection's own
+        checkpoint (the keys load_weights takes), filling output columns [n_begin, n_begin + its width).  The
+        reference keeps q/k/v and gate/up as separate linears (qwen3_quantized.rs:84-96, 532-551)."""
+        scales = weights.get("scales")
+        if scales is None:
+            raise W4A16Error("Missing 'scales' in weights")
+        self._load(weights, int(n_begin), int(scales.shape[-1]))
+
+    def set_epilogue(self, epilogue: int) -> None:
+        """EPILOGUE_SWIGLU: the handle holds gate_proj | up_proj and forward writes silu(gate) * up
+        (fused_swiglu_bf16, swiglu.cu:40-45); before any load."""
+        check(lib().w4a16_set_epilogue(self._h, int(epilogue)))
+
+    def _load(self, weights: Mapping[str, torch.Tensor], n_begin: Optional[int], nf: int) -> None:
         def need(key):
             t = weights.get(key)
             if t is None:
@@ -187,7 +209,7 @@ class B200W4A16Linear(QuantizedLinear):
                 t = t.view(dtype)  # checkpoints hold the packed words as I32 / U32: same bits
             return t.to(self._device).contiguous()
 
-        kf, nf = self._full
+        kf = self._full[0]
         qweight = dev(need("qweight"), torch.int32)
         scales = dev(need("scales"))
         if scales.dtype not in DTYPE_CODE:
@@ -196,6 +218,8 @@ class B200W4A16Linear(QuantizedLinear):
         bias = dev(weights.get("bias"))
         if bias is not None and bias.dtype not in DTYPE_CODE:
             raise W4A16Error(f"bias dtype {bias.dtype} not supported")
+        if bias is not None and bias.numel() != nf:
+            raise W4A16Error(f"bias holds {bias.numel()} entries, expected {nf}")
         g = 1 if self._group_size <= 0 else kf // self._group_size   # marlin.rs:308-341: K % group_size == 0
         exp_qw = (kf, nf // 8) if self._fmt == FORMAT_AWQ else (kf // 8, nf)
         if tuple(qweight.shape) != exp_qw:
@@ -205,25 +229,42 @@ class B200W4A16Linear(QuantizedLinear):
         if qzeros is not None and tuple(qzeros.shape) != (g, nf // 8):
             raise W4A16Error(f"qzeros shape {tuple(qzeros.shape)} != expected [{g}, {nf // 8}]")
         ptr = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None  # noqa: E731
+        bias_code = DTYPE_CODE[bias.dtype] if bias is not None else 1
+        part = () if n_begin is None else (n_begin, nf)
         with torch.cuda.device(self._device):
             s = _stream_ptr(qweight)
             if self._fmt == FORMAT_AWQ:
                 if qzeros is None:
                     raise W4A16Error("Missing 'qzeros' in weights")
-                check(lib().w4a16_load_awq(self._h, ptr(qweight), ptr(qzeros), ptr(scales), DTYPE_CODE[scales.dtype],
-                                           ptr(bias), DTYPE_CODE[bias.dtype] if bias is not None else 1, s))
+                fn = lib().w4a16_load_awq if n_begin is None else lib().w4a16_load_awq_part
+                check(fn(self._h, *part, ptr(qweight), ptr(qzeros), ptr(scales), DTYPE_CODE[scales.dtype],
+                         ptr(bias), bias_code, s))
             else:
                 g_idx = weights.get("g_idx")
                 if g_idx is not None:
                     if g_idx.dtype.is_floating_point or g_idx.numel() != kf:
                         raise W4A16Error(f"g_idx must hold {kf} integer entries, got {g_idx.numel()} of {g_idx.dtype}")
                     g_idx = g_idx.to(self._device, torch.int32).contiguous()
-                check(lib().w4a16_load_gptq(self._h, ptr(qweight), ptr(qzeros), ptr(scales),
-                                            DTYPE_CODE[scales.dtype], ptr(g_idx), ptr(bias),
-                                            DTYPE_CODE[bias.dtype] if bias is not None else 1, s))
+                fn = lib().w4a16_load_gptq if n_begin is None else lib().w4a16_load_gptq_part
+                check(fn(self._h, *part, ptr(qweight), ptr(qzeros), ptr(scales), DTYPE_CODE[scales.dtype], ptr(g_idx),
+                         ptr(bias), bias_code, s))
             # the checkpoint tensors are locals: keep them alive until the repack has run
             torch.cuda.current_stream().synchronize()
         self._loaded = True
+
+    # -- cache of the resident layout (w4a16_save_tiled / w4a16_load_tiled) -------------------------
+    def save_tiled(self, path, fingerprint: int = 0) -> None:
+        check(lib().w4a16_save_tiled(self._h, os.fsencode(path), fingerprint & (2 ** 64 - 1)))
+
+    def load_tiled(self, path, fingerprint: int = 0) -> None:
+        """Replaces load_weights: reads the repacked bytes back with plain copies; the handle must have been created
+        with the geometry, format, bias flag, shard and epilogue the file was written from."""
+        with torch.cuda.device(self._device):
+            check(lib().w4a16_load_tiled(self._h, os.fsencode(path), fingerprint & (2 ** 64 - 1), _stream_ptr()))
+        self._loaded = True
+
+    def weight_rows(self) -> int:
+        return int(lib().w4a16_weight_rows(self._h))
 
     def _check_x(self, x: torch.Tensor):
         if not x.is_cuda:
@@ -276,13 +317,13 @@ class B200W4A16Linear(QuantizedLinear):
     # -- parity hooks -------------------------------------------------------------------
     def dequantize(self) -> torch.Tensor:
         """Dense [K, N] bf16 on the D2 grid (awq_marlin_dequant.cu:45-68, gptq_dequant.cu:58-86)."""
-        w = torch.empty((self.in_features(), self.out_features()), dtype=torch.bfloat16, device=self._device)
+        w = torch.empty((self.in_features(), self.weight_rows()), dtype=torch.bfloat16, device=self._device)
         with torch.cuda.device(self._device):
             check(lib().w4a16_dequant_into(self._h, ctypes.c_void_p(w.data_ptr()), _stream_ptr(w)))
         return w
 
     def unpack(self):
-        k, n = self.in_features(), self.out_features()
+        k, n = self.in_features(), self.weight_rows()
         g = self.weight_groups()
         q = torch.empty((k, n), dtype=torch.uint8, device=self._device)
         z = torch.empty((g, n), dtype=torch.uint8, device=self._device)
@@ -292,7 +333,7 @@ class B200W4A16Linear(QuantizedLinear):
         return q, z
 
     def scales(self) -> torch.Tensor:
-        s = torch.empty((self.weight_groups(), self.out_features()), dtype=torch.bfloat16, device=self._device)
+        s = torch.empty((self.weight_groups(), self.weight_rows()), dtype=torch.bfloat16, device=self._device)
         with torch.cuda.device(self._device):
             check(lib().w4a16_scales_into(self._h, ctypes.c_void_p(s.data_ptr()), _stream_ptr(s)))
         return s
@@ -303,7 +344,7 @@ class B200W4A16Linear(QuantizedLinear):
         sc = scales.to(self._device).contiguous()
         if sc.dtype not in DTYPE_CODE:
             raise W4A16Error(f"scales dtype {sc.dtype} not supported")
-        w = torch.empty((self.in_features(), self.out_features()), dtype=torch.float16, device=self._device)
+        w = torch.empty((self.in_features(), self.weight_rows()), dtype=torch.float16, device=self._device)
         with torch.cuda.device(self._device):
             check(lib().w4a16_dequant_d1_into(self._h, ctypes.c_void_p(sc.data_ptr()), DTYPE_CODE[sc.dtype],
                                               ctypes.c_void_p(w.data_ptr()), _stream_ptr(w)))
@@ -525,10 +566,14 @@ def create_config(detected: DetectedQuantConfig) -> QuantizationConfig:
 
 # ---- weight loaders (weight_loader.rs) --------------------------------------------------
 class _Loader:
-    """`tensors` plays the VarBuilder: a mapping "prefix.name" -> tensor (any device)."""
+    """`tensors` plays the VarBuilder: a mapping "prefix.name" -> tensor (any device), e.g. a
+    checkpoint.SafetensorsCheckpoint.  cache_dir: directory of W4T cache files (save_tiled / load_tiled): a layer
+    whose cache file exists and matches is read back instead of repacked, else it is repacked and written."""
 
-    def __init__(self, tensors: Mapping[str, torch.Tensor], config, device):
+    def __init__(self, tensors: Mapping[str, torch.Tensor], config, device, cache_dir=None):
         self.tensors, self.config, self._device = tensors, config, torch.device(device)
+        self.cache_dir = cache_dir
+        self.cache_hits = 0
 
     def device(self):
         return self._device
@@ -545,6 +590,91 @@ class _Loader:
                              f"got {list(t.shape)}")
         return t
 
+    # -- shared by the AWQ and GPTQ loaders --------------------------------------------------------------------
+    def _weights(self, prefix: str, in_features: int, out_features: int, bias: bool) -> Dict[str, torch.Tensor]:
+        raise NotImplementedError
+
+    def _fingerprint(self, prefixes, weights_list) -> int:
+        """Identity of the source tensors for the cache: names, dtypes, shapes and (cheaply) contents --
+        the checkpoint's own hash when the mapping has one, else a hash of the packed tensors' bytes."""
+        h = hashlib.blake2b(digest_size=8)
+        ident = getattr(self.tensors, "fingerprint", None)
+        for prefix, w in zip(prefixes, weights_list):
+            for k in sorted(w):
+                t = w[k]
+                h.update(f"{prefix}.{k}:{t.dtype}:{list(t.shape)};".encode())
+                if ident is None:
+                    h.update(t.detach().cpu().contiguous().view(torch.uint8).numpy().tobytes())
+        if ident is not None:
+            h.update(str(ident() if callable(ident) else ident).encode())
+        return int.from_bytes(h.digest(), "little") or 1
+
+    def _cache_path(self, prefixes, tp) -> Optional[str]:
+        if not self.cache_dir:
+            return None
+        tag = "+".join(prefixes).replace("/", "_")
+        if tp:
+            tag += f".tp{tp.get('tp_mode', 0)}r{tp.get('tp_rank', 0)}of{tp.get('tp_size', 1)}"
+        return os.path.join(os.fspath(self.cache_dir), tag + ".w4t")
+
+    def _load_cached(self, lin, path, fp, do_load) -> None:
+        if path and os.path.exists(path):
+            try:
+                lin.load_tiled(path, fp)
+                self.cache_hits += 1
+                return
+            except W4A16Error:
+                pass   # stale or foreign file: repack and overwrite it
+        do_load()
+        if path:
+            os.makedirs(os.path.dirname(path), exist_ok=True)
+            lin.save_tiled(path, fp)
+
+    def load_linear(self, prefix: str, in_features: int, out_features: int, bias: bool, **tp) -> QuantizedLinear:
+        if self.config.is_layer_skipped(prefix):
+            raise W4A16Error(f"{prefix} is in modules_to_not_convert: it is a dense layer, not on the W4A16 path")
+        w = self._weights(prefix, in_features, out_features, bias)
+        lin = self.config.create_linear(in_features, out_features, "bias" in w, self._device, **tp)
+        path = self._cache_path([prefix], tp)
+        fp = self._fingerprint([prefix], [w]) if path else 0
+        self._load_cached(lin, path, fp, lambda: lin.load_weights(w))
+        return lin
+
+    def load_fused(self, prefixes: Sequence[str], in_features: int, out_features: Sequence[int], bias: bool,
+                   epilogue: int = EPILOGUE_NONE) -> QuantizedLinear:
+        """Sibling projections of one input as ONE linear (w4a16_load_*_part): e.g. prefixes
+        [..q_proj, ..k_proj, ..v_proj] -> y = [q | k | v], or [..gate_proj, ..up_proj] with EPILOGUE_SWIGLU ->
+        y = silu(gate) * up.  The reference creates and runs them one by one (qwen3_quantized.rs:84-96, 179-181,
+        532-551).  Each sibling keeps its own checkpoint tensors; nothing is concatenated on the host."""
+        if len(prefixes) != len(out_features) or not prefixes:
+            raise W4A16Error("load_fused: one out_features entry per prefix")
+        for prefix in prefixes:
+            if self.config.is_layer_skipped(prefix):
+                raise W4A16Error(f"{prefix} is in modules_to_not_convert: it is a dense layer, not on the W4A16 path")
+        ws = [self._weights(pfx, in_features, n, bias) for pfx, n in zip(prefixes, out_features)]
+        has_bias = ["bias" in w for w in ws]
+        if any(has_bias) and not all(has_bias):
+            raise W4A16Error("load_fused: either every sibling has a bias or none has")
+        lin = self.config.create_linear(in_features, sum(out_features), has_bias[0], self._device)
+        if epilogue != EPILOGUE_NONE:
+            lin.set_epilogue(epilogue)
+        path = self._cache_path(list(prefixes) + ([f"ep{epilogue}"] if epilogue else []), None)
+        fp = self._fingerprint(prefixes, ws) if path else 0
+
+        def do_load():
+            n0 = 0
+            for w, n in zip(ws, out_features):
+                lin.load_part(n0, w)
+                n0 += n
+        self._load_cached(lin, path, fp, do_load)
+        return lin
+
+    def load_swiglu(self, gate_prefix: str, up_prefix: str, hidden_size: int, intermediate_size: int,
+                    bias: bool = False) -> QuantizedLinear:
+        """QuantizedSwiGluMlp's gate_proj + up_proj + fused_swiglu (qwen3_quantized.rs:501-551) as one linear."""
+        return self.load_fused([gate_prefix, up_prefix], hidden_size, [intermediate_size, intermediate_size], bias,
+                               EPILOGUE_SWIGLU)
+
 
 class AwqWeightLoader(_Loader):
     """weight_loader.rs:596-714."""
@@ -552,9 +682,7 @@ class AwqWeightLoader(_Loader):
     def method(self):
         return QuantizationMethod.AWQ
 
-    def load_linear(self, prefix: str, in_features: int, out_features: int, bias: bool, **tp) -> QuantizedLinear:
-        if self.config.is_layer_skipped(prefix):
-            raise W4A16Error(f"{prefix} is in modules_to_not_convert: it is a dense layer, not on the W4A16 path")
+    def _weights(self, prefix, in_features, out_features, bias):
         packed_out = -(-out_features // 8)
         g = self.config.num_groups(in_features)
         w = {"qweight": self._get(prefix, "qweight", (in_features, packed_out), "AWQ"),
@@ -562,10 +690,7 @@ class AwqWeightLoader(_Loader):
              "qzeros": self._get(prefix, "qzeros", (g, packed_out), "AWQ")}
         if bias and f"{prefix}.bias" in self.tensors:
             w["bias"] = self.tensors[f"{prefix}.bias"]
-        has_bias = "bias" in w
-        lin = self.config.create_linear(in_features, out_features, has_bias, self._device, **tp)
-        lin.load_weights(w)
-        return lin
+        return w
 
 
 class GptqWeightLoader(_Loader):
@@ -574,7 +699,7 @@ class GptqWeightLoader(_Loader):
     def method(self):
         return QuantizationMethod.GPTQ
 
-    def load_linear(self, prefix: str, in_features: int, out_features: int, bias: bool, **tp) -> QuantizedLinear:
+    def _weights(self, prefix, in_features, out_features, bias):
         gs = self.config.group_size
         g = 1 if gs <= 0 else -(-in_features // gs)
         w = {"qweight": self._get(prefix, "qweight", (in_features // 8, out_features), "GPTQ"),
@@ -584,17 +709,16 @@ class GptqWeightLoader(_Loader):
             w["g_idx"] = self.tensors[f"{prefix}.g_idx"]
         if bias and f"{prefix}.bias" in self.tensors:
             w["bias"] = self.tensors[f"{prefix}.bias"]
-        lin = self.config.create_linear(in_features, out_features, "bias" in w, self._device, **tp)
-        lin.load_weights(w)
-        return lin
+        return w
 
 
-def create_weight_loader_with_params(tensors: Mapping[str, torch.Tensor], detected: DetectedQuantConfig, device):
+def create_weight_loader_with_params(tensors: Mapping[str, torch.Tensor], detected: DetectedQuantConfig, device,
+                                     cache_dir=None):
     """weight_loader.rs:1596-1706 for the W4A16 members."""
     cfg = create_config(detected)
     if isinstance(cfg, AwqConfig):
-        return AwqWeightLoader(tensors, cfg, device)
-    return GptqWeightLoader(tensors, cfg, device)
+        return AwqWeightLoader(tensors, cfg, device, cache_dir)
+    return GptqWeightLoader(tensors, cfg, device, cache_dir)
 
 
 def kernel_launches() -> int:
