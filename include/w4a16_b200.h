@@ -208,6 +208,37 @@ int w4a16_peer_destroy(w4a16_peer_t peer);
 int w4a16_forward_row_fused(w4a16_handle_t h, const void *x_bf16, void *y_bf16, int64_t M,
                             w4a16_peer_t peer, w4a16_comm_t comm, w4a16_stream_t stream);
 
+/* -- a chain of decode linears in ONE launch ------------------
+ * The reference's decode step calls its quantized linears one after the other in a fixed
+ * order -- q/k/v and o around attention (qwen3_quantized.rs:704-709), gate/up -> silu*mul
+ * -> down (:532-551), layer after layer (:890-925) -- and replays that sequence as a CUDA
+ * graph (engine/cuda_graph.rs).  A chain is that fixed sequence for M <= 4 tokens as one
+ * object: linear i reads x[i] and writes y[i], in order, and linear i+1 may read what
+ * linear i wrote (x[i+1] == y[i], or any overlap).  Where the shapes allow it (every
+ * in_features a multiple of 4096, one group size of 32 / 64 / 128 for all, no act-order
+ * gather) chain_run is ONE persistent launch: one CTA per SM streams every linear's weights
+ * through one shared-memory ring that stays full across the boundaries between linears, and
+ * consecutive linears are separated by a grid-wide barrier.  Otherwise chain_run makes the
+ * n w4a16_forward_into calls itself (w4a16_chain_kernel tells which).  Results: those of
+ * w4a16_forward_into (bit-identical for in_features == 4096; same bounds otherwise).
+ * x / y pointers are fixed at creation, like the arguments of a captured graph; SwiGLU
+ * handles and biases are honoured; a ROW shard writes its partial sum (no collective
+ * inside a chain).  chain_run never allocates or synchronises and can be captured in a
+ * CUDA graph.  The persistent launch needs every SM of the device: all its CTAs must be
+ * resident together (it waits for earlier kernels, but must not share the device with a
+ * kernel that waits for IT).  One chain must not run concurrently with itself.          */
+typedef struct w4a16_chain *w4a16_chain_t;
+int w4a16_chain_create(w4a16_chain_t *out, int n, const w4a16_handle_t *handles,
+                       const void *const *x_bf16, void *const *y_bf16, int64_t M);
+int w4a16_chain_run(w4a16_chain_t chain, w4a16_stream_t stream);
+int w4a16_chain_destroy(w4a16_chain_t chain);
+/* "chain_imma" (persistent launch) or "per_linear (<reason>)". */
+const char *w4a16_chain_kernel(w4a16_chain_t chain);
+/* Profiling hook (W4A16_GV_DEBUG=1 at chain_create): %globaltimer stamps
+ * [n][CTAs][4] = {linear started, activations staged, weights streamed, y written + barrier passed}
+ * of the last run; synchronises the device. */
+int w4a16_chain_debug_stamps(w4a16_chain_t chain, uint64_t *out, int64_t words);
+
 /* Communicator bootstrap for callers that do not already hold an ncclComm_t
  * (distributed/launcher.rs:132-262: ncclGetUniqueId on rank 0, out-of-band
  * broadcast of the 128-byte id, ncclCommInitRank).  NCCL is dlopen'ed as

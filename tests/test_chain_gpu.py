@@ -1,0 +1,187 @@
+"""a chain of decode linears in one persistent launch (w4a16_chain_*, csrc/w4a16_chain.cu).
+
+The reference runs its quantized linears one launch at a time in a fixed per-layer order (qwen3_quantized.rs:704-709,
+532-551) and replays that order as a CUDA graph (engine/cuda_graph.rs).  The chain must give what those separate calls
+give.  Checks:
+  * every linear of a chain against the float64 oracle (reference tolerance + the 1e-2 north-star bound) and against
+    the product's own per-linear w4a16_forward_into: bit-identical for in_features == 4096 (same kernel arithmetic and
+    summation order), within tolerance otherwise;
+  * a TRUE dependency chain (x[i+1] is y[i]): the grid barrier orders the write of one linear before the read of the
+    next -- compared with the same chain run call by call;
+  * M = 1..4, group sizes 32 / 64 / 128, bias, the SwiGLU handle (gate/up -> silu*mul -> down as a two-linear chain),
+    row blocks fewer than CTAs, repeated runs (the barrier counter is monotonic over runs), CUDA-graph capture;
+  * shapes the persistent kernel does not take fall back to per-linear launches with the same results, and say so;
+  * argument errors."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O
+from helpers import assert_close_ref, awq_unpacked, bits_of, oracle_forward, t_bf16_from_bits, t_i32
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def make_linear(product, K, N, g, seed, bias=False):
+    qweight, qzeros, scales, b = O.make_awq_checkpoint(K, N, g, seed=seed, bias=bias)
+    lin = product.AwqConfig.int4(g).create_linear(K, N, bias, DEV)
+    w = {"qweight": t_i32(qweight), "qzeros": t_i32(qzeros), "scales": torch.from_numpy(scales)}
+    if bias:
+        w["bias"] = torch.from_numpy(b).to(torch.bfloat16)
+    lin.load_weights(w)
+    q, z, sb = awq_unpacked(qweight, qzeros, scales)
+    return lin, (q, z, sb, O.np_bf16_round(b) if bias else None)
+
+
+@pytest.mark.parametrize("M", [1, 2, 3, 4])
+@pytest.mark.parametrize("g", [128, 32])
+def test_independent_linears_match_oracle_and_per_linear_calls(product, M, g):
+    shapes = [(4096, 1024, False), (8192, 512, True), (4096, 2368 + 64, False), (4096, 256, True)]   # N / 16 < 148 on the last
+    lins, cks, xs, ys = [], [], [], []
+    for i, (K, N, bias) in enumerate(shapes):
+        lin, ck = make_linear(product, K, N, g, seed=10 + i, bias=bias)
+        lins.append(lin); cks.append(ck)
+        xs.append(t_bf16_from_bits(O.make_activations(M, K, seed=50 + i + M)).to(DEV))
+        ys.append(torch.full((M, N), float("nan"), dtype=torch.bfloat16, device=DEV))
+    chain = product.DecodeChain(list(zip(lins, xs, ys)))
+    assert chain.kernel() == "chain_imma" and len(chain) == len(shapes)
+    for rep in range(3):                       # the barrier counter keeps counting over runs
+        for y in ys:
+            y.fill_(float("nan"))
+        chain.run()
+        torch.cuda.synchronize()
+        for i, (K, N, bias) in enumerate(shapes):
+            q, z, sb, b = cks[i]
+            want = oracle_forward(bits_of(xs[i]), q, z, sb, g, bias_f32=b)
+            assert_close_ref(bits_of(ys[i]), want, f"chain linear {i} M={M} g={g} rep={rep}")
+            single = lins[i].forward(xs[i])
+            if K == 4096:
+                assert (bits_of(single) == bits_of(ys[i])).all(), f"linear {i}: chain != forward_into bit for bit"
+            else:
+                assert_close_ref(bits_of(single), want, "per-linear")
+
+
+@pytest.mark.parametrize("M", [1, 4])
+def test_true_dependency_chain_equals_call_by_call(product, M):
+    """x[i+1] = y[i]: qkv-like -> o-like -> gate_up (SwiGLU) -> down, twice."""
+    H, I = 4096, 4096
+    g = 128
+    qweight = {}
+    def swiglu(seed):
+        lin = product.AwqConfig.int4(g).create_linear(H, 2 * I, False, DEV)
+        lin.set_epilogue(product.EPILOGUE_SWIGLU)
+        for half in range(2):
+            qw, qz, sc, _ = O.make_awq_checkpoint(H, I, g, seed=seed + half)
+            # small scales keep the magnitudes of a deep chain in range
+            lin.load_part(half * I, {"qweight": t_i32(qw), "qzeros": t_i32(qz), "scales": torch.from_numpy(sc * 0.25)})
+        return lin
+    def plain(K, N, seed, scale):
+        qw, qz, sc, _ = O.make_awq_checkpoint(K, N, g, seed=seed)
+        lin = product.AwqConfig.int4(g).create_linear(K, N, False, DEV)
+        lin.load_weights({"qweight": t_i32(qw), "qzeros": t_i32(qz), "scales": torch.from_numpy(sc * scale)})
+        return lin
+    lins = []
+    for layer in range(2):
+        lins += [plain(H, H, 100 + 10 * layer, 0.3), plain(H, H, 101 + 10 * layer, 0.3), swiglu(102 + 10 * layer),
+                 plain(I, H, 105 + 10 * layer, 0.3)]
+    x0 = t_bf16_from_bits(O.make_activations(M, H, seed=3)).to(DEV)
+    def buffers():
+        bufs = [x0.clone()]
+        for lin in lins:
+            bufs.append(torch.zeros((M, lin.out_features()), dtype=torch.bfloat16, device=DEV))
+        return bufs
+    a, b = buffers(), buffers()
+    chain = product.DecodeChain([(lin, a[i], a[i + 1]) for i, lin in enumerate(lins)])
+    assert chain.kernel() == "chain_imma"
+    chain.run()
+    for i, lin in enumerate(lins):
+        lin.forward_into(b[i], b[i + 1])
+    torch.cuda.synchronize()
+    for i in range(1, len(a)):
+        assert torch.isfinite(a[i].float()).all()
+        assert (bits_of(a[i]) == bits_of(b[i])).all(), f"buffer {i} differs between the chain and the call-by-call run"
+    assert float(a[-1].float().abs().max()) > 0.0
+    # CUDA-graph capture + replay on fresh inputs
+    x1 = t_bf16_from_bits(O.make_activations(M, H, seed=4)).to(DEV)
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        chain.run()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=st):
+            chain.run()
+        a[0].copy_(x1)
+        graph.replay()
+        graph.replay()
+    st.synchronize()
+    b[0].copy_(x1)
+    for i, lin in enumerate(lins):
+        lin.forward_into(b[i], b[i + 1])
+    torch.cuda.synchronize()
+    assert (bits_of(a[-1]) == bits_of(b[-1])).all()
+
+
+def test_mlp_chain_k12288_against_oracle(product):
+    """Qwen3-8B MLP shapes: gate_up 4096 -> 2 x 12288 (SwiGLU) then down 12288 -> 4096 (three stages per row block)."""
+    H, I, g, M = 4096, 12288, 128, 2
+    gu = product.AwqConfig.int4(g).create_linear(H, 2 * I, False, DEV)
+    gu.set_epilogue(product.EPILOGUE_SWIGLU)
+    for half in range(2):
+        qw, qz, sc, _ = O.make_awq_checkpoint(H, I, g, seed=31 + half)
+        gu.load_part(half * I, {"qweight": t_i32(qw), "qzeros": t_i32(qz), "scales": torch.from_numpy(sc)})
+    down, (q, z, sb, _) = make_linear(product, I, H, g, seed=40)
+    x = t_bf16_from_bits(O.make_activations(M, H, seed=9)).to(DEV)
+    mid = torch.zeros((M, I), dtype=torch.bfloat16, device=DEV)
+    y = torch.zeros((M, H), dtype=torch.bfloat16, device=DEV)
+    chain = product.DecodeChain([(gu, x, mid), (down, mid, y)])
+    assert chain.kernel() == "chain_imma"
+    chain.run()
+    torch.cuda.synchronize()
+    mid_ref = gu.forward(x)
+    assert (bits_of(mid_ref) == bits_of(mid)).all()           # gate_up has K = 4096: same arithmetic as the single launch
+    want = oracle_forward(bits_of(mid), q, z, sb, g)
+    assert_close_ref(bits_of(y), want, "down after swiglu")
+
+
+def test_fallback_per_linear(product):
+    M, g = 2, 128
+    a, (q, z, sb, _) = make_linear(product, 2560, 512, g, seed=1)      # K not a multiple of 4096
+    b, _ = make_linear(product, 4096, 512, g, seed=2)
+    xa = t_bf16_from_bits(O.make_activations(M, 2560, seed=1)).to(DEV)
+    xb = t_bf16_from_bits(O.make_activations(M, 4096, seed=2)).to(DEV)
+    ya = torch.zeros((M, 512), dtype=torch.bfloat16, device=DEV)
+    yb = torch.zeros((M, 512), dtype=torch.bfloat16, device=DEV)
+    chain = product.DecodeChain([(a, xa, ya), (b, xb, yb)])
+    assert chain.kernel().startswith("per_linear") and "4096" in chain.kernel()
+    chain.run()
+    torch.cuda.synchronize()
+    assert (bits_of(ya) == bits_of(a.forward(xa))).all() and (bits_of(yb) == bits_of(b.forward(xb))).all()
+    assert_close_ref(bits_of(ya), oracle_forward(bits_of(xa), q, z, sb, g), "fallback")
+    # more than 4 tokens: also per linear
+    x8 = t_bf16_from_bits(O.make_activations(8, 4096, seed=3)).to(DEV)
+    y8 = torch.zeros((8, 512), dtype=torch.bfloat16, device=DEV)
+    c8 = product.DecodeChain([(b, x8, y8)])
+    assert c8.kernel().startswith("per_linear")
+    c8.run()
+    torch.cuda.synchronize()
+    assert (bits_of(y8) == bits_of(b.forward(x8))).all()
+
+
+def test_chain_errors(product):
+    lin, _ = make_linear(product, 4096, 256, 128, seed=5)
+    x = torch.zeros((1, 4096), dtype=torch.bfloat16, device=DEV)
+    y = torch.zeros((1, 256), dtype=torch.bfloat16, device=DEV)
+    with pytest.raises(product.W4A16Error, match="at least one"):
+        product.DecodeChain([])
+    with pytest.raises(product.W4A16Error, match="BF16"):
+        product.DecodeChain([(lin, x.float(), y)])
+    with pytest.raises(product.W4A16Error, match="in_features"):
+        product.DecodeChain([(lin, torch.zeros((1, 2048), dtype=torch.bfloat16, device=DEV), y)])
+    with pytest.raises(product.W4A16Error, match="y of step 0"):
+        product.DecodeChain([(lin, x, torch.zeros((1, 128), dtype=torch.bfloat16, device=DEV))])
+    with pytest.raises(product.W4A16Error, match="same M"):
+        product.DecodeChain([(lin, x, y), (lin, torch.zeros((2, 4096), dtype=torch.bfloat16, device=DEV),
+                                            torch.zeros((2, 256), dtype=torch.bfloat16, device=DEV))])
+    unloaded = product.AwqConfig.int4(128).create_linear(4096, 256, False, DEV)
+    with pytest.raises(product.W4A16Error, match="not loaded"):
+        product.DecodeChain([(unloaded, x, y)])

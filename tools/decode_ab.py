@@ -20,6 +20,8 @@ def main():
     ap.add_argument("--m", type=int, default=1)
     ap.add_argument("--layers", type=int, default=36)
     ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--chain", action="store_true", help="every linear reads what the previous one wrote (M = 1)")
+    ap.add_argument("--api", default="linear", choices=["linear", "chain"], help="chain: one DecodeChain (persistent launch) per step")
     args = ap.parse_args()
     import torch
     P = bench.load_product()
@@ -30,13 +32,25 @@ def main():
     ys = {N: torch.empty((M, N), device=dev, dtype=torch.bfloat16) for _, _, N, *_ in layers}
     step_bytes = sum(bench.algo_bytes(M, K, N) for _, K, N, *_ in layers)
 
+    bufs = [torch.randn((1, 24576), device=dev).to(torch.bfloat16) for _ in range(2)]
+
     def step():
-        for name, K, N, Kl, Nl, mode, lin in layers:
-            lin.forward_into(xs[K], ys[N])
+        for i, (name, K, N, Kl, Nl, mode, lin) in enumerate(layers):
+            if args.chain:
+                lin.forward_into(bufs[i & 1][:, :K], bufs[(i + 1) & 1][:, :N])
+            else:
+                lin.forward_into(xs[K], ys[N])
     for cfg in args.cfg or [""]:
         kv = dict(item.split("=", 1) for item in cfg.split(",") if item)
         for k, v in kv.items():
             os.environ[k] = v
+        if args.api == "chain":
+            steps = []
+            for i, (name, K, N, Kl, Nl, mode, lin) in enumerate(layers):
+                steps.append((lin, bufs[i & 1][:, :K], bufs[(i + 1) & 1][:, :N]) if args.chain else (lin, xs[K], ys[N]))
+            dchain = P.DecodeChain(steps)
+            print("[ab] chain kernel:", dchain.kernel(), flush=True)
+            step = dchain.run
         best = None
         for rep in range(2):
             st = torch.cuda.Stream(dev)

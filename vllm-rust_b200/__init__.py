@@ -10,7 +10,7 @@ from .quantization import (  # noqa: F401
     B200W4A16Linear, check_marlin_supports_shape,
     AwqWeightLoader, GptqWeightLoader, create_weight_loader_with_params,
     detect_from_json, detect_from_directory, is_supported, create_config, kernel_launches, set_dispatch,
-    DetectedQuantConfig, EPILOGUE_NONE, EPILOGUE_SWIGLU,
+    DetectedQuantConfig, EPILOGUE_NONE, EPILOGUE_SWIGLU, DecodeChain,
 )
 from .checkpoint import SafetensorsCheckpoint, load_decoder_linears, save_safetensors, save_sharded  # noqa: F401
 from .parallel import (  # noqa: F401

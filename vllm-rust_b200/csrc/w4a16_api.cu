@@ -241,6 +241,12 @@ static int forward_local(Linear *L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
     return 0;
 }
 
+// per-linear forward for callers outside this file (the chain's fallback, w4a16_chain.cu)
+int forward_linear(Linear *L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, cudaStream_t stream) {
+    const bool add_bias = L->tp_mode != W4A16_TP_ROW || L->tp_size == 1;
+    return forward_local(L, x, y, M, add_bias, stream);
+}
+
 }  // namespace w4
 
 using namespace w4;

@@ -1,0 +1,601 @@
+// w4a16_chain.cu -- a CHAIN of decode linears (M <= 4 tokens) executed by ONE persistent launch.
+//
+// Why: launched one by one, every decode linear pays a dependency hand-over (0.65 us), the activation load + staging
+// (1.0-1.6 us) and the drain of its shared-memory ring + combine (1.0-1.6 us), and while it pays them HBM idles unless
+// the NEXT linear's resident CTA still has ring space to fill -- which is 96 KB per SM, one hop ahead, and qkv / o are
+// smaller than that (profiles/r2_decode_timeline.md: 25.4 us per Qwen3-8B layer against 15.3 us at copy speed).  The
+// dependency itself cannot be removed (linear i+1 reads what linear i wrote), but the weight stream does not depend on
+// anything: here ONE CTA per SM owns ONE ring of 5-6 stages of 33.5 KB for the whole chain, a producer warp keeps it
+// full ACROSS the boundaries between linears (weights of linear i+1, i+2, ... arrive while linear i still computes and
+// while the grid meets at the barrier), and the consumer warps run the int8 tensor-core GEMV of w4a16_gemv_imma2.cu on
+// whatever stage comes next.  Between consecutive linears: combine the warps' partial sums, write y, grid-wide barrier
+// (one release-add + acquire-poll per CTA on a monotonic counter), stage the next x.  HBM never waits for any of it as
+// long as the ring (28 MB chip-wide) outlasts the barrier.
+//
+// Replaces, for the decode step, the per-linear launches of the reference's layer loop (qwen3_quantized.rs:704-709
+// attention projections, :532-551 gate/up -> silu*mul -> down; each one a marlin_gemm_pooled launch,
+// marlin_cuda.rs:1655-1753) and its CUDA-graph replay of that loop (engine/cuda_graph.rs).  Arithmetic, W4T stream and
+// the activation quantisation are those of gemv_imma2_kernel (see there); results are bit-identical to it for K = 4096.
+#include <algorithm>
+#include <mutex>
+
+#include "w4a16_gemv_common.cuh"
+
+namespace w4 {
+
+constexpr int CH_GROUPS = 2;                          // consumer groups; group gi takes row blocks gi, gi + 2, ... of a CTA's range
+constexpr int CH_GWARPS = 8;                          // warps per group: 4 units each = one 32-unit stage per iteration
+constexpr int CH_UPW = 4;
+constexpr int CH_CONS_WARPS = CH_GROUPS * CH_GWARPS;
+constexpr int CH_CONS_THREADS = CH_CONS_WARPS * 32;   // 512
+constexpr int CH_THREADS = CH_CONS_THREADS + 32;      // + the producer warp
+constexpr int CH_MAX_STAGES = 8;
+constexpr int CH_SMEM_MAX = 227 * 1024;
+constexpr int CH_MAX_OPS = 4096;
+constexpr int CH_DBG_WORDS = 4;                       // stamps per (CTA, op): op start, staged, streamed, y written
+
+struct ChainOp {
+    const uint8_t *qw, *meta;
+    const __nv_bfloat16 *bias, *x;
+    __nv_bfloat16 *y;
+    const int *rb;             // [grid + 1]: CTA c owns row blocks [rb[c], rb[c + 1])
+    int M, K, N, UPR;
+    int spr;                   // 32-unit stages per row block = K / 4096
+    int swiglu, hoist, pad;
+};
+
+struct ChainParams {
+    const ChainOp *ops;
+    int n_ops;
+    unsigned long long *counter;   // grid-barrier arrivals, monotonic over the life of the chain
+    unsigned int *runs;            // launches completed so far (read by every CTA at start, advanced by CTA 0 at the end)
+    int S, slot_stride;            // ring stages, bytes per stage slot
+    int off_xs, off_gtab, off_part, off_ring;
+    unsigned long long *dbg;       // [n_ops][grid][CH_DBG_WORDS] %globaltimer stamps, or null
+};
+
+__device__ __forceinline__ void ch_imma(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void ch_bar_consumers() { asm volatile("bar.sync 1, %0;" ::"n"(CH_CONS_THREADS) : "memory"); }
+__device__ __forceinline__ void ch_mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+// Activation staging of one linear by the 512 consumer threads: identical to gemv_imma2_kernel's (per-(group, token)
+// power-of-two scale, two signed-byte planes in B-fragment order, integer group sums, Inf / NaN poison the group), but x
+// is read with ld.global.cg: another CTA of THIS launch wrote it a barrier ago.
+template <int MR, int MPU>
+__device__ __forceinline__ void ch_stage_x(const __nv_bfloat16 *x, uint8_t *xs, int2 *gtab, int M, int K, int tid, int lane) {
+    constexpr int COLS = 2 * MR;
+    constexpr int GL = (GV_UNIT_K / MPU) / 8;
+    const int ppr = K >> 3, total = M * ppr;
+    const uint4 *x16 = reinterpret_cast<const uint4 *>(x);
+    constexpr int BATCH = 4;
+    for (int base = 0; base < total; base += BATCH * CH_CONS_THREADS) {
+        uint4 v[BATCH];
+#pragma unroll
+        for (int r = 0; r < BATCH; ++r) {
+            const int i = base + r * CH_CONS_THREADS + tid;
+            v[r] = i < total ? __ldcg(x16 + i) : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int r = 0; r < BATCH; ++r) {
+            const int i = base + r * CH_CONS_THREADS + tid;
+            if (base + r * CH_CONS_THREADS >= total) break;               // warp-uniform
+            const uint32_t w4[4] = {v[r].x, v[r].y, v[r].z, v[r].w};
+            uint32_t mx = 0;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) mx = max(mx, max(w4[q] & 0x7FFFu, (w4[q] >> 16) & 0x7FFFu));
+#pragma unroll
+            for (int o = GL / 2; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            int E = (int)(mx >> 7);
+            E = min(max(E, 14), 254);
+            const float scale = __int_as_float((267 - E) << 23);     // max|x| lands in [2^13, 2^14)
+            uint32_t pk[4];
+            int sum = 0;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float lo = fmaf(__uint_as_float(w4[q] << 16), scale, 12582912.f);
+                const float hi = fmaf(__uint_as_float(w4[q] & 0xFFFF0000u), scale, 12582912.f);
+                pk[q] = __byte_perm(__float_as_uint(lo), __float_as_uint(hi), 0x5410);
+                sum = __dp2a_lo((int)pk[q], 0x0101, sum);
+            }
+#pragma unroll
+            for (int o = GL / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+            if (i < total) {
+                const int m = MR == 1 ? 0 : (i >= ppr) + (MR > 2 ? (i >= 2 * ppr) + (i >= 3 * ppr) : 0);
+                const int c = i - m * ppr;
+                const int j = (c & 15) >> 1;
+                uint8_t *dst = xs + ((size_t)(((c >> 4) * 4 + (j >> 1)) * 4 + 2 * (c & 1)) * COLS + 2 * m) * 8 + (j & 1) * 4;
+                uint32_t hiP[4], loP[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) { hiP[q] = (pk[q] >> 7) & 0x00FF00FFu; loP[q] = pk[q] & 0x007F007Fu; }
+                uint32_t v0 = hiP[0] | (hiP[1] << 8), v1 = loP[0] | (loP[1] << 8);
+                uint32_t v2 = hiP[2] | (hiP[3] << 8), v3 = loP[2] | (loP[3] << 8);
+                if constexpr (MR >= 2) {   // rotate the order of the four stores per lane group: 16-way -> 4-way bank conflicts
+                    const int rot = (lane >> 2) & 3;
+                    if (rot & 1) { const uint32_t tv = v0; v0 = v1; v1 = v2; v2 = v3; v3 = tv; }
+                    if (rot & 2) { uint32_t tv = v0; v0 = v2; v2 = tv; tv = v1; v1 = v3; v3 = tv; }
+                    const uint32_t vv[4] = {v0, v1, v2, v3};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int idx = (k + rot) & 3;
+                        *reinterpret_cast<uint32_t *>(dst + (idx & 1) * 8 + (idx >> 1) * (COLS * 8)) = vv[k];
+                    }
+                } else {
+                    *reinterpret_cast<uint32_t *>(dst) = v0;
+                    *reinterpret_cast<uint32_t *>(dst + 8) = v1;
+                    *reinterpret_cast<uint32_t *>(dst + COLS * 8) = v2;
+                    *reinterpret_cast<uint32_t *>(dst + COLS * 8 + 8) = v3;
+                }
+                if ((c & (GL - 1)) == 0)
+                    gtab[(size_t)(c / GL) * MR + m] = make_int2(sum, mx >= 0x7F80u ? 0x7FC00000 : (E - 13) << 23);
+            }
+        }
+    }
+}
+
+// The row blocks of one linear that belong to this consumer group: stage after stage from the ring.
+// pos = {slot, parity} of the group's next stage; advanced here over the group's own stages and over the other
+// group's (`skip` stages after every row block).
+template <int MR, int MPU, bool HOIST>
+__device__ __forceinline__ void ch_row_blocks(const ChainParams &p, const ChainOp &op, int n_slots, int gi, int wi, int lane,
+                                              uint32_t ring, uint32_t bar_full, uint32_t bar_empty, uint32_t xs_u32, uint32_t gtab_u32,
+                                              float2 *part, int &slot, uint32_t &parity) {
+    constexpr int COLS = 2 * MR;
+    constexpr int IPG = 4 / MPU;
+    constexpr uint32_t STAGE_W = 32 * GV_UNIT_BYTES;
+    constexpr uint32_t XU = 4 * 4 * COLS * 8;  // bytes of B fragments per unit
+    constexpr uint32_t GU = MPU * MR * 8;      // bytes of group table per unit
+    const int g = lane >> 2, t = lane & 3;
+    const uint32_t xs_l = xs_u32 + (uint32_t)((t * COLS + (g & (COLS - 1))) * 8);
+    const uint32_t gt_l = gtab_u32 + (uint32_t)((t & (MR - 1)) * 8);
+    const bool b_lane = COLS >= 8 || g < COLS;   // only the lanes of the data columns need real B values
+
+    uint32_t bq[HOIST ? CH_UPW : 1][4][2];
+    int gX[HOIST ? CH_UPW : 1];
+    float gE[HOIST ? CH_UPW : 1];
+    if constexpr (HOIST) {   // K = 4096: the warp meets the same four k-units in every row block
+#pragma unroll
+        for (int j = 0; j < CH_UPW; ++j) {
+            const uint32_t xk = xs_l + (uint32_t)(wi + 8 * j) * XU;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                bq[j][i][0] = 0; bq[j][i][1] = 0;
+                if (b_lane) asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(bq[j][i][0]), "=r"(bq[j][i][1]) : "r"(xk + (uint32_t)(i * 4 * COLS * 8)));
+            }
+            int e2b;
+            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(gX[j]), "=r"(e2b) : "r"(gt_l + (uint32_t)(wi + 8 * j) * GU));
+            gE[j] = __int_as_float(e2b);
+        }
+    }
+    const uint32_t offW = (uint32_t)(wi * GV_UNIT_BYTES + lane * 16);
+    const uint32_t offM = STAGE_W + (uint32_t)(wi * MPU * META_BYTES);
+    const int spr = op.spr, skip = spr * (CH_GROUPS - 1);
+    for (int s = gi; s < n_slots; s += CH_GROUPS) {
+        float y0 = 0.f, y1 = 0.f;                  // rows g / g+8 of this row block, token slot t
+        for (int m = 0; m < spr; ++m) {
+            const uint32_t sb = ring + (uint32_t)slot * (uint32_t)p.slot_stride;
+            gv_mbar_wait(bar_full + 8 * slot, parity);
+            uint32_t w[CH_UPW][8], s2[CH_UPW][MPU], zb[CH_UPW][MPU];
+#pragma unroll
+            for (int j = 0; j < CH_UPW; ++j) {
+                const uint32_t sw = sb + offW + (uint32_t)(8 * j * GV_UNIT_BYTES), sm = sb + offM + (uint32_t)(8 * j * MPU * META_BYTES);
+                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]) : "r"(sw));
+                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4+512];" : "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7]) : "r"(sw));
+#pragma unroll
+                for (int h = 0; h < MPU; ++h) {
+                    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(s2[j][h]) : "r"(sm + h * META_BYTES + 4 * g));
+                    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(zb[j][h]) : "r"(sm + h * META_BYTES + META_ZERO_OFF + g));
+                }
+            }
+            __syncwarp();                       // every lane holds its words: the slot may be refilled
+            if (lane == 0) ch_mbar_arrive(bar_empty + 8 * slot);
+            int acc[CH_UPW][MPU][4];
+#pragma unroll
+            for (int j = 0; j < CH_UPW; ++j)
+#pragma unroll
+                for (int h = 0; h < MPU; ++h)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) acc[j][h][q] = 0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+#pragma unroll
+                for (int j = 0; j < CH_UPW; ++j) {
+                    const uint32_t wa = w[j][2 * i], wb = w[j][2 * i + 1];
+                    uint32_t b0, b1;
+                    if constexpr (HOIST) {
+                        b0 = bq[j][i][0]; b1 = bq[j][i][1];
+                    } else {
+                        b0 = 0; b1 = 0;
+                        if (b_lane)
+                            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(b0), "=r"(b1)
+                                         : "r"(xs_l + (uint32_t)(32 * m + wi + 8 * j) * XU + (uint32_t)(i * 4 * COLS * 8)));
+                    }
+                    // rows g: the low nibbles; rows g+8: the RAW bytes 16 q[g+8] + q[g] (rows g are subtracted afterwards)
+                    ch_imma(acc[j][i / IPG], wa & 0x0F0F0F0Fu, wa, wb & 0x0F0F0F0Fu, wb, b0, b1);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < CH_UPW; ++j) {
+#pragma unroll
+                for (int h = 0; h < MPU; ++h) {
+                    int X;
+                    float e2;
+                    if constexpr (HOIST) {
+                        X = gX[j]; e2 = gE[j];
+                    } else {
+                        int e2b;
+                        asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(X), "=r"(e2b)
+                                     : "r"(gt_l + (uint32_t)(32 * m + wi + 8 * j) * GU + (uint32_t)(h * MR * 8)));
+                        e2 = __int_as_float(e2b);
+                    }
+                    const int tg = acc[j][h][0] * 128 + acc[j][h][1];
+                    const int tr = acc[j][h][2] * 128 + acc[j][h][3];
+                    const int ug = tg - (int)(zb[j][h] & 0x0Fu) * X;
+                    const int ug8 = tr - tg - (int)(zb[j][h] & 0xF0u) * X;          // 16 * (row g+8 - z8 * X)
+                    const float slo = __uint_as_float(s2[j][h] << 16) * e2;
+                    const float shi = __uint_as_float(s2[j][h] & 0xFFFF0000u) * (e2 * 0.0625f);
+                    y0 = fmaf(slo, (float)ug, y0);
+                    y1 = fmaf(shi, (float)ug8, y1);
+                }
+            }
+            if (++slot == p.S) { slot = 0; parity ^= 1u; }
+        }
+        if (t < MR) part[(((size_t)s * CH_GWARPS + wi) * 8 + g) * MR + t] = make_float2(y0, y1);
+        slot += skip;                               // the other group's stages of the next row block
+        while (slot >= p.S) { slot -= p.S; parity ^= 1u; }
+    }
+}
+
+template <int MR, int MPU>
+__global__ void __maxnreg__(112) chain_kernel(const ChainParams p) {
+    extern __shared__ __align__(128) uint8_t ch_smem[];
+    uint8_t *xs = ch_smem + p.off_xs;
+    int2 *gtab = reinterpret_cast<int2 *>(ch_smem + p.off_gtab);
+    float2 *part = reinterpret_cast<float2 *>(ch_smem + p.off_part);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int cta = blockIdx.x, grid = gridDim.x;
+    const uint32_t bar_full = gv_smem_u32(ch_smem), bar_empty = bar_full + 8 * CH_MAX_STAGES;
+    const uint32_t ring = gv_smem_u32(ch_smem + p.off_ring);
+    constexpr uint32_t STAGE_W = 32 * GV_UNIT_BYTES, STAGE_M = 32 * MPU * META_BYTES;
+
+    if (tid == 0) {
+        for (int s = 0; s < p.S; ++s) { gv_mbar_init(bar_full + 8 * s, 1); gv_mbar_init(bar_empty + 8 * s, CH_GWARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (warp == CH_CONS_WARPS) {
+        // ---- producer: the CTA's share of every linear's W4T stream, in chain order, as fast as slots come free.
+        //      Weights are immutable, so this neither waits for the previous kernel nor for the grid barriers. ----
+        if (lane == 0) {
+            int slot = 0;
+            uint32_t parity = 1u;                    // first round: slots are free (wait on the phase before the first)
+            for (int o = 0; o < p.n_ops; ++o) {
+                const ChainOp *op = p.ops + o;
+                const int *rb = op->rb;
+                const int R0 = __ldg(rb + cta), R1 = __ldg(rb + cta + 1);
+                const int nst = (R1 - R0) * op->spr;
+                const size_t unit0 = (size_t)R0 * op->UPR;
+                const uint8_t *w = op->qw + unit0 * GV_UNIT_BYTES;
+                const uint8_t *m = op->meta + unit0 * (MPU * META_BYTES);
+                for (int s = 0; s < nst; ++s) {
+                    gv_mbar_wait(bar_empty + 8 * slot, parity);
+                    const uint32_t bar = bar_full + 8 * slot, dst = ring + (uint32_t)slot * (uint32_t)p.slot_stride;
+                    gv_mbar_expect_tx(bar, STAGE_W + STAGE_M);
+                    gv_bulk_g2s(dst, w, STAGE_W, bar);
+                    gv_bulk_g2s(dst + STAGE_W, m, STAGE_M, bar);
+                    w += STAGE_W; m += STAGE_M;
+                    if (++slot == p.S) { slot = 0; parity ^= 1u; }
+                }
+            }
+        }
+        return;
+    }
+
+    // ---- consumers ----
+    const int gi = warp / CH_GWARPS, wi = warp % CH_GWARPS;
+    const unsigned int run = p.n_ops > 1 ? __ldcg(p.runs) : 0u;
+    const unsigned long long bar_base = (unsigned long long)run * (unsigned long long)(p.n_ops - 1);
+    auto stamp = [&](int o, int i) {
+        if (p.dbg && tid == 0) {
+            unsigned long long tt;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt));
+            p.dbg[((size_t)o * grid + cta) * CH_DBG_WORDS + i] = tt;
+        }
+    };
+    asm volatile("griddepcontrol.wait;" ::: "memory");   // the first x may come from the previous kernel
+    int slot = 0;                                         // ring position of the CTA's first stage of the current linear
+    uint32_t parity = 0u;
+    for (int o = 0; o < p.n_ops; ++o) {
+        const ChainOp op = p.ops[o];
+        const int R0 = __ldg(op.rb + cta), n_slots = __ldg(op.rb + cta + 1) - R0;
+        stamp(o, 0);
+        if (o + 1 == p.n_ops) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+        ch_stage_x<MR, MPU>(op.x, xs, gtab, op.M, op.K, tid, lane);
+        ch_bar_consumers();
+        stamp(o, 1);
+        // this group's first stage: gi row blocks further on
+        int gslot = slot + gi * op.spr;
+        uint32_t gpar = parity;
+        while (gslot >= p.S) { gslot -= p.S; gpar ^= 1u; }
+        if (MPU == 1 && op.hoist)
+            ch_row_blocks<MR, MPU, MPU == 1>(p, op, n_slots, gi, wi, lane, ring, bar_full, bar_empty, gv_smem_u32(xs), gv_smem_u32(gtab), part, gslot, gpar);
+        else
+            ch_row_blocks<MR, MPU, false>(p, op, n_slots, gi, wi, lane, ring, bar_full, bar_empty, gv_smem_u32(xs), gv_smem_u32(gtab), part, gslot, gpar);
+        slot += n_slots * op.spr;
+        while (slot >= p.S) { slot -= p.S; parity ^= 1u; }
+        ch_bar_consumers();
+        stamp(o, 2);
+        // combine the 8 warps of every row block (fixed tree: deterministic) and write y
+        for (int i = tid; i < n_slots * 32 * MR; i += CH_CONS_THREADS) {      // multiples of 32: whole warps
+            const int q = i & 3, e = (i >> 2) & (8 * MR - 1), sl = i / (32 * MR);
+            const float2 *src = part + ((size_t)sl * CH_GWARPS + 2 * q) * 8 * MR + e;
+            float2 v = src[0];
+            const float2 o2 = src[8 * MR];
+            v.x += o2.x; v.y += o2.y;
+            v.x += __shfl_xor_sync(0xffffffffu, v.x, 1); v.y += __shfl_xor_sync(0xffffffffu, v.y, 1);
+            v.x += __shfl_xor_sync(0xffffffffu, v.x, 2); v.y += __shfl_xor_sync(0xffffffffu, v.y, 2);
+            const int tok = e % MR, n0 = (R0 + sl) * 16 + e / MR;
+            if (q == 0 && tok < op.M) {
+                const float b0 = op.bias ? __bfloat162float(op.bias[n0]) : 0.f;
+                const float b1 = op.bias ? __bfloat162float(op.bias[n0 + 8]) : 0.f;
+                if (op.swiglu) {   // rows g / g+8 are (gate, up) of output column 8 R + g
+                    op.y[(size_t)tok * (op.N >> 1) + (n0 >> 4) * 8 + (n0 & 7)] = swiglu_bf16(v.x + b0, v.y + b1);
+                } else {
+                    op.y[(size_t)tok * op.N + n0] = __float2bfloat16_rn(v.x + b0);
+                    op.y[(size_t)tok * op.N + n0 + 8] = __float2bfloat16_rn(v.y + b1);
+                }
+            }
+        }
+        if (o + 1 < p.n_ops) {
+            // grid barrier: every CTA's y of linear o is visible before anybody stages it as the x of linear o + 1
+            __threadfence();
+            ch_bar_consumers();
+            if (tid == 0) {
+                const unsigned long long target = (bar_base + (unsigned long long)o + 1ull) * (unsigned long long)grid;
+                asm volatile("red.release.gpu.global.add.u64 [%0], 1;" ::"l"(p.counter) : "memory");
+                unsigned long long seen;
+                uint32_t spins = 0;
+                do {
+                    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(seen) : "l"(p.counter) : "memory");
+                    if (++spins > GV_SPIN_LIMIT) __trap();
+                } while (seen < target);
+            }
+            ch_bar_consumers();
+        }
+        stamp(o, 3);
+    }
+    if (p.n_ops > 1 && cta == 0 && tid == 0) *p.runs = run + 1u;   // everybody read `runs` before the first barrier
+}
+
+// ---- host side ------------------------------------------------------------------------------------------------------
+struct Chain {
+    int device = 0, n = 0;
+    int64_t M = 0;
+    std::vector<Linear *> lin;
+    std::vector<const __nv_bfloat16 *> x;
+    std::vector<__nv_bfloat16 *> y;
+    bool persistent = false;       // the chain kernel takes it; otherwise the linears are launched one by one
+    std::string why_not;
+    ChainOp *d_ops = nullptr;
+    int *d_rb = nullptr;
+    unsigned long long *d_counter = nullptr;
+    unsigned int *d_runs = nullptr;
+    unsigned long long *d_dbg = nullptr;
+    ChainParams prm{};
+    int MR = 1, mpu = 1, smem = 0, grid = 0;
+};
+
+template <int MR, int MPU>
+static int chain_launch_t(const Chain &c, cudaStream_t stream, bool pdl) {
+    static bool attr_set[64] = {};
+    if (c.device >= 0 && c.device < 64 && !attr_set[c.device]) {
+        W4_CUDA_OK(cudaFuncSetAttribute(chain_kernel<MR, MPU>, cudaFuncAttributeMaxDynamicSharedMemorySize, CH_SMEM_MAX));
+        attr_set[c.device] = true;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)c.grid);
+    cfg.blockDim = dim3(CH_THREADS);
+    cfg.dynamicSmemBytes = (size_t)c.smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    W4_CUDA_OK(cudaLaunchKernelEx(&cfg, chain_kernel<MR, MPU>, c.prm));
+    count_launch();
+    return 0;
+}
+
+static int chain_launch(const Chain &c, cudaStream_t stream) {
+    const bool pdl = gv_env_int("W4A16_NO_PDL", 0) == 0;
+#define W4_CH(MR_)                                                       \
+    do {                                                                 \
+        if (c.mpu == 1) return chain_launch_t<MR_, 1>(c, stream, pdl);   \
+        if (c.mpu == 2) return chain_launch_t<MR_, 2>(c, stream, pdl);   \
+        return chain_launch_t<MR_, 4>(c, stream, pdl);                   \
+    } while (0)
+    switch (c.MR) {
+        case 1: W4_CH(1);
+        case 2: W4_CH(2);
+        default: W4_CH(4);
+    }
+#undef W4_CH
+}
+
+static void chain_free(Chain *c) {
+    if (!c) return;
+    cudaFree(c->d_ops); cudaFree(c->d_rb); cudaFree(c->d_counter); cudaFree(c->d_runs); cudaFree(c->d_dbg);
+    delete c;
+}
+
+// Decides whether the persistent kernel takes the chain and builds its device tables.
+static int chain_plan(Chain *c) {
+    c->persistent = false;
+    if (gv_env_int("W4A16_NO_CHAIN_KERNEL", 0)) { c->why_not = "disabled by W4A16_NO_CHAIN_KERNEL"; return 0; }
+    if (c->M > 4) { c->why_not = "more than 4 tokens"; return 0; }
+    if (c->n > CH_MAX_OPS) { c->why_not = "too many linears"; return 0; }
+    DeviceScratch *ds = nullptr;
+    if (get_device_scratch(c->device, &ds)) return 1;
+    const int grid = ds->sm_count;
+    int gs = 0;
+    int64_t maxK = 0, max_slots = 1;
+    for (Linear *L : c->lin) {
+        if (L->d.K % (32 * GV_UNIT_K)) { c->why_not = "in_features not a multiple of 4096"; return 0; }
+        if (L->d.gs != 32 && L->d.gs != 64 && L->d.gs != 128) { c->why_not = "group size not 32 / 64 / 128"; return 0; }
+        if (gs && L->d.gs != gs) { c->why_not = "mixed group sizes"; return 0; }
+        if (L->perm && !L->perm_external) { c->why_not = "act-order linear (activation gather)"; return 0; }
+        if (L->d.NR * (L->d.K / GV_UNIT_K) >= ((int64_t)1 << 30)) { c->why_not = "linear too large"; return 0; }
+        gs = L->d.gs;
+        maxK = std::max(maxK, L->d.K);
+        max_slots = std::max<int64_t>(max_slots, (L->d.NR + grid - 1) / grid);
+    }
+    c->mpu = 128 / gs;
+    c->MR = c->M <= 1 ? 1 : c->M <= 2 ? 2 : 4;
+    int64_t off = 2 * 8 * CH_MAX_STAGES;
+    off = (off + 127) & ~(int64_t)127;
+    const int off_xs = (int)off; off += maxK * 2 * c->MR;
+    const int off_gtab = (int)off; off += (maxK / gs) * c->MR * 8;
+    off = (off + 15) & ~(int64_t)15;
+    const int off_part = (int)off; off += max_slots * CH_GWARPS * 8 * c->MR * 8;
+    off = (off + 127) & ~(int64_t)127;
+    const int64_t stride = 32 * (GV_UNIT_BYTES + c->mpu * META_BYTES);
+    int64_t S = (CH_SMEM_MAX - off) / stride;
+    if (S < 3) { c->why_not = "activations leave no room for a ring of 3 stages"; return 0; }
+    S = std::min<int64_t>(S, std::min<int64_t>(CH_MAX_STAGES, gv_env_int("W4A16_CHAIN_STAGES", CH_MAX_STAGES)));
+    const int off_ring = (int)off; off += S * stride;
+    c->smem = (int)off;
+    c->grid = grid;
+
+    std::vector<int> rb((size_t)c->n * (grid + 1));
+    std::vector<ChainOp> ops(c->n);
+    W4_CUDA_OK(cudaMalloc(&c->d_rb, rb.size() * sizeof(int)));
+    for (int i = 0; i < c->n; ++i) {
+        Linear *L = c->lin[i];
+        for (int k = 0; k <= grid; ++k) rb[(size_t)i * (grid + 1) + k] = (int)((int64_t)k * L->d.NR / grid);
+        ChainOp &o = ops[i];
+        o.qw = reinterpret_cast<const uint8_t *>(L->qw);
+        o.meta = L->meta;
+        const bool add_bias = L->tp_mode != W4A16_TP_ROW || L->tp_size == 1;
+        o.bias = add_bias && L->has_bias ? L->bias : nullptr;
+        o.x = c->x[i]; o.y = c->y[i];
+        o.rb = c->d_rb + (size_t)i * (grid + 1);
+        o.M = (int)c->M; o.K = (int)L->d.K; o.N = (int)L->d.N;
+        o.UPR = (int)(L->d.K / GV_UNIT_K);
+        o.spr = o.UPR / 32;
+        o.swiglu = L->epilogue == W4A16_EPILOGUE_SWIGLU;
+        o.hoist = o.spr == 1 && c->mpu == 1;
+        o.pad = 0;
+    }
+    W4_CUDA_OK(cudaMemcpy(c->d_rb, rb.data(), rb.size() * sizeof(int), cudaMemcpyHostToDevice));
+    W4_CUDA_OK(cudaMalloc(&c->d_ops, ops.size() * sizeof(ChainOp)));
+    W4_CUDA_OK(cudaMemcpy(c->d_ops, ops.data(), ops.size() * sizeof(ChainOp), cudaMemcpyHostToDevice));
+    W4_CUDA_OK(cudaMalloc(&c->d_counter, sizeof(unsigned long long)));
+    W4_CUDA_OK(cudaMemset(c->d_counter, 0, sizeof(unsigned long long)));
+    W4_CUDA_OK(cudaMalloc(&c->d_runs, sizeof(unsigned int)));
+    W4_CUDA_OK(cudaMemset(c->d_runs, 0, sizeof(unsigned int)));
+    if (gv_env_int("W4A16_GV_DEBUG", 0)) {
+        const size_t words = (size_t)c->n * grid * CH_DBG_WORDS;
+        W4_CUDA_OK(cudaMalloc(&c->d_dbg, words * sizeof(unsigned long long)));
+        W4_CUDA_OK(cudaMemset(c->d_dbg, 0, words * sizeof(unsigned long long)));
+    }
+    ChainParams &p = c->prm;
+    p.ops = c->d_ops; p.n_ops = c->n;
+    p.counter = c->d_counter; p.runs = c->d_runs;
+    p.S = (int)S; p.slot_stride = (int)stride;
+    p.off_xs = off_xs; p.off_gtab = off_gtab; p.off_part = off_part; p.off_ring = off_ring;
+    p.dbg = c->d_dbg;
+    c->persistent = true;
+    return 0;
+}
+
+int forward_linear(Linear *L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, cudaStream_t stream);   // w4a16_api.cu
+
+}  // namespace w4
+
+using namespace w4;
+
+extern "C" {
+
+int w4a16_chain_create(w4a16_chain_t *out, int n, const w4a16_handle_t *handles, const void *const *x, void *const *y, int64_t M) {
+    if (!out) return fail("chain_create: null out");
+    *out = nullptr;
+    if (n < 1 || !handles || !x || !y) return fail("chain_create: need at least one linear and its x / y pointers");
+    if (M < 1) return fail("chain_create: M must be >= 1");
+    Chain *c = new Chain();
+    c->n = n; c->M = M;
+    for (int i = 0; i < n; ++i) {
+        Linear *L = reinterpret_cast<Linear *>(handles[i]);
+        if (!L) { chain_free(c); return fail("chain_create: null handle at position " + std::to_string(i)); }
+        if (!L->loaded) { chain_free(c); return fail("chain_create: weights not loaded (call load_weights first) at position " + std::to_string(i)); }
+        if (i == 0) c->device = L->device;
+        if (L->device != c->device) { chain_free(c); return fail("chain_create: all linears must live on one device"); }
+        if (!x[i] || !y[i]) { chain_free(c); return fail("chain_create: null x or y at position " + std::to_string(i)); }
+        if ((reinterpret_cast<uintptr_t>(x[i]) & 15) || (reinterpret_cast<uintptr_t>(y[i]) & 15)) {
+            chain_free(c);
+            return fail("chain_create: x and y must be 16-byte aligned");
+        }
+        c->lin.push_back(L);
+        c->x.push_back(reinterpret_cast<const __nv_bfloat16 *>(x[i]));
+        c->y.push_back(reinterpret_cast<__nv_bfloat16 *>(y[i]));
+    }
+    int prev = 0;
+    cudaGetDevice(&prev);
+    cudaSetDevice(c->device);
+    const int rc = chain_plan(c);
+    cudaSetDevice(prev);
+    if (rc) { chain_free(c); return 1; }
+    *out = reinterpret_cast<w4a16_chain_t>(c);
+    return 0;
+}
+
+int w4a16_chain_run(w4a16_chain_t chain, w4a16_stream_t stream) {
+    Chain *c = reinterpret_cast<Chain *>(chain);
+    if (!c) return fail("chain_run: null chain");
+    int prev = 0;
+    cudaGetDevice(&prev);
+    if (prev != c->device) cudaSetDevice(c->device);
+    int rc = 0;
+    if (c->persistent) {
+        rc = chain_launch(*c, reinterpret_cast<cudaStream_t>(stream));
+    } else {
+        for (int i = 0; i < c->n && !rc; ++i)
+            rc = forward_linear(c->lin[i], c->x[i], c->y[i], c->M, reinterpret_cast<cudaStream_t>(stream));
+    }
+    if (prev != c->device) cudaSetDevice(prev);
+    return rc;
+}
+
+const char *w4a16_chain_kernel(w4a16_chain_t chain) {
+    Chain *c = reinterpret_cast<Chain *>(chain);
+    if (!c) return "";
+    if (c->persistent) return "chain_imma";
+    static thread_local std::string s;
+    s = "per_linear (" + c->why_not + ")";
+    return s.c_str();
+}
+
+int w4a16_chain_destroy(w4a16_chain_t chain) {
+    chain_free(reinterpret_cast<Chain *>(chain));
+    return 0;
+}
+
+int w4a16_chain_debug_stamps(w4a16_chain_t chain, uint64_t *out, int64_t words) {
+    Chain *c = reinterpret_cast<Chain *>(chain);
+    if (!c || !c->d_dbg) return fail("chain_debug_stamps: no stamps (set W4A16_GV_DEBUG=1 before chain_create)");
+    const int64_t have = (int64_t)c->n * c->grid * CH_DBG_WORDS;
+    if (words < have) return fail("chain_debug_stamps: buffer too small, need " + std::to_string(have) + " words");
+    W4_CUDA_OK(cudaDeviceSynchronize());
+    W4_CUDA_OK(cudaMemcpy(out, c->d_dbg, (size_t)have * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+}  // extern "C"

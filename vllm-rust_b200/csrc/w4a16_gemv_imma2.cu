@@ -108,6 +108,11 @@ __global__ void __launch_bounds__(G2_THREADS, 2) gemv_imma2_kernel(const GemvPar
                 for (int q = 0; q < 4; ++q) mx = max(mx, max(w4[q] & 0x7FFFu, (w4[q] >> 16) & 0x7FFFu));
 #pragma unroll
                 for (int o = GL / 2; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+                if (p.dbg && tid == 0 && base == 0 && r == 0) {   // stamp 6: the first activation load has arrived
+                    unsigned long long tt;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt));
+                    p.dbg[(size_t)cta * 8 + 6] = tt;
+                }
                 int E = (int)(mx >> 7);
                 E = min(max(E, 14), 254);
                 const float scale = __int_as_float((267 - E) << 23);     // max|x| lands in [2^13, 2^14)

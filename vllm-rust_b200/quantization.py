@@ -721,6 +721,64 @@ def create_weight_loader_with_params(tensors: Mapping[str, torch.Tensor], detect
     return GptqWeightLoader(tensors, cfg, device, cache_dir)
 
 
+class DecodeChain:
+    """A fixed sequence of decode linears (M <= 4 tokens) run by one call -- the reference's per-layer call order
+    (qwen3_quantized.rs:704-709 q/k/v/o, :532-551 gate/up -> silu*mul -> down) as its CUDA-graph replay sees it
+    (engine/cuda_graph.rs).  `steps` is a list of (linear, x, y): x [M, in_features] and y [M, out_features] bf16
+    CUDA tensors that stay alive and in place for the life of the chain (like graph arguments); linear i+1 may read
+    what linear i wrote.  Where the shapes allow it run() is ONE persistent launch (`kernel()` == "chain_imma"),
+    otherwise the chain calls the linears one by one."""
+
+    def __init__(self, steps: Sequence):
+        steps = list(steps)
+        if not steps:
+            raise W4A16Error("DecodeChain: need at least one (linear, x, y) step")
+        m = steps[0][1].shape[0]
+        self._keep = steps
+        n = len(steps)
+        hs, xs, ys = (ctypes.c_void_p * n)(), (ctypes.c_void_p * n)(), (ctypes.c_void_p * n)()
+        for i, (lin, x, y) in enumerate(steps):
+            inner = getattr(lin, "inner", lin)   # Column/RowParallel wrappers expose their local linear
+            inner._check_x(x)
+            if x.dim() != 2 or y.dim() != 2 or not x.is_contiguous() or not y.is_contiguous():
+                raise W4A16Error("DecodeChain: x and y must be contiguous rank-2 tensors")
+            if x.shape[0] != m or y.shape[0] != m:
+                raise W4A16Error(f"DecodeChain: every step must have the same M = {m}")
+            if y.dtype != torch.bfloat16 or y.shape[1] != inner.out_features() or not y.is_cuda:
+                raise W4A16Error(f"DecodeChain: y of step {i} must be a CUDA bf16 tensor [M, {inner.out_features()}]")
+            hs[i], xs[i], ys[i] = inner._h, x.data_ptr(), y.data_ptr()
+        self._device = steps[0][1].device
+        self._c = ctypes.c_void_p()
+        check(lib().w4a16_chain_create(ctypes.byref(self._c), n, hs, xs, ys, m))
+        self._n, self._m = n, m
+
+    def __del__(self):
+        c = getattr(self, "_c", None)
+        if c:
+            try:
+                lib().w4a16_chain_destroy(c)
+            except Exception:
+                pass
+            self._c = None
+
+    def __len__(self) -> int:
+        return self._n
+
+    def kernel(self) -> str:
+        return lib().w4a16_chain_kernel(self._c).decode()
+
+    def run(self) -> None:
+        check(lib().w4a16_chain_run(self._c, torch.cuda.current_stream(self._device).cuda_stream))
+
+    def debug_stamps(self):
+        """[n, CTAs, 4] %globaltimer stamps of the last run (W4A16_GV_DEBUG=1 at creation)."""
+        import numpy as np
+        sms = torch.cuda.get_device_properties(self._device).multi_processor_count
+        buf = np.zeros((self._n, sms, 4), dtype=np.uint64)
+        check(lib().w4a16_chain_debug_stamps(self._c, ctypes.c_void_p(buf.ctypes.data), buf.size))
+        return buf
+
+
 def kernel_launches() -> int:
     return int(lib().w4a16_kernel_launches())
 
