@@ -189,6 +189,25 @@ def build_layers(P, torch, shapes, n_layers, device, comm=None, seed=0, peers=No
     return layers
 
 
+def chain_steps(torch, layers, M, dev):
+    """(linear, x, y) of every linear of the step with the data flow of the model wherever the shapes allow it: one
+    output buffer per shape (re-used layer after layer, as a CUDA-graph replay re-uses its buffers), and every linear
+    reads the previous linear's output -- all of it when the widths agree, at M = 1 also a leading part of it
+    (qkv 6144 -> o 4096 stands in for attention, gate_up 24576 -> down 12288 for silu*mul); otherwise its own x."""
+    ys, xs, steps, prev = {}, {}, [], None
+    for name, K, N, Kl, Nl, mode, lin in layers:
+        y = ys.setdefault((name, Nl), torch.zeros((M, Nl), device=dev, dtype=torch.bfloat16))
+        if prev is not None and prev.shape[1] == Kl:
+            x = prev
+        elif prev is not None and M == 1 and prev.shape[1] > Kl:
+            x = prev[:, :Kl]
+        else:
+            x = xs.setdefault((name, Kl), (torch.randn((M, Kl), device=dev, dtype=torch.float32) * 0.05).to(torch.bfloat16))
+        steps.append((lin, x, y))
+        prev = y
+    return steps
+
+
 def timed_steps(torch, dist, dev, run, stream, args, world, rank, local):
     for _ in range(args.warmup):
         run()

@@ -220,7 +220,8 @@ int w4a16_forward_row_fused(w4a16_handle_t h, const void *x_bf16, void *y_bf16, 
  * through one shared-memory ring that stays full across the boundaries between linears, and
  * consecutive linears are separated by a grid-wide barrier.  Otherwise chain_run makes the
  * n w4a16_forward_into calls itself (w4a16_chain_kernel tells which).  Results: those of
- * w4a16_forward_into (bit-identical for in_features == 4096; same bounds otherwise).
+ * w4a16_forward_into up to the summation order of the fp32 partial sums (same integer
+ * arithmetic, same bounds, same non-finite policy).
  * x / y pointers are fixed at creation, like the arguments of a captured graph; SwiGLU
  * handles and biases are honoured; a ROW shard writes its partial sum (no collective
  * inside a chain).  chain_run never allocates or synchronises and can be captured in a
@@ -232,7 +233,13 @@ int w4a16_chain_create(w4a16_chain_t *out, int n, const w4a16_handle_t *handles,
                        const void *const *x_bf16, void *const *y_bf16, int64_t M);
 int w4a16_chain_run(w4a16_chain_t chain, w4a16_stream_t stream);
 int w4a16_chain_destroy(w4a16_chain_t chain);
-/* "chain_imma" (persistent launch) or "per_linear (<reason>)". */
+/* "chain_imma (<m> mailboxes, <b> barriers)" (persistent launch) or "per_linear (<reason>)".
+ * Ordering inside the persistent launch: where x[i] lies inside the y of the latest earlier
+ * linear that wrote it (the normal case: x[i] == y[j], or at M = 1 any 16-byte aligned
+ * sub-range of it), that y is also stored into a chain-owned mailbox whose words hold a
+ * sentinel until written and linear i polls the mailbox -- no grid barrier, the data are
+ * their own flags.  Any other overlap between the buffers of two linears puts a grid-wide
+ * barrier in front of the later one.  Linears that share nothing are not ordered at all. */
 const char *w4a16_chain_kernel(w4a16_chain_t chain);
 /* Profiling hook (W4A16_GV_DEBUG=1 at chain_create): %globaltimer stamps
  * [n][CTAs][4] = {linear started, activations staged, weights streamed, y written + barrier passed}

@@ -4,10 +4,10 @@ The reference runs its quantized linears one launch at a time in a fixed per-lay
 532-551) and replays that order as a CUDA graph (engine/cuda_graph.rs).  The chain must give what those separate calls
 give.  Checks:
   * every linear of a chain against the float64 oracle (reference tolerance + the 1e-2 north-star bound) and against
-    the product's own per-linear w4a16_forward_into: bit-identical for in_features == 4096 (same kernel arithmetic and
-    summation order), within tolerance otherwise;
+    the product's own per-linear w4a16_forward_into (same integer arithmetic, another summation order of the fp32
+    partial sums: equal within a few bf16 ulps of max|y|);
   * a TRUE dependency chain (x[i+1] is y[i]): the grid barrier orders the write of one linear before the read of the
-    next -- compared with the same chain run call by call;
+    next -- every buffer of the chain must be the linear of the buffer before it, run after run on changing inputs;
   * M = 1..4, group sizes 32 / 64 / 128, bias, the SwiGLU handle (gate/up -> silu*mul -> down as a two-linear chain),
     row blocks fewer than CTAs, repeated runs (the barrier counter is monotonic over runs), CUDA-graph capture;
   * shapes the persistent kernel does not take fall back to per-linear launches with the same results, and say so;
@@ -45,7 +45,7 @@ def test_independent_linears_match_oracle_and_per_linear_calls(product, M, g):
         xs.append(t_bf16_from_bits(O.make_activations(M, K, seed=50 + i + M)).to(DEV))
         ys.append(torch.full((M, N), float("nan"), dtype=torch.bfloat16, device=DEV))
     chain = product.DecodeChain(list(zip(lins, xs, ys)))
-    assert chain.kernel() == "chain_imma" and len(chain) == len(shapes)
+    assert chain.kernel().startswith("chain_imma") and len(chain) == len(shapes)
     for rep in range(3):                       # the barrier counter keeps counting over runs
         for y in ys:
             y.fill_(float("nan"))
@@ -55,11 +55,8 @@ def test_independent_linears_match_oracle_and_per_linear_calls(product, M, g):
             q, z, sb, b = cks[i]
             want = oracle_forward(bits_of(xs[i]), q, z, sb, g, bias_f32=b)
             assert_close_ref(bits_of(ys[i]), want, f"chain linear {i} M={M} g={g} rep={rep}")
-            single = lins[i].forward(xs[i])
-            if K == 4096:
-                assert (bits_of(single) == bits_of(ys[i])).all(), f"linear {i}: chain != forward_into bit for bit"
-            else:
-                assert_close_ref(bits_of(single), want, "per-linear")
+            single = lins[i].forward(xs[i]).float()
+            assert float((single - ys[i].float()).abs().max()) <= 2.0 ** -6 * float(single.abs().max())
 
 
 @pytest.mark.parametrize("M", [1, 4])
@@ -91,34 +88,39 @@ def test_true_dependency_chain_equals_call_by_call(product, M):
         for lin in lins:
             bufs.append(torch.zeros((M, lin.out_features()), dtype=torch.bfloat16, device=DEV))
         return bufs
-    a, b = buffers(), buffers()
+    a = buffers()
     chain = product.DecodeChain([(lin, a[i], a[i + 1]) for i, lin in enumerate(lins)])
-    assert chain.kernel() == "chain_imma"
+    assert chain.kernel() == "chain_imma (7 mailboxes, 0 barriers)"
+
+    def check(tag):
+        torch.cuda.synchronize()
+        for i, lin in enumerate(lins):
+            want = lin.forward(a[i]).float()          # the linear of what the chain itself left in buffer i
+            got = a[i + 1].float()
+            assert torch.isfinite(got).all()
+            scale = float(want.abs().max())
+            assert scale > 0.0
+            assert float((want - got).abs().max()) <= 2.0 ** -6 * scale, f"{tag}: buffer {i + 1} is not linear {i} of buffer {i}"
+
     chain.run()
-    for i, lin in enumerate(lins):
-        lin.forward_into(b[i], b[i + 1])
-    torch.cuda.synchronize()
-    for i in range(1, len(a)):
-        assert torch.isfinite(a[i].float()).all()
-        assert (bits_of(a[i]) == bits_of(b[i])).all(), f"buffer {i} differs between the chain and the call-by-call run"
-    assert float(a[-1].float().abs().max()) > 0.0
+    check("first run")
+    for seed in (4, 5, 6):                      # stale data of the previous run would show
+        a[0].copy_(t_bf16_from_bits(O.make_activations(M, H, seed=seed)).to(DEV))
+        chain.run()
+        check(f"seed {seed}")
     # CUDA-graph capture + replay on fresh inputs
-    x1 = t_bf16_from_bits(O.make_activations(M, H, seed=4)).to(DEV)
     st = torch.cuda.Stream()
     with torch.cuda.stream(st):
         chain.run()
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph, stream=st):
             chain.run()
-        a[0].copy_(x1)
+            chain.run()                         # back to back: the second launch may start before the first has ended
+        a[0].copy_(t_bf16_from_bits(O.make_activations(M, H, seed=7)).to(DEV))
         graph.replay()
         graph.replay()
     st.synchronize()
-    b[0].copy_(x1)
-    for i, lin in enumerate(lins):
-        lin.forward_into(b[i], b[i + 1])
-    torch.cuda.synchronize()
-    assert (bits_of(a[-1]) == bits_of(b[-1])).all()
+    check("graph replay")
 
 
 def test_mlp_chain_k12288_against_oracle(product):
@@ -134,13 +136,44 @@ def test_mlp_chain_k12288_against_oracle(product):
     mid = torch.zeros((M, I), dtype=torch.bfloat16, device=DEV)
     y = torch.zeros((M, H), dtype=torch.bfloat16, device=DEV)
     chain = product.DecodeChain([(gu, x, mid), (down, mid, y)])
-    assert chain.kernel() == "chain_imma"
+    assert chain.kernel() == "chain_imma (1 mailboxes, 0 barriers)"
     chain.run()
     torch.cuda.synchronize()
-    mid_ref = gu.forward(x)
-    assert (bits_of(mid_ref) == bits_of(mid)).all()           # gate_up has K = 4096: same arithmetic as the single launch
+    mid_ref = gu.forward(x).float()
+    assert float((mid_ref - mid.float()).abs().max()) <= 2.0 ** -6 * float(mid_ref.abs().max())
     want = oracle_forward(bits_of(mid), q, z, sb, g)
     assert_close_ref(bits_of(y), want, "down after swiglu")
+
+
+@pytest.mark.parametrize("M", [1, 3])
+def test_ping_pong_buffers_get_barriers(product, M):
+    """Two buffers used alternately by linears of different widths: partial overlaps the mailboxes do not cover."""
+    g = 128
+    shapes = [(4096, 6144), (4096, 4096), (4096, 8192), (8192, 4096), (4096, 6144), (4096, 4096)]
+    lins = [make_linear(product, K, N, g, seed=70 + i)[0] for i, (K, N) in enumerate(shapes)]
+    width = 8192
+    bufs = [torch.zeros((M * width,), dtype=torch.bfloat16, device=DEV) for _ in range(2)]
+    def view(b, n):
+        return bufs[b][:M * n].view(M, n)
+    x0 = t_bf16_from_bits(O.make_activations(M, 4096, seed=11)).to(DEV) * 0.05
+    steps = [(lin, view(i & 1, K), view((i + 1) & 1, N)) for i, (lin, (K, N)) in enumerate(zip(lins, shapes))]
+    chain = product.DecodeChain(steps)
+    name = chain.kernel()
+    assert name.startswith("chain_imma") and "0 barriers" not in name
+    for rep in range(3):
+        view(0, 4096).copy_(x0 * (rep + 1))
+        chain.run()
+        torch.cuda.synchronize()
+        got = view(len(shapes) & 1, shapes[-1][1]).clone()
+        # the same sequence call by call (each call reads what the previous one left in the other buffer)
+        view(0, 4096).copy_(x0 * (rep + 1))
+        for lin, x, y in steps:
+            lin.forward_into(x, y)
+        torch.cuda.synchronize()
+        want = view(len(shapes) & 1, shapes[-1][1]).float()
+        scale = float(want.abs().max())
+        assert scale > 0 and torch.isfinite(want).all()
+        assert float((want - got.float()).abs().max()) <= 0.05 * scale    # six linears of compounding bf16 roundings
 
 
 def test_fallback_per_linear(product):

@@ -25,10 +25,8 @@ def main():
     dev = torch.device("cuda", 0)
     cfg = P.AwqConfig.int4(128)
     M = args.m
-    bufs = [torch.randn((M, 24576), device=dev).to(torch.bfloat16).contiguous() for _ in range(2)]
-    xs = {K: torch.randn((M, K), device=dev).to(torch.bfloat16) for _, K, _ in SHAPES}
-    ys = {N: torch.empty((M, N), device=dev, dtype=torch.bfloat16) for _, _, N in SHAPES}
-    steps, names = [], []
+    import bench
+    layers, names = [], []
     for c in range(args.layers):
         for name, K, N in SHAPES:
             qweight = torch.randint(-2**31, 2**31 - 1, (K, N // 8), dtype=torch.int32, device=dev)
@@ -36,12 +34,9 @@ def main():
             scales = (torch.rand((K // 128, N), device=dev) * 0.018 + 0.002).to(torch.float16)
             lin = cfg.create_linear(K, N, False, dev)
             lin.load_weights({"qweight": qweight, "qzeros": qzeros, "scales": scales})
-            i = len(steps)
-            if M == 1:
-                steps.append((lin, bufs[i & 1][:, :K], bufs[(i + 1) & 1][:, :N]))
-            else:
-                steps.append((lin, xs[K], ys[N]))
+            layers.append((name, K, N, K, N, None, lin))
             names.append(name)
+    steps = bench.chain_steps(torch, layers, M, dev)
     chain = P.DecodeChain(steps)
     print("kernel:", chain.kernel())
     st = torch.cuda.Stream(dev)

@@ -45,9 +45,10 @@ def main():
         for k, v in kv.items():
             os.environ[k] = v
         if args.api == "chain":
-            steps = []
-            for i, (name, K, N, Kl, Nl, mode, lin) in enumerate(layers):
-                steps.append((lin, bufs[i & 1][:, :K], bufs[(i + 1) & 1][:, :N]) if args.chain else (lin, xs[K], ys[N]))
+            if args.chain:
+                steps = bench.chain_steps(torch, layers, M, dev)
+            else:
+                steps = [(lin, xs[K], ys[N]) for name, K, N, Kl, Nl, mode, lin in layers]
             dchain = P.DecodeChain(steps)
             print("[ab] chain kernel:", dchain.kernel(), flush=True)
             step = dchain.run

@@ -15,7 +15,7 @@
 // Replaces, for the decode step, the per-linear launches of the reference's layer loop (qwen3_quantized.rs:704-709
 // attention projections, :532-551 gate/up -> silu*mul -> down; each one a marlin_gemm_pooled launch,
 // marlin_cuda.rs:1655-1753) and its CUDA-graph replay of that loop (engine/cuda_graph.rs).  Arithmetic, W4T stream and
-// the activation quantisation are those of gemv_imma2_kernel (see there); results are bit-identical to it for K = 4096.
+// the activation quantisation are those of gemv_imma_kernel / gemv_imma2_kernel (see there).
 #include <algorithm>
 #include <mutex>
 
@@ -23,10 +23,8 @@
 
 namespace w4 {
 
-constexpr int CH_GROUPS = 2;                          // consumer groups; group gi takes row blocks gi, gi + 2, ... of a CTA's range
-constexpr int CH_GWARPS = 8;                          // warps per group: 4 units each = one 32-unit stage per iteration
-constexpr int CH_UPW = 4;
-constexpr int CH_CONS_WARPS = CH_GROUPS * CH_GWARPS;
+constexpr int CH_CONS_WARPS = 16;                     // consumer warps: 2 units each = one 32-unit stage per iteration
+constexpr int CH_UPW = 2;
 constexpr int CH_CONS_THREADS = CH_CONS_WARPS * 32;   // 512
 constexpr int CH_THREADS = CH_CONS_THREADS + 32;      // + the producer warp
 constexpr int CH_MAX_STAGES = 8;
@@ -41,7 +39,12 @@ struct ChainOp {
     const int *rb;             // [grid + 1]: CTA c owns row blocks [rb[c], rb[c + 1])
     int M, K, N, UPR;
     int spr;                   // 32-unit stages per row block = K / 4096
-    int swiglu, hoist, pad;
+    int swiglu, hoist;
+    int barrier_before;        // a grid-wide barrier separates this linear from the one before it (hazards the mailboxes do not cover)
+    // Mailboxes: y of a linear that a later linear of the chain reads is ALSO stored into a chain-owned copy whose
+    // words hold the sentinel 0xFFFF until written; the reader polls that copy instead of waiting at a barrier.
+    unsigned short *mbox_out;        // parity-0 copy of this linear's y ([M][out width]) or null
+    const unsigned short *mbox_in;   // parity-0 address of this linear's x inside its producer's mailbox, or null (read op.x)
 };
 
 struct ChainParams {
@@ -49,6 +52,8 @@ struct ChainParams {
     int n_ops;
     unsigned long long *counter;   // grid-barrier arrivals, monotonic over the life of the chain
     unsigned int *runs;            // launches completed so far (read by every CTA at start, advanced by CTA 0 at the end)
+    int n_barriers;                // grid barriers per run
+    long long mbox_stride;         // elements between the two parities of every mailbox (run r uses parity r & 1)
     int S, slot_stride;            // ring stages, bytes per stage slot
     int off_xs, off_gtab, off_part, off_ring;
     unsigned long long *dbg;       // [n_ops][grid][CH_DBG_WORDS] %globaltimer stamps, or null
@@ -68,8 +73,29 @@ __device__ __forceinline__ void ch_mbar_arrive(uint32_t bar) {
 // Activation staging of one linear by the 512 consumer threads: identical to gemv_imma2_kernel's (per-(group, token)
 // power-of-two scale, two signed-byte planes in B-fragment order, integer group sums, Inf / NaN poison the group), but x
 // is read with ld.global.cg: another CTA of THIS launch wrote it a barrier ago.
+// a value can never be the sentinel: 0xFFFF (a NaN) is stored as the canonical NaN 0x7FFF
+__device__ __forceinline__ void ch_mbox_store(unsigned short *p, __nv_bfloat16 v) {
+    unsigned short b = __bfloat16_as_ushort(v);
+    if (b == 0xFFFFu) b = 0x7FFFu;
+    asm volatile("st.relaxed.gpu.global.u16 [%0], %1;" ::"l"(p), "h"(b) : "memory");
+}
+__device__ __forceinline__ uint4 ch_ld_relaxed(const uint4 *p) {
+    uint4 v;
+    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+// any 16-bit half of the four words equal to 0xFFFF (the mailbox sentinel)?
+__device__ __forceinline__ bool ch_has_sentinel(const uint4 &v) {
+    uint32_t hit = 0;
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { const uint32_t t = ~w[q]; hit |= (t - 0x00010001u) & ~t & 0x80008000u; }
+    return hit != 0;
+}
+
+// poll: x is a mailbox (see ChainOp): every 16-byte piece is re-read until none of its eight values is the sentinel.
 template <int MR, int MPU>
-__device__ __forceinline__ void ch_stage_x(const __nv_bfloat16 *x, uint8_t *xs, int2 *gtab, int M, int K, int tid, int lane) {
+__device__ __forceinline__ void ch_stage_x(const __nv_bfloat16 *x, uint8_t *xs, int2 *gtab, int M, int K, int tid, int lane, bool poll) {
     constexpr int COLS = 2 * MR;
     constexpr int GL = (GV_UNIT_K / MPU) / 8;
     const int ppr = K >> 3, total = M * ppr;
@@ -80,7 +106,19 @@ __device__ __forceinline__ void ch_stage_x(const __nv_bfloat16 *x, uint8_t *xs, 
 #pragma unroll
         for (int r = 0; r < BATCH; ++r) {
             const int i = base + r * CH_CONS_THREADS + tid;
-            v[r] = i < total ? __ldcg(x16 + i) : make_uint4(0, 0, 0, 0);
+            v[r] = i < total ? (poll ? ch_ld_relaxed(x16 + i) : __ldcg(x16 + i)) : make_uint4(0, 0, 0, 0);
+        }
+        if (poll) {
+#pragma unroll
+            for (int r = 0; r < BATCH; ++r) {
+                const int i = base + r * CH_CONS_THREADS + tid;
+                uint32_t spins = 0;
+                while (i < total && ch_has_sentinel(v[r])) {
+                    v[r] = ch_ld_relaxed(x16 + i);
+                    if (++spins > GV_SPIN_LIMIT) __trap();
+                }
+            }
+            __syncwarp();
         }
 #pragma unroll
         for (int r = 0; r < BATCH; ++r) {
@@ -139,11 +177,10 @@ __device__ __forceinline__ void ch_stage_x(const __nv_bfloat16 *x, uint8_t *xs, 
     }
 }
 
-// The row blocks of one linear that belong to this consumer group: stage after stage from the ring.
-// pos = {slot, parity} of the group's next stage; advanced here over the group's own stages and over the other
-// group's (`skip` stages after every row block).
+// The row blocks of one linear, stage after stage from the ring; every warp takes two units (wi, wi + 16) of every
+// stage, so a stage passes through the CTA in the latency of 8 IMMAs.  {slot, parity} = the CTA's next stage.
 template <int MR, int MPU, bool HOIST>
-__device__ __forceinline__ void ch_row_blocks(const ChainParams &p, const ChainOp &op, int n_slots, int gi, int wi, int lane,
+__device__ __forceinline__ void ch_row_blocks(const ChainParams &p, const ChainOp &op, int n_slots, int wi, int lane,
                                               uint32_t ring, uint32_t bar_full, uint32_t bar_empty, uint32_t xs_u32, uint32_t gtab_u32,
                                               float2 *part, int &slot, uint32_t &parity) {
     constexpr int COLS = 2 * MR;
@@ -157,26 +194,21 @@ __device__ __forceinline__ void ch_row_blocks(const ChainParams &p, const ChainO
     const bool b_lane = COLS >= 8 || g < COLS;   // only the lanes of the data columns need real B values
 
     uint32_t bq[HOIST ? CH_UPW : 1][4][2];
-    int gX[HOIST ? CH_UPW : 1];
-    float gE[HOIST ? CH_UPW : 1];
     if constexpr (HOIST) {   // K = 4096: the warp meets the same four k-units in every row block
 #pragma unroll
         for (int j = 0; j < CH_UPW; ++j) {
-            const uint32_t xk = xs_l + (uint32_t)(wi + 8 * j) * XU;
+            const uint32_t xk = xs_l + (uint32_t)(wi + CH_CONS_WARPS * j) * XU;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 bq[j][i][0] = 0; bq[j][i][1] = 0;
                 if (b_lane) asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(bq[j][i][0]), "=r"(bq[j][i][1]) : "r"(xk + (uint32_t)(i * 4 * COLS * 8)));
             }
-            int e2b;
-            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(gX[j]), "=r"(e2b) : "r"(gt_l + (uint32_t)(wi + 8 * j) * GU));
-            gE[j] = __int_as_float(e2b);
         }
     }
     const uint32_t offW = (uint32_t)(wi * GV_UNIT_BYTES + lane * 16);
     const uint32_t offM = STAGE_W + (uint32_t)(wi * MPU * META_BYTES);
-    const int spr = op.spr, skip = spr * (CH_GROUPS - 1);
-    for (int s = gi; s < n_slots; s += CH_GROUPS) {
+    const int spr = op.spr;
+    for (int s = 0; s < n_slots; ++s) {
         float y0 = 0.f, y1 = 0.f;                  // rows g / g+8 of this row block, token slot t
         for (int m = 0; m < spr; ++m) {
             const uint32_t sb = ring + (uint32_t)slot * (uint32_t)p.slot_stride;
@@ -184,7 +216,7 @@ __device__ __forceinline__ void ch_row_blocks(const ChainParams &p, const ChainO
             uint32_t w[CH_UPW][8], s2[CH_UPW][MPU], zb[CH_UPW][MPU];
 #pragma unroll
             for (int j = 0; j < CH_UPW; ++j) {
-                const uint32_t sw = sb + offW + (uint32_t)(8 * j * GV_UNIT_BYTES), sm = sb + offM + (uint32_t)(8 * j * MPU * META_BYTES);
+                const uint32_t sw = sb + offW + (uint32_t)(CH_CONS_WARPS * j * GV_UNIT_BYTES), sm = sb + offM + (uint32_t)(CH_CONS_WARPS * j * MPU * META_BYTES);
                 asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]) : "r"(sw));
                 asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4+512];" : "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7]) : "r"(sw));
 #pragma unroll
@@ -214,7 +246,7 @@ __device__ __forceinline__ void ch_row_blocks(const ChainParams &p, const ChainO
                         b0 = 0; b1 = 0;
                         if (b_lane)
                             asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(b0), "=r"(b1)
-                                         : "r"(xs_l + (uint32_t)(32 * m + wi + 8 * j) * XU + (uint32_t)(i * 4 * COLS * 8)));
+                                         : "r"(xs_l + (uint32_t)(32 * m + wi + CH_CONS_WARPS * j) * XU + (uint32_t)(i * 4 * COLS * 8)));
                     }
                     // rows g: the low nibbles; rows g+8: the RAW bytes 16 q[g+8] + q[g] (rows g are subtracted afterwards)
                     ch_imma(acc[j][i / IPG], wa & 0x0F0F0F0Fu, wa, wb & 0x0F0F0F0Fu, wb, b0, b1);
@@ -224,16 +256,10 @@ __device__ __forceinline__ void ch_row_blocks(const ChainParams &p, const ChainO
             for (int j = 0; j < CH_UPW; ++j) {
 #pragma unroll
                 for (int h = 0; h < MPU; ++h) {
-                    int X;
-                    float e2;
-                    if constexpr (HOIST) {
-                        X = gX[j]; e2 = gE[j];
-                    } else {
-                        int e2b;
-                        asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(X), "=r"(e2b)
-                                     : "r"(gt_l + (uint32_t)(32 * m + wi + 8 * j) * GU + (uint32_t)(h * MR * 8)));
-                        e2 = __int_as_float(e2b);
-                    }
+                    int X, e2b;      // HOIST: m == 0 always
+                    asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(X), "=r"(e2b)
+                                 : "r"(gt_l + (uint32_t)(32 * m + wi + CH_CONS_WARPS * j) * GU + (uint32_t)(h * MR * 8)));
+                    const float e2 = __int_as_float(e2b);
                     const int tg = acc[j][h][0] * 128 + acc[j][h][1];
                     const int tr = acc[j][h][2] * 128 + acc[j][h][3];
                     const int ug = tg - (int)(zb[j][h] & 0x0Fu) * X;
@@ -246,14 +272,12 @@ __device__ __forceinline__ void ch_row_blocks(const ChainParams &p, const ChainO
             }
             if (++slot == p.S) { slot = 0; parity ^= 1u; }
         }
-        if (t < MR) part[(((size_t)s * CH_GWARPS + wi) * 8 + g) * MR + t] = make_float2(y0, y1);
-        slot += skip;                               // the other group's stages of the next row block
-        while (slot >= p.S) { slot -= p.S; parity ^= 1u; }
+        if (t < MR) part[(((size_t)s * CH_CONS_WARPS + wi) * 8 + g) * MR + t] = make_float2(y0, y1);
     }
 }
 
 template <int MR, int MPU>
-__global__ void __maxnreg__(112) chain_kernel(const ChainParams p) {
+__global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams p) {
     extern __shared__ __align__(128) uint8_t ch_smem[];
     uint8_t *xs = ch_smem + p.off_xs;
     int2 *gtab = reinterpret_cast<int2 *>(ch_smem + p.off_gtab);
@@ -265,7 +289,7 @@ __global__ void __maxnreg__(112) chain_kernel(const ChainParams p) {
     constexpr uint32_t STAGE_W = 32 * GV_UNIT_BYTES, STAGE_M = 32 * MPU * META_BYTES;
 
     if (tid == 0) {
-        for (int s = 0; s < p.S; ++s) { gv_mbar_init(bar_full + 8 * s, 1); gv_mbar_init(bar_empty + 8 * s, CH_GWARPS); }
+        for (int s = 0; s < p.S; ++s) { gv_mbar_init(bar_full + 8 * s, 1); gv_mbar_init(bar_empty + 8 * s, CH_CONS_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -300,9 +324,7 @@ __global__ void __maxnreg__(112) chain_kernel(const ChainParams p) {
     }
 
     // ---- consumers ----
-    const int gi = warp / CH_GWARPS, wi = warp % CH_GWARPS;
-    const unsigned int run = p.n_ops > 1 ? __ldcg(p.runs) : 0u;
-    const unsigned long long bar_base = (unsigned long long)run * (unsigned long long)(p.n_ops - 1);
+    const int wi = warp;
     auto stamp = [&](int o, int i) {
         if (p.dbg && tid == 0) {
             unsigned long long tt;
@@ -310,56 +332,22 @@ __global__ void __maxnreg__(112) chain_kernel(const ChainParams p) {
             p.dbg[((size_t)o * grid + cta) * CH_DBG_WORDS + i] = tt;
         }
     };
-    asm volatile("griddepcontrol.wait;" ::: "memory");   // the first x may come from the previous kernel
+    asm volatile("griddepcontrol.wait;" ::: "memory");   // the first x may come from the previous kernel; and the
+    // previous run of this chain (which may have released this launch early) has stored `runs` only now
+    const unsigned int run = p.n_ops > 1 ? __ldcg(p.runs) : 0u;
+    unsigned long long bar_count = (unsigned long long)run * (unsigned long long)p.n_barriers;   // barriers passed so far
+    const long long mb_cur = (run & 1u) ? p.mbox_stride : 0, mb_nxt = (run & 1u) ? 0 : p.mbox_stride;
     int slot = 0;                                         // ring position of the CTA's first stage of the current linear
     uint32_t parity = 0u;
     for (int o = 0; o < p.n_ops; ++o) {
         const ChainOp op = p.ops[o];
         const int R0 = __ldg(op.rb + cta), n_slots = __ldg(op.rb + cta + 1) - R0;
-        stamp(o, 0);
-        if (o + 1 == p.n_ops) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-        ch_stage_x<MR, MPU>(op.x, xs, gtab, op.M, op.K, tid, lane);
-        ch_bar_consumers();
-        stamp(o, 1);
-        // this group's first stage: gi row blocks further on
-        int gslot = slot + gi * op.spr;
-        uint32_t gpar = parity;
-        while (gslot >= p.S) { gslot -= p.S; gpar ^= 1u; }
-        if (MPU == 1 && op.hoist)
-            ch_row_blocks<MR, MPU, MPU == 1>(p, op, n_slots, gi, wi, lane, ring, bar_full, bar_empty, gv_smem_u32(xs), gv_smem_u32(gtab), part, gslot, gpar);
-        else
-            ch_row_blocks<MR, MPU, false>(p, op, n_slots, gi, wi, lane, ring, bar_full, bar_empty, gv_smem_u32(xs), gv_smem_u32(gtab), part, gslot, gpar);
-        slot += n_slots * op.spr;
-        while (slot >= p.S) { slot -= p.S; parity ^= 1u; }
-        ch_bar_consumers();
-        stamp(o, 2);
-        // combine the 8 warps of every row block (fixed tree: deterministic) and write y
-        for (int i = tid; i < n_slots * 32 * MR; i += CH_CONS_THREADS) {      // multiples of 32: whole warps
-            const int q = i & 3, e = (i >> 2) & (8 * MR - 1), sl = i / (32 * MR);
-            const float2 *src = part + ((size_t)sl * CH_GWARPS + 2 * q) * 8 * MR + e;
-            float2 v = src[0];
-            const float2 o2 = src[8 * MR];
-            v.x += o2.x; v.y += o2.y;
-            v.x += __shfl_xor_sync(0xffffffffu, v.x, 1); v.y += __shfl_xor_sync(0xffffffffu, v.y, 1);
-            v.x += __shfl_xor_sync(0xffffffffu, v.x, 2); v.y += __shfl_xor_sync(0xffffffffu, v.y, 2);
-            const int tok = e % MR, n0 = (R0 + sl) * 16 + e / MR;
-            if (q == 0 && tok < op.M) {
-                const float b0 = op.bias ? __bfloat162float(op.bias[n0]) : 0.f;
-                const float b1 = op.bias ? __bfloat162float(op.bias[n0 + 8]) : 0.f;
-                if (op.swiglu) {   // rows g / g+8 are (gate, up) of output column 8 R + g
-                    op.y[(size_t)tok * (op.N >> 1) + (n0 >> 4) * 8 + (n0 & 7)] = swiglu_bf16(v.x + b0, v.y + b1);
-                } else {
-                    op.y[(size_t)tok * op.N + n0] = __float2bfloat16_rn(v.x + b0);
-                    op.y[(size_t)tok * op.N + n0 + 8] = __float2bfloat16_rn(v.y + b1);
-                }
-            }
-        }
-        if (o + 1 < p.n_ops) {
-            // grid barrier: every CTA's y of linear o is visible before anybody stages it as the x of linear o + 1
-            __threadfence();
-            ch_bar_consumers();
+        if (op.barrier_before) {
+            // grid barrier: everything the linears before this one wrote is visible, everything they read has been read
+            // (the CTA barrier below the combine ordered every thread's stores before thread 0's gpu-scope release)
             if (tid == 0) {
-                const unsigned long long target = (bar_base + (unsigned long long)o + 1ull) * (unsigned long long)grid;
+                ++bar_count;
+                const unsigned long long target = bar_count * (unsigned long long)grid;
                 asm volatile("red.release.gpu.global.add.u64 [%0], 1;" ::"l"(p.counter) : "memory");
                 unsigned long long seen;
                 uint32_t spins = 0;
@@ -370,6 +358,55 @@ __global__ void __maxnreg__(112) chain_kernel(const ChainParams p) {
             }
             ch_bar_consumers();
         }
+        stamp(o, 0);
+        if (o + 1 == p.n_ops) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+        const bool poll = op.mbox_in != nullptr;
+        ch_stage_x<MR, MPU>(poll ? reinterpret_cast<const __nv_bfloat16 *>(op.mbox_in + mb_cur) : op.x, xs, gtab, op.M, op.K, tid, lane, poll);
+        if (poll) {
+            // put the sentinel back into the OTHER parity of what was just read: its last readers finished a run ago, its
+            // next writers run a run from now (they cannot start before every CTA has passed this point)
+            uint4 *dst = reinterpret_cast<uint4 *>(const_cast<unsigned short *>(op.mbox_in) + mb_nxt);
+            const int pieces = (op.M * op.K) >> 3;
+            for (int i = cta + tid * grid; i < pieces; i += grid * CH_CONS_THREADS)
+                dst[i] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+        }
+        ch_bar_consumers();
+        stamp(o, 1);
+        if (MPU == 1 && op.hoist)
+            ch_row_blocks<MR, MPU, MPU == 1>(p, op, n_slots, wi, lane, ring, bar_full, bar_empty, gv_smem_u32(xs), gv_smem_u32(gtab), part, slot, parity);
+        else
+            ch_row_blocks<MR, MPU, false>(p, op, n_slots, wi, lane, ring, bar_full, bar_empty, gv_smem_u32(xs), gv_smem_u32(gtab), part, slot, parity);
+        ch_bar_consumers();
+        stamp(o, 2);
+        // combine the 16 warps of every row block (fixed tree: deterministic) and write y
+        for (int i = tid; i < n_slots * 32 * MR; i += CH_CONS_THREADS) {      // multiples of 32: whole warps
+            const int q = i & 3, e = (i >> 2) & (8 * MR - 1), sl = i / (32 * MR);
+            const float2 *src = part + ((size_t)sl * CH_CONS_WARPS + 4 * q) * 8 * MR + e;
+            float2 v = src[0];
+#pragma unroll
+            for (int k = 1; k < 4; ++k) { const float2 o2 = src[k * 8 * MR]; v.x += o2.x; v.y += o2.y; }
+            v.x += __shfl_xor_sync(0xffffffffu, v.x, 1); v.y += __shfl_xor_sync(0xffffffffu, v.y, 1);
+            v.x += __shfl_xor_sync(0xffffffffu, v.x, 2); v.y += __shfl_xor_sync(0xffffffffu, v.y, 2);
+            const int tok = e % MR, n0 = (R0 + sl) * 16 + e / MR;
+            if (q == 0 && tok < op.M) {
+                const float b0 = op.bias ? __bfloat162float(op.bias[n0]) : 0.f;
+                const float b1 = op.bias ? __bfloat162float(op.bias[n0 + 8]) : 0.f;
+                unsigned short *mb = op.mbox_out ? op.mbox_out + mb_cur : nullptr;
+                if (op.swiglu) {   // rows g / g+8 are (gate, up) of output column 8 R + g
+                    const size_t at = (size_t)tok * (op.N >> 1) + (n0 >> 4) * 8 + (n0 & 7);
+                    const __nv_bfloat16 r = swiglu_bf16(v.x + b0, v.y + b1);
+                    op.y[at] = r;
+                    if (mb) ch_mbox_store(mb + at, r);
+                } else {
+                    const size_t at = (size_t)tok * op.N + n0;
+                    const __nv_bfloat16 r0 = __float2bfloat16_rn(v.x + b0), r1 = __float2bfloat16_rn(v.y + b1);
+                    op.y[at] = r0;
+                    op.y[at + 8] = r1;
+                    if (mb) { ch_mbox_store(mb + at, r0); ch_mbox_store(mb + at + 8, r1); }
+                }
+            }
+        }
+        ch_bar_consumers();   // part / xs are free again; this CTA's y stores precede whatever thread 0 releases next
         stamp(o, 3);
     }
     if (p.n_ops > 1 && cta == 0 && tid == 0) *p.runs = run + 1u;   // everybody read `runs` before the first barrier
@@ -388,6 +425,8 @@ struct Chain {
     int *d_rb = nullptr;
     unsigned long long *d_counter = nullptr;
     unsigned int *d_runs = nullptr;
+    unsigned short *d_mbox = nullptr;
+    int n_mailboxes = 0, n_barriers = 0;
     unsigned long long *d_dbg = nullptr;
     ChainParams prm{};
     int MR = 1, mpu = 1, smem = 0, grid = 0;
@@ -433,7 +472,7 @@ static int chain_launch(const Chain &c, cudaStream_t stream) {
 
 static void chain_free(Chain *c) {
     if (!c) return;
-    cudaFree(c->d_ops); cudaFree(c->d_rb); cudaFree(c->d_counter); cudaFree(c->d_runs); cudaFree(c->d_dbg);
+    cudaFree(c->d_ops); cudaFree(c->d_rb); cudaFree(c->d_counter); cudaFree(c->d_runs); cudaFree(c->d_mbox); cudaFree(c->d_dbg);
     delete c;
 }
 
@@ -465,7 +504,7 @@ static int chain_plan(Chain *c) {
     const int off_xs = (int)off; off += maxK * 2 * c->MR;
     const int off_gtab = (int)off; off += (maxK / gs) * c->MR * 8;
     off = (off + 15) & ~(int64_t)15;
-    const int off_part = (int)off; off += max_slots * CH_GWARPS * 8 * c->MR * 8;
+    const int off_part = (int)off; off += max_slots * CH_CONS_WARPS * 8 * c->MR * 8;
     off = (off + 127) & ~(int64_t)127;
     const int64_t stride = 32 * (GV_UNIT_BYTES + c->mpu * META_BYTES);
     int64_t S = (CH_SMEM_MAX - off) / stride;
@@ -474,6 +513,49 @@ static int chain_plan(Chain *c) {
     const int off_ring = (int)off; off += S * stride;
     c->smem = (int)off;
     c->grid = grid;
+
+    // ---- dependencies between the linears (byte ranges of the caller's buffers) ----
+    // RAW: x[i] inside the y of its latest writer j -> mailbox (data-as-flag hand-over, no barrier).  Everything else that
+    // needs an order -- a partial overlap, a write over something an earlier linear reads from the caller's memory, two
+    // linears writing overlapping ranges with different row partitions -- gets a grid barrier in front of linear i.
+    const int n = c->n;
+    const int64_t M = c->M;
+    auto width = [&](int i) { Linear *L = c->lin[i]; return L->epilogue == W4A16_EPILOGUE_SWIGLU ? L->d.N / 2 : L->d.N; };
+    auto lo_x = [&](int i) { return reinterpret_cast<uintptr_t>(c->x[i]); };
+    auto hi_x = [&](int i) { return lo_x(i) + (uintptr_t)(M * c->lin[i]->d.K * 2); };
+    auto lo_y = [&](int i) { return reinterpret_cast<uintptr_t>(c->y[i]); };
+    auto hi_y = [&](int i) { return lo_y(i) + (uintptr_t)(M * width(i) * 2); };
+    auto overlap = [](uintptr_t a0, uintptr_t a1, uintptr_t b0, uintptr_t b1) { return a0 < b1 && b0 < a1; };
+    std::vector<int> dep(n, -1), barrier(n, 0);
+    const bool no_mbox = gv_env_int("W4A16_CHAIN_NO_MAILBOX", 0) != 0;
+    for (int i = 1; i < n; ++i) {
+        for (int j = i - 1; j >= 0; --j) {
+            if (!overlap(lo_x(i), hi_x(i), lo_y(j), hi_y(j))) continue;
+            const bool inside = lo_x(i) >= lo_y(j) && hi_x(i) <= hi_y(j) && ((lo_x(i) - lo_y(j)) & 15) == 0 &&
+                                (M == 1 || (lo_x(i) == lo_y(j) && c->lin[i]->d.K == width(j)));
+            if (inside && !no_mbox) dep[i] = j; else barrier[i] = 1;
+            break;                                   // the latest writer decides
+        }
+        for (int j = 0; j < i && !barrier[i]; ++j) {
+            if (overlap(lo_y(i), hi_y(i), lo_y(j), hi_y(j)) &&
+                !(lo_y(i) == lo_y(j) && c->lin[i]->d.N == c->lin[j]->d.N && width(i) == width(j)))
+                barrier[i] = 1;                      // same rows from the same CTA in program order would be fine
+            if (overlap(lo_y(i), hi_y(i), lo_x(j), hi_x(j)) && dep[j] < 0) barrier[i] = 1;   // j reads the caller's memory
+        }
+        if (barrier[i]) dep[i] = -1;                 // behind a barrier the caller's buffer itself is read
+    }
+    std::vector<int64_t> mbox_off(n, -1);
+    int64_t mbox_total = 0;
+    for (int i = 0; i < n; ++i)
+        if (dep[i] >= 0 && mbox_off[dep[i]] < 0) {
+            mbox_off[dep[i]] = mbox_total;
+            mbox_total += (M * width(dep[i]) + 7) & ~(int64_t)7;
+            ++c->n_mailboxes;
+        }
+    if (mbox_total) {
+        W4_CUDA_OK(cudaMalloc(&c->d_mbox, (size_t)mbox_total * 2 * sizeof(unsigned short)));
+        W4_CUDA_OK(cudaMemset(c->d_mbox, 0xFF, (size_t)mbox_total * 2 * sizeof(unsigned short)));
+    }
 
     std::vector<int> rb((size_t)c->n * (grid + 1));
     std::vector<ChainOp> ops(c->n);
@@ -493,7 +575,10 @@ static int chain_plan(Chain *c) {
         o.spr = o.UPR / 32;
         o.swiglu = L->epilogue == W4A16_EPILOGUE_SWIGLU;
         o.hoist = o.spr == 1 && c->mpu == 1;
-        o.pad = 0;
+        o.barrier_before = barrier[i];
+        c->n_barriers += barrier[i];
+        o.mbox_out = mbox_off[i] >= 0 ? c->d_mbox + mbox_off[i] : nullptr;
+        o.mbox_in = dep[i] >= 0 ? c->d_mbox + mbox_off[dep[i]] + (lo_x(i) - lo_y(dep[i])) / 2 : nullptr;
     }
     W4_CUDA_OK(cudaMemcpy(c->d_rb, rb.data(), rb.size() * sizeof(int), cudaMemcpyHostToDevice));
     W4_CUDA_OK(cudaMalloc(&c->d_ops, ops.size() * sizeof(ChainOp)));
@@ -510,6 +595,7 @@ static int chain_plan(Chain *c) {
     ChainParams &p = c->prm;
     p.ops = c->d_ops; p.n_ops = c->n;
     p.counter = c->d_counter; p.runs = c->d_runs;
+    p.n_barriers = c->n_barriers; p.mbox_stride = mbox_total;
     p.S = (int)S; p.slot_stride = (int)stride;
     p.off_xs = off_xs; p.off_gtab = off_gtab; p.off_part = off_part; p.off_ring = off_ring;
     p.dbg = c->d_dbg;
@@ -577,8 +663,11 @@ int w4a16_chain_run(w4a16_chain_t chain, w4a16_stream_t stream) {
 const char *w4a16_chain_kernel(w4a16_chain_t chain) {
     Chain *c = reinterpret_cast<Chain *>(chain);
     if (!c) return "";
-    if (c->persistent) return "chain_imma";
     static thread_local std::string s;
+    if (c->persistent) {
+        s = "chain_imma (" + std::to_string(c->n_mailboxes) + " mailboxes, " + std::to_string(c->n_barriers) + " barriers)";
+        return s.c_str();
+    }
     s = "per_linear (" + c->why_not + ")";
     return s.c_str();
 }
