@@ -242,8 +242,8 @@ int w4a16_chain_destroy(w4a16_chain_t chain);
  * barrier in front of the later one.  Linears that share nothing are not ordered at all. */
 const char *w4a16_chain_kernel(w4a16_chain_t chain);
 /* Profiling hook (W4A16_GV_DEBUG=1 at chain_create): %globaltimer stamps
- * [n][CTAs][4] = {linear started, activations staged, weights streamed, y written + barrier passed}
- * of the last run; synchronises the device. */
+ * [n][CTAs][8] = {linear started, activations staged, weights streamed, y written, arrival hint
+ * seen, first activations valid, re-reads of those, -} of the last run; synchronises the device. */
 int w4a16_chain_debug_stamps(w4a16_chain_t chain, uint64_t *out, int64_t words);
 
 /* Communicator bootstrap for callers that do not already hold an ncclComm_t

@@ -47,12 +47,15 @@ def main():
     a = chain.debug_stamps().astype(np.int64)       # [n, ctas, 4]
     n = len(steps)
     t0 = a[n - 4, :, 0].min()
-    labels = ["started", "staged", "streamed", "written"]
+    labels = [(0, "started"), (4, "hint-seen"), (5, "x-valid"), (1, "staged"), (2, "streamed"), (3, "written")]
     for o in range(n - 4, n):
         print(f"-- {names[o]}")
-        for i, nm in enumerate(labels):
+        for i, nm in labels:
+            if a[o, :, i].max() == 0:
+                continue
             v = (a[o, :, i] - t0) / 1e3
             print(f"   {nm:9s} min {v.min():8.2f}  med {np.median(v):8.2f}  max {v.max():8.2f} us")
+        print(f"   re-reads of the first pieces: med {np.median(a[o, :, 6]):.0f} max {a[o, :, 6].max()}")
     total = (a[n - 1, :, 3].max() - a[0, :, 0].min()) / 1e3
     print(f"whole chain ({n} linears): {total:.2f} us = {total / args.layers:.2f} us per layer")
 

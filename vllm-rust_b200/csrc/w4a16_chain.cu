@@ -30,7 +30,7 @@ constexpr int CH_THREADS = CH_CONS_THREADS + 32;      // + the producer warp
 constexpr int CH_MAX_STAGES = 8;
 constexpr int CH_SMEM_MAX = 227 * 1024;
 constexpr int CH_MAX_OPS = 4096;
-constexpr int CH_DBG_WORDS = 4;                       // stamps per (CTA, op): op start, staged, streamed, y written
+constexpr int CH_DBG_WORDS = 8;                       // stamps per (CTA, op): op start, staged, streamed, y written, hint seen, x valid, -, -
 
 struct ChainOp {
     const uint8_t *qw, *meta;
@@ -45,6 +45,11 @@ struct ChainOp {
     // words hold the sentinel 0xFFFF until written; the reader polls that copy instead of waiting at a barrier.
     unsigned short *mbox_out;        // parity-0 copy of this linear's y ([M][out width]) or null
     const unsigned short *mbox_in;   // parity-0 address of this linear's x inside its producer's mailbox, or null (read op.x)
+    // Arrival hint of a mailbox: every CTA adds 1 (relaxed, no fence) once its part of y is on its way; the reader's
+    // thread 0 polls this ONE word instead of 148 x 512 threads hammering the mailbox lines the writers still have to
+    // reach, and only then are the pieces read -- and still validated against the sentinel, because the hint orders nothing.
+    unsigned long long *arrive_out;        // this linear's own counter (null without a mailbox)
+    const unsigned long long *arrive_in;   // the producer's counter (null without mbox_in)
 };
 
 struct ChainParams {
@@ -55,6 +60,8 @@ struct ChainParams {
     int n_barriers;                // grid barriers per run
     long long mbox_stride;         // elements between the two parities of every mailbox (run r uses parity r & 1)
     int S, slot_stride;            // ring stages, bytes per stage slot
+    int exp_nometa;                // timing experiment only (wrong results): the producer skips the meta copies
+    int max_inflight;              // stages the producer keeps in flight (<= S)
     int off_xs, off_gtab, off_part, off_ring;
     unsigned long long *dbg;       // [n_ops][grid][CH_DBG_WORDS] %globaltimer stamps, or null
 };
@@ -73,6 +80,17 @@ __device__ __forceinline__ void ch_mbar_arrive(uint32_t bar) {
 // Activation staging of one linear by the 512 consumer threads: identical to gemv_imma2_kernel's (per-(group, token)
 // power-of-two scale, two signed-byte planes in B-fragment order, integer group sums, Inf / NaN poison the group), but x
 // is read with ld.global.cg: another CTA of THIS launch wrote it a barrier ago.
+// reductions over an aligned group of lanes (one instruction instead of a shuffle tree)
+__device__ __forceinline__ uint32_t ch_redux_max(uint32_t v, uint32_t mask) {
+    uint32_t r;
+    asm volatile("redux.sync.max.u32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(mask));
+    return r;
+}
+__device__ __forceinline__ int ch_redux_add(int v, uint32_t mask) {
+    int r;
+    asm volatile("redux.sync.add.s32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(mask));
+    return r;
+}
 // a value can never be the sentinel: 0xFFFF (a NaN) is stored as the canonical NaN 0x7FFF
 __device__ __forceinline__ void ch_mbox_store(unsigned short *p, __nv_bfloat16 v) {
     unsigned short b = __bfloat16_as_ushort(v);
@@ -95,12 +113,14 @@ __device__ __forceinline__ bool ch_has_sentinel(const uint4 &v) {
 
 // poll: x is a mailbox (see ChainOp): every 16-byte piece is re-read until none of its eight values is the sentinel.
 template <int MR, int MPU>
-__device__ __forceinline__ void ch_stage_x(const __nv_bfloat16 *x, uint8_t *xs, int2 *gtab, int M, int K, int tid, int lane, bool poll) {
+__device__ __forceinline__ void ch_stage_x(const __nv_bfloat16 *x, uint8_t *xs, int2 *gtab, int M, int K, int tid, int lane, bool poll,
+                                           unsigned long long *dbg_valid) {
     constexpr int COLS = 2 * MR;
     constexpr int GL = (GV_UNIT_K / MPU) / 8;
     const int ppr = K >> 3, total = M * ppr;
     const uint4 *x16 = reinterpret_cast<const uint4 *>(x);
     constexpr int BATCH = 4;
+    const uint32_t gmask = (GL >= 32 ? 0xFFFFFFFFu : ((1u << GL) - 1u)) << (lane & ~(GL - 1));
     for (int base = 0; base < total; base += BATCH * CH_CONS_THREADS) {
         uint4 v[BATCH];
 #pragma unroll
@@ -109,14 +129,26 @@ __device__ __forceinline__ void ch_stage_x(const __nv_bfloat16 *x, uint8_t *xs, 
             v[r] = i < total ? (poll ? ch_ld_relaxed(x16 + i) : __ldcg(x16 + i)) : make_uint4(0, 0, 0, 0);
         }
         if (poll) {
+            // re-read every piece that still holds a sentinel, all of them in flight together
+            uint32_t spins = 0;
+            for (;;) {
+                bool bad[BATCH], any = false;
 #pragma unroll
-            for (int r = 0; r < BATCH; ++r) {
-                const int i = base + r * CH_CONS_THREADS + tid;
-                uint32_t spins = 0;
-                while (i < total && ch_has_sentinel(v[r])) {
-                    v[r] = ch_ld_relaxed(x16 + i);
-                    if (++spins > GV_SPIN_LIMIT) __trap();
+                for (int r = 0; r < BATCH; ++r) {
+                    bad[r] = base + r * CH_CONS_THREADS + tid < total && ch_has_sentinel(v[r]);
+                    any |= bad[r];
                 }
+                if (!any) break;
+#pragma unroll
+                for (int r = 0; r < BATCH; ++r)
+                    if (bad[r]) v[r] = ch_ld_relaxed(x16 + base + r * CH_CONS_THREADS + tid);
+                if (++spins > GV_SPIN_LIMIT) __trap();
+            }
+            if (dbg_valid && tid == 0 && base == 0) {
+                unsigned long long tt;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt));
+                dbg_valid[0] = tt;
+                dbg_valid[1] = spins;
             }
             __syncwarp();
         }
@@ -128,8 +160,7 @@ __device__ __forceinline__ void ch_stage_x(const __nv_bfloat16 *x, uint8_t *xs, 
             uint32_t mx = 0;
 #pragma unroll
             for (int q = 0; q < 4; ++q) mx = max(mx, max(w4[q] & 0x7FFFu, (w4[q] >> 16) & 0x7FFFu));
-#pragma unroll
-            for (int o = GL / 2; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            mx = ch_redux_max(mx, gmask);            // over the GL lanes that hold the group
             int E = (int)(mx >> 7);
             E = min(max(E, 14), 254);
             const float scale = __int_as_float((267 - E) << 23);     // max|x| lands in [2^13, 2^14)
@@ -142,8 +173,7 @@ __device__ __forceinline__ void ch_stage_x(const __nv_bfloat16 *x, uint8_t *xs, 
                 pk[q] = __byte_perm(__float_as_uint(lo), __float_as_uint(hi), 0x5410);
                 sum = __dp2a_lo((int)pk[q], 0x0101, sum);
             }
-#pragma unroll
-            for (int o = GL / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+            sum = ch_redux_add(sum, gmask);
             if (i < total) {
                 const int m = MR == 1 ? 0 : (i >= ppr) + (MR > 2 ? (i >= 2 * ppr) + (i >= 3 * ppr) : 0);
                 const int c = i - m * ppr;
@@ -299,8 +329,8 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
         // ---- producer: the CTA's share of every linear's W4T stream, in chain order, as fast as slots come free.
         //      Weights are immutable, so this neither waits for the previous kernel nor for the grid barriers. ----
         if (lane == 0) {
-            int slot = 0;
-            uint32_t parity = 1u;                    // first round: slots are free (wait on the phase before the first)
+            int slot = 0, lslot = 0, issued = 0;
+            uint32_t parity = 1u, lpar = 0u;         // first round: slots are free (wait on the phase before the first)
             for (int o = 0; o < p.n_ops; ++o) {
                 const ChainOp *op = p.ops + o;
                 const int *rb = op->rb;
@@ -309,12 +339,21 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
                 const size_t unit0 = (size_t)R0 * op->UPR;
                 const uint8_t *w = op->qw + unit0 * GV_UNIT_BYTES;
                 const uint8_t *m = op->meta + unit0 * (MPU * META_BYTES);
-                for (int s = 0; s < nst; ++s) {
+                for (int s = 0; s < nst; ++s, ++issued) {
+                    if (issued >= p.max_inflight) {          // stage issued - max_inflight must have landed
+                        gv_mbar_wait(bar_full + 8 * lslot, lpar);
+                        if (++lslot == p.S) { lslot = 0; lpar ^= 1u; }
+                    }
                     gv_mbar_wait(bar_empty + 8 * slot, parity);
                     const uint32_t bar = bar_full + 8 * slot, dst = ring + (uint32_t)slot * (uint32_t)p.slot_stride;
-                    gv_mbar_expect_tx(bar, STAGE_W + STAGE_M);
-                    gv_bulk_g2s(dst, w, STAGE_W, bar);
-                    gv_bulk_g2s(dst + STAGE_W, m, STAGE_M, bar);
+                    if (p.exp_nometa) {
+                        gv_mbar_expect_tx(bar, STAGE_W);
+                        gv_bulk_g2s(dst, w, STAGE_W, bar);
+                    } else {
+                        gv_mbar_expect_tx(bar, STAGE_W + STAGE_M);
+                        gv_bulk_g2s(dst, w, STAGE_W, bar);
+                        gv_bulk_g2s(dst + STAGE_W, m, STAGE_M, bar);
+                    }
                     w += STAGE_W; m += STAGE_M;
                     if (++slot == p.S) { slot = 0; parity ^= 1u; }
                 }
@@ -356,12 +395,27 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
                     if (++spins > GV_SPIN_LIMIT) __trap();
                 } while (seen < target);
             }
+            stamp(o, 4);
             ch_bar_consumers();
         }
         stamp(o, 0);
         if (o + 1 == p.n_ops) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
         const bool poll = op.mbox_in != nullptr;
-        ch_stage_x<MR, MPU>(poll ? reinterpret_cast<const __nv_bfloat16 *>(op.mbox_in + mb_cur) : op.x, xs, gtab, op.M, op.K, tid, lane, poll);
+        if (poll) {
+            if (tid == 0) {
+                const unsigned long long target = ((unsigned long long)run + 1ull) * (unsigned long long)grid;
+                unsigned long long seen;
+                uint32_t spins = 0;
+                do {
+                    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(seen) : "l"(op.arrive_in) : "memory");
+                    if (++spins > GV_SPIN_LIMIT) __trap();
+                } while (seen < target);
+            }
+            stamp(o, 4);
+            ch_bar_consumers();
+        }
+        ch_stage_x<MR, MPU>(poll ? reinterpret_cast<const __nv_bfloat16 *>(op.mbox_in + mb_cur) : op.x, xs, gtab, op.M, op.K, tid, lane, poll,
+                            p.dbg ? p.dbg + ((size_t)o * grid + cta) * CH_DBG_WORDS + 5 : nullptr);
         if (poll) {
             // put the sentinel back into the OTHER parity of what was just read: its last readers finished a run ago, its
             // next writers run a run from now (they cannot start before every CTA has passed this point)
@@ -407,6 +461,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
             }
         }
         ch_bar_consumers();   // part / xs are free again; this CTA's y stores precede whatever thread 0 releases next
+        if (op.arrive_out && tid == 0) asm volatile("red.relaxed.gpu.global.add.u64 [%0], 1;" ::"l"(op.arrive_out) : "memory");
         stamp(o, 3);
     }
     if (p.n_ops > 1 && cta == 0 && tid == 0) *p.runs = run + 1u;   // everybody read `runs` before the first barrier
@@ -426,6 +481,7 @@ struct Chain {
     unsigned long long *d_counter = nullptr;
     unsigned int *d_runs = nullptr;
     unsigned short *d_mbox = nullptr;
+    unsigned long long *d_arrive = nullptr;
     int n_mailboxes = 0, n_barriers = 0;
     unsigned long long *d_dbg = nullptr;
     ChainParams prm{};
@@ -472,7 +528,7 @@ static int chain_launch(const Chain &c, cudaStream_t stream) {
 
 static void chain_free(Chain *c) {
     if (!c) return;
-    cudaFree(c->d_ops); cudaFree(c->d_rb); cudaFree(c->d_counter); cudaFree(c->d_runs); cudaFree(c->d_mbox); cudaFree(c->d_dbg);
+    cudaFree(c->d_ops); cudaFree(c->d_rb); cudaFree(c->d_counter); cudaFree(c->d_runs); cudaFree(c->d_mbox); cudaFree(c->d_arrive); cudaFree(c->d_dbg);
     delete c;
 }
 
@@ -553,6 +609,8 @@ static int chain_plan(Chain *c) {
             ++c->n_mailboxes;
         }
     if (mbox_total) {
+        W4_CUDA_OK(cudaMalloc(&c->d_arrive, (size_t)n * 16 * sizeof(unsigned long long)));     // one 128-byte line per linear
+        W4_CUDA_OK(cudaMemset(c->d_arrive, 0, (size_t)n * 16 * sizeof(unsigned long long)));
         W4_CUDA_OK(cudaMalloc(&c->d_mbox, (size_t)mbox_total * 2 * sizeof(unsigned short)));
         W4_CUDA_OK(cudaMemset(c->d_mbox, 0xFF, (size_t)mbox_total * 2 * sizeof(unsigned short)));
     }
@@ -579,6 +637,8 @@ static int chain_plan(Chain *c) {
         c->n_barriers += barrier[i];
         o.mbox_out = mbox_off[i] >= 0 ? c->d_mbox + mbox_off[i] : nullptr;
         o.mbox_in = dep[i] >= 0 ? c->d_mbox + mbox_off[dep[i]] + (lo_x(i) - lo_y(dep[i])) / 2 : nullptr;
+        o.arrive_out = mbox_off[i] >= 0 ? c->d_arrive + (size_t)i * 16 : nullptr;
+        o.arrive_in = dep[i] >= 0 ? c->d_arrive + (size_t)dep[i] * 16 : nullptr;
     }
     W4_CUDA_OK(cudaMemcpy(c->d_rb, rb.data(), rb.size() * sizeof(int), cudaMemcpyHostToDevice));
     W4_CUDA_OK(cudaMalloc(&c->d_ops, ops.size() * sizeof(ChainOp)));
@@ -597,6 +657,8 @@ static int chain_plan(Chain *c) {
     p.counter = c->d_counter; p.runs = c->d_runs;
     p.n_barriers = c->n_barriers; p.mbox_stride = mbox_total;
     p.S = (int)S; p.slot_stride = (int)stride;
+    p.exp_nometa = gv_env_int("W4A16_CHAIN_EXP_NOMETA", 0);
+    p.max_inflight = std::max(1, std::min<int>((int)S, gv_env_int("W4A16_CHAIN_INFLIGHT", (int)S)));
     p.off_xs = off_xs; p.off_gtab = off_gtab; p.off_part = off_part; p.off_ring = off_ring;
     p.dbg = c->d_dbg;
     c->persistent = true;

@@ -771,10 +771,10 @@ class DecodeChain:
         check(lib().w4a16_chain_run(self._c, torch.cuda.current_stream(self._device).cuda_stream))
 
     def debug_stamps(self):
-        """[n, CTAs, 4] %globaltimer stamps of the last run (W4A16_GV_DEBUG=1 at creation)."""
+        """[n, CTAs, 8] %globaltimer stamps of the last run (W4A16_GV_DEBUG=1 at creation)."""
         import numpy as np
         sms = torch.cuda.get_device_properties(self._device).multi_processor_count
-        buf = np.zeros((self._n, sms, 4), dtype=np.uint64)
+        buf = np.zeros((self._n, sms, 8), dtype=np.uint64)
         check(lib().w4a16_chain_debug_stamps(self._c, ctypes.c_void_p(buf.ctypes.data), buf.size))
         return buf
 
