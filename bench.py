@@ -63,11 +63,12 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
 
 
-def decode_traffic(world):
-    """dram bytes per launch of the decode kernel from the committed ncu --set full capture (profiles/, written by
-    tools/capture_decode_traffic.py together with the git hash of the tree it measured), averaged over the four
-    Qwen3-8B shapes like `achieved`; None for the TP workload (not captured under ncu)."""
-    for name in ("r2_decode_traffic.json", "r1_decode_traffic.json"):
+def decode_traffic(world, chain, n_linears):
+    """dram bytes per LINEAR from the committed ncu --set full capture of the kernel in use (profiles/, written together
+    with the git hash of the tree it measured), in the unit of `achieved` (per linear, averaged over the step's shapes);
+    None for the TP workload (not captured under ncu)."""
+    names = ("r2_chain_traffic.json",) if chain else ("r2_decode_traffic.json", "r1_decode_traffic.json")
+    for name in names:
         p = os.path.join(ROOT, "profiles", name)
         if world == 1 and os.path.exists(p):
             d = json.load(open(p))
@@ -302,6 +303,32 @@ def run_gpu(args):
                 one_step()
         run = graph.replay if graph is not None else one_step
         ms_per_step, clk = timed_steps(torch, dist, dev, run, stream, args, world, rank, local)
+    per_linear = {"api": "w4a16_forward_into per linear, one CUDA graph per step, programmatic launches",
+                  "ms_per_step": round(ms_per_step, 4), "GBps": round(step_bytes / (ms_per_step * 1e-3) / 1e9, 1),
+                  "kernel": layers[0][6].kernel_for(M), "launches_per_step": int(launches_per_step),
+                  "data_flow": "static x per shape (linears ordered by the stream only)"}
+    # N = 1 headline: the same 144 linears as ONE DecodeChain (w4a16_chain_run, one persistent launch per step) with the
+    # model's data flow -- every linear reads what the previous one wrote, so the order is a true dependency
+    chain, chain_kernel, launch = None, None, "cuda-graph replay" if graph is not None else "stream launches"
+    if world == 1 and args.api == "chain":
+        chain = P.DecodeChain(chain_steps(torch, layers, M, dev))
+        chain_kernel = chain.kernel()
+        if not chain_kernel.startswith("chain_imma"):
+            chain = None
+    if chain is not None:
+        cgraph = None
+        launches0 = P.kernel_launches()
+        with torch.cuda.stream(stream):
+            chain.run()
+            launches_per_step = P.kernel_launches() - launches0
+            if args.graph:
+                cgraph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(cgraph, stream=stream):
+                    chain.run()
+            ms_per_step, clk = timed_steps(torch, dist, dev, cgraph.replay if cgraph is not None else chain.run, stream, args,
+                                           world, rank, local)
+        per_linear["frac_measured_hbm"] = round(per_linear["GBps"] / peaks["hbm_gbs"], 4)
+        launch = "one persistent launch per step (w4a16_chain_run" + (", CUDA-graph replay)" if cgraph is not None else ")")
     gbs = step_bytes / (ms_per_step * 1e-3) / 1e9
     n_lin = len(layers)
 
@@ -313,7 +340,9 @@ def run_gpu(args):
         "config": {"workload": workload, "group_size": GROUP, "M": M, "parallelism": parallelism,
                    "linears_per_step": n_lin, "weight_bytes_per_step": step_bytes,
                    "l2_policy": "inputs larger than L2: every step streams %.2f GB of distinct weights" % (step_bytes / 1e9 / max(world, 1)),
-                   "launch": "cuda-graph replay" if graph is not None else "stream launches", "pdl": os.environ.get("W4A16_NO_PDL", "0") == "0",
+                   "launch": launch, "pdl": os.environ.get("W4A16_NO_PDL", "0") == "0",
+                   "data_flow": ("every linear reads the previous linear's output (bench.chain_steps): true dependencies"
+                                 if chain is not None else "static x per shape"),
                    "allreduce": (None if world == 1 else "fused GEMV epilogue over NVLink peer memory (one kernel, no NCCL launch)"
                                  if peers is not None else "ncclAllReduce after the GEMV")},
         "gpu_launches": int(launches_per_step * args.steps),
@@ -322,19 +351,27 @@ def run_gpu(args):
     if tp_chk is not None:
         out["tp_check"] = tp_chk
     # -- roofline of the dominant kernel (decode GEMV) ---------------------------------
-    per_launch_bytes = step_bytes / n_lin / max(world, 1)
-    per_launch_ms = ms_per_step / n_lin
+    n_launch = 1 if chain is not None else n_lin          # the chain is ONE launch per step
+    per_launch_bytes = step_bytes / n_launch / max(world, 1)
+    per_launch_ms = ms_per_step / n_launch
     achieved = per_launch_bytes / (per_launch_ms * 1e-3) / 1e9
-    traffic, traffic_src = decode_traffic(world)
-    out["roofline"] = {"bound": "hbm", "kernel": layers[0][6].kernel_for(M), "achieved": round(achieved, 1),
+    traffic, traffic_src = decode_traffic(world, chain is not None, n_lin)
+    if chain is not None:
+        out["per_linear_api"] = per_linear
+    out["roofline"] = {"bound": "hbm", "kernel": chain_kernel if chain is not None else layers[0][6].kernel_for(M),
+                       "achieved": round(achieved, 1),
                        "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": round(achieved / peaks["hbm_gbs"], 4),
                        "traffic": traffic, "traffic_source": traffic_src, "peak_source": peaks["source"],
                        "frac_of_spec_8TBs": round(achieved / 8000.0, 4),
                        "algorithmic_bytes_per_launch": int(per_launch_bytes)}
     if rank == 0 and world == 1:
         if not args.quick:
-            out["e2e"] = e2e_host(P, torch, dev, layers, args)
-        del layers, xs, ys, graph
+            if chain is not None:
+                out["e2e"] = e2e_chain(P, torch, dev, chain, layers, args)
+                out["e2e_per_linear"] = e2e_host(P, torch, dev, layers, args)
+            else:
+                out["e2e"] = e2e_host(P, torch, dev, layers, args)
+        del layers, xs, ys, graph, chain
         torch.cuda.empty_cache()
         out["per_shape"], out["sweep"] = shape_sweep(P, torch, dev, peaks, args)
         if not args.quick:
@@ -639,6 +676,25 @@ def reference_gpu(torch, dev, peaks):
             "points": rows}
 
 
+def e2e_chain(P, torch, dev, chain, layers, args):
+    """The end-to-end decode step through the C ABI with HOST buffers: w4a16_chain_run_host = H2D copy of the step's
+    input (the first linear's x, pinned), the chain, D2H copy of the step's result (the last linear's y), stream sync.
+    The activations between the linears stay on the device, as they do in the reference."""
+    M = 1
+    hx = torch.randn((M, layers[0][3])).mul_(0.05).to(torch.bfloat16).pin_memory()
+    hy = torch.empty((M, layers[-1][4]), dtype=torch.bfloat16).pin_memory()
+    steps = max(3, min(args.steps, 20))
+    chain.run_host(hx, hy)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        chain.run_host(hx, hy)
+    dt = (time.perf_counter() - t0) / steps
+    step_bytes = sum(algo_bytes(M, K, N) for _, K, N, *_ in layers)
+    return {"value": round(step_bytes / dt / 1e9, 1), "unit": "GB/s", "ms_per_step": round(dt * 1e3, 3),
+            "h2d_bytes_per_step": int(hx.numel() * 2), "d2h_bytes_per_step": int(hy.numel() * 2),
+            "api": "w4a16_chain_run_host per step (pinned host x of the first linear in, y of the last linear out, sync per step)"}
+
+
 def e2e_host(P, torch, dev, layers, args):
     """The reference-facing call with HOST buffers: w4a16_forward_host per linear
     (pinned x -> H2D -> kernel -> D2H -> pinned y -> stream sync), every linear of the step."""
@@ -748,6 +804,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--layers", type=int, default=0, help="override the number of decoder layers (debug)")
     ap.add_argument("--no-graph", dest="graph", action="store_false")
+    ap.add_argument("--api", default="chain", choices=["chain", "linear"],
+                    help="N=1 headline: the step as one DecodeChain (persistent launch) or as per-linear launches")
     ap.add_argument("--no-fused-ar", dest="fused_ar", action="store_false",
                     help="TP runs: all-reduce through ncclAllReduce instead of the fused GEMV epilogue over peer memory")
     ap.add_argument("--quick", action="store_true", help="decode step + short sweep only (no prefill / e2e / cpu legs)")

@@ -232,6 +232,11 @@ typedef struct w4a16_chain *w4a16_chain_t;
 int w4a16_chain_create(w4a16_chain_t *out, int n, const w4a16_handle_t *handles,
                        const void *const *x_bf16, void *const *y_bf16, int64_t M);
 int w4a16_chain_run(w4a16_chain_t chain, w4a16_stream_t stream);
+/* chain_run with HOST buffers at the two ends: H2D copy of the first linear's x ([M, in_features] bf16), the chain,
+ * D2H copy of the last linear's y, stream synchronise -- what one decode step moves between host and device (the
+ * activations in between never leave the GPU, in the reference neither).  The end-to-end call bench.py times. */
+int w4a16_chain_run_host(w4a16_chain_t chain, const void *x0_bf16_host, void *y_last_bf16_host,
+                         w4a16_stream_t stream);
 int w4a16_chain_destroy(w4a16_chain_t chain);
 /* "chain_imma (<m> mailboxes, <b> barriers)" (persistent launch) or "per_linear (<reason>)".
  * Ordering inside the persistent launch: where x[i] lies inside the y of the latest earlier

@@ -47,7 +47,7 @@ def main():
     a = chain.debug_stamps().astype(np.int64)       # [n, ctas, 4]
     n = len(steps)
     t0 = a[n - 4, :, 0].min()
-    labels = [(0, "started"), (4, "hint-seen"), (5, "x-valid"), (1, "staged"), (2, "streamed"), (3, "written")]
+    labels = [(0, "started"), (4, "hint-seen"), (5, "x-valid"), (7, "x-all"), (1, "staged"), (2, "streamed"), (3, "written")]
     for o in range(n - 4, n):
         print(f"-- {names[o]}")
         for i, nm in labels:

@@ -1,5 +1,5 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 300 python tools/decode_ab.py --api chain --chain --cfg "" --cfg "W4A16_CHAIN_INFLIGHT=1" --cfg "W4A16_CHAIN_INFLIGHT=2" --cfg "W4A16_CHAIN_INFLIGHT=3" --cfg "W4A16_CHAIN_INFLIGHT=4" 2>&1 | grep "\[ab\]" | tee gpurun_out/i_ab.log
-W4A16_CHAIN_INFLIGHT=2 timeout 300 python tools/chain_timeline.py > gpurun_out/i_ctl2.log 2>&1
-cat gpurun_out/i_ctl2.log
+timeout 120 python tools/prof_chain.py > gpurun_out/j_prof_plain.log 2>&1 && \
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:chain_kernel -s 1 -c 1 -o gpurun_out/j_chain2 -f python tools/prof_chain.py > gpurun_out/j_ncu.log 2>&1
+tail -3 gpurun_out/j_ncu.log

@@ -60,8 +60,6 @@ struct ChainParams {
     int n_barriers;                // grid barriers per run
     long long mbox_stride;         // elements between the two parities of every mailbox (run r uses parity r & 1)
     int S, slot_stride;            // ring stages, bytes per stage slot
-    int exp_nometa;                // timing experiment only (wrong results): the producer skips the meta copies
-    int max_inflight;              // stages the producer keeps in flight (<= S)
     int off_xs, off_gtab, off_part, off_ring;
     unsigned long long *dbg;       // [n_ops][grid][CH_DBG_WORDS] %globaltimer stamps, or null
 };
@@ -111,100 +109,132 @@ __device__ __forceinline__ bool ch_has_sentinel(const uint4 &v) {
     return hit != 0;
 }
 
-// poll: x is a mailbox (see ChainOp): every 16-byte piece is re-read until none of its eight values is the sentinel.
+// One batch of NB 16-byte pieces per thread (pieces base + r * 512 + tid).  poll: x is a mailbox (see ChainOp): every
+// piece is re-read until none of its eight values is the sentinel.  The arithmetic of the NB pieces runs side by side
+// (independent dependency chains), the shared-memory stores follow.
+template <int MR, int MPU, int NB>
+__device__ __forceinline__ void ch_stage_batch(const uint4 *x16, uint8_t *xs, int2 *gtab, int ppr, int total, int base, int tid, int lane,
+                                               bool poll, unsigned long long *dbg_valid) {
+    constexpr int COLS = 2 * MR;
+    constexpr int GL = (GV_UNIT_K / MPU) / 8;
+    const uint32_t gmask = (GL >= 32 ? 0xFFFFFFFFu : ((1u << GL) - 1u)) << (lane & ~(GL - 1));
+    uint4 v[NB];
+#pragma unroll
+    for (int r = 0; r < NB; ++r) {
+        const int i = base + r * CH_CONS_THREADS + tid;
+        v[r] = i < total ? (poll ? ch_ld_relaxed(x16 + i) : __ldcg(x16 + i)) : make_uint4(0, 0, 0, 0);
+    }
+    if (poll) {
+        uint32_t spins = 0;
+        for (;;) {
+            bool bad[NB], any = false;
+#pragma unroll
+            for (int r = 0; r < NB; ++r) {
+                bad[r] = base + r * CH_CONS_THREADS + tid < total && ch_has_sentinel(v[r]);
+                any |= bad[r];
+            }
+            if (!any) break;
+#pragma unroll
+            for (int r = 0; r < NB; ++r)
+                if (bad[r]) v[r] = ch_ld_relaxed(x16 + base + r * CH_CONS_THREADS + tid);
+            if (++spins > GV_SPIN_LIMIT) __trap();
+        }
+        if (dbg_valid && tid == 0 && base == 0) {
+            unsigned long long tt;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt));
+            dbg_valid[0] = tt;
+            dbg_valid[1] = spins;
+        }
+        __syncwarp();
+    }
+    if (dbg_valid) {   // profiling only: when has EVERY thread of the CTA got its pieces?  (word 7 of the stamps)
+        ch_bar_consumers();
+        if (tid == 0) {
+            unsigned long long tt;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt));
+            dbg_valid[2] = tt;
+        }
+    }
+    uint32_t pkA[NB][4], mxA[NB];
+    int sumA[NB], EA[NB];
+#pragma unroll
+    for (int r = 0; r < NB; ++r) {
+        const uint32_t w4[4] = {v[r].x, v[r].y, v[r].z, v[r].w};
+        uint32_t mx = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) mx = max(mx, max(w4[q] & 0x7FFFu, (w4[q] >> 16) & 0x7FFFu));
+        mxA[r] = mx;
+    }
+#pragma unroll
+    for (int r = 0; r < NB; ++r) mxA[r] = ch_redux_max(mxA[r], gmask);   // over the GL lanes that hold the group
+#pragma unroll
+    for (int r = 0; r < NB; ++r) {
+        const uint32_t w4[4] = {v[r].x, v[r].y, v[r].z, v[r].w};
+        int E = (int)(mxA[r] >> 7);
+        E = min(max(E, 14), 254);
+        EA[r] = E;
+        const float scale = __int_as_float((267 - E) << 23);     // max|x| lands in [2^13, 2^14)
+        int sum = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const float lo = fmaf(__uint_as_float(w4[q] << 16), scale, 12582912.f);
+            const float hi = fmaf(__uint_as_float(w4[q] & 0xFFFF0000u), scale, 12582912.f);
+            pkA[r][q] = __byte_perm(__float_as_uint(lo), __float_as_uint(hi), 0x5410);
+            sum = __dp2a_lo((int)pkA[r][q], 0x0101, sum);
+        }
+        sumA[r] = sum;
+    }
+#pragma unroll
+    for (int r = 0; r < NB; ++r) sumA[r] = ch_redux_add(sumA[r], gmask);
+#pragma unroll
+    for (int r = 0; r < NB; ++r) {
+        const int i = base + r * CH_CONS_THREADS + tid;
+        const uint32_t *pk = pkA[r];
+        if (i < total) {
+            const int m = MR == 1 ? 0 : (i >= ppr) + (MR > 2 ? (i >= 2 * ppr) + (i >= 3 * ppr) : 0);
+            const int c = i - m * ppr;
+            const int j = (c & 15) >> 1;
+            uint8_t *dst = xs + ((size_t)(((c >> 4) * 4 + (j >> 1)) * 4 + 2 * (c & 1)) * COLS + 2 * m) * 8 + (j & 1) * 4;
+            uint32_t hiP[4], loP[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { hiP[q] = (pk[q] >> 7) & 0x00FF00FFu; loP[q] = pk[q] & 0x007F007Fu; }
+            uint32_t v0 = hiP[0] | (hiP[1] << 8), v1 = loP[0] | (loP[1] << 8);
+            uint32_t v2 = hiP[2] | (hiP[3] << 8), v3 = loP[2] | (loP[3] << 8);
+            if constexpr (MR >= 2) {   // rotate the order of the four stores per lane group: 16-way -> 4-way bank conflicts
+                const int rot = (lane >> 2) & 3;
+                if (rot & 1) { const uint32_t tv = v0; v0 = v1; v1 = v2; v2 = v3; v3 = tv; }
+                if (rot & 2) { uint32_t tv = v0; v0 = v2; v2 = tv; tv = v1; v1 = v3; v3 = tv; }
+                const uint32_t vv[4] = {v0, v1, v2, v3};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int idx = (k + rot) & 3;
+                    *reinterpret_cast<uint32_t *>(dst + (idx & 1) * 8 + (idx >> 1) * (COLS * 8)) = vv[k];
+                }
+            } else {
+                *reinterpret_cast<uint32_t *>(dst) = v0;
+                *reinterpret_cast<uint32_t *>(dst + 8) = v1;
+                *reinterpret_cast<uint32_t *>(dst + COLS * 8) = v2;
+                *reinterpret_cast<uint32_t *>(dst + COLS * 8 + 8) = v3;
+            }
+            if ((c & (GL - 1)) == 0)
+                gtab[(size_t)(c / GL) * MR + m] = make_int2(sumA[r], mxA[r] >= 0x7F80u ? 0x7FC00000 : (EA[r] - 13) << 23);
+        }
+    }
+}
+
+// Activation staging of one linear by the 512 consumer threads: the arithmetic of gemv_imma_kernel (per-(group, token)
+// power-of-two scale, two signed-byte planes in B-fragment order, integer group sums, Inf / NaN poison the group).
 template <int MR, int MPU>
 __device__ __forceinline__ void ch_stage_x(const __nv_bfloat16 *x, uint8_t *xs, int2 *gtab, int M, int K, int tid, int lane, bool poll,
                                            unsigned long long *dbg_valid) {
-    constexpr int COLS = 2 * MR;
-    constexpr int GL = (GV_UNIT_K / MPU) / 8;
     const int ppr = K >> 3, total = M * ppr;
     const uint4 *x16 = reinterpret_cast<const uint4 *>(x);
-    constexpr int BATCH = 4;
-    const uint32_t gmask = (GL >= 32 ? 0xFFFFFFFFu : ((1u << GL) - 1u)) << (lane & ~(GL - 1));
-    for (int base = 0; base < total; base += BATCH * CH_CONS_THREADS) {
-        uint4 v[BATCH];
-#pragma unroll
-        for (int r = 0; r < BATCH; ++r) {
-            const int i = base + r * CH_CONS_THREADS + tid;
-            v[r] = i < total ? (poll ? ch_ld_relaxed(x16 + i) : __ldcg(x16 + i)) : make_uint4(0, 0, 0, 0);
-        }
-        if (poll) {
-            // re-read every piece that still holds a sentinel, all of them in flight together
-            uint32_t spins = 0;
-            for (;;) {
-                bool bad[BATCH], any = false;
-#pragma unroll
-                for (int r = 0; r < BATCH; ++r) {
-                    bad[r] = base + r * CH_CONS_THREADS + tid < total && ch_has_sentinel(v[r]);
-                    any |= bad[r];
-                }
-                if (!any) break;
-#pragma unroll
-                for (int r = 0; r < BATCH; ++r)
-                    if (bad[r]) v[r] = ch_ld_relaxed(x16 + base + r * CH_CONS_THREADS + tid);
-                if (++spins > GV_SPIN_LIMIT) __trap();
-            }
-            if (dbg_valid && tid == 0 && base == 0) {
-                unsigned long long tt;
-                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt));
-                dbg_valid[0] = tt;
-                dbg_valid[1] = spins;
-            }
-            __syncwarp();
-        }
-#pragma unroll
-        for (int r = 0; r < BATCH; ++r) {
-            const int i = base + r * CH_CONS_THREADS + tid;
-            if (base + r * CH_CONS_THREADS >= total) break;               // warp-uniform
-            const uint32_t w4[4] = {v[r].x, v[r].y, v[r].z, v[r].w};
-            uint32_t mx = 0;
-#pragma unroll
-            for (int q = 0; q < 4; ++q) mx = max(mx, max(w4[q] & 0x7FFFu, (w4[q] >> 16) & 0x7FFFu));
-            mx = ch_redux_max(mx, gmask);            // over the GL lanes that hold the group
-            int E = (int)(mx >> 7);
-            E = min(max(E, 14), 254);
-            const float scale = __int_as_float((267 - E) << 23);     // max|x| lands in [2^13, 2^14)
-            uint32_t pk[4];
-            int sum = 0;
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const float lo = fmaf(__uint_as_float(w4[q] << 16), scale, 12582912.f);
-                const float hi = fmaf(__uint_as_float(w4[q] & 0xFFFF0000u), scale, 12582912.f);
-                pk[q] = __byte_perm(__float_as_uint(lo), __float_as_uint(hi), 0x5410);
-                sum = __dp2a_lo((int)pk[q], 0x0101, sum);
-            }
-            sum = ch_redux_add(sum, gmask);
-            if (i < total) {
-                const int m = MR == 1 ? 0 : (i >= ppr) + (MR > 2 ? (i >= 2 * ppr) + (i >= 3 * ppr) : 0);
-                const int c = i - m * ppr;
-                const int j = (c & 15) >> 1;
-                uint8_t *dst = xs + ((size_t)(((c >> 4) * 4 + (j >> 1)) * 4 + 2 * (c & 1)) * COLS + 2 * m) * 8 + (j & 1) * 4;
-                uint32_t hiP[4], loP[4];
-#pragma unroll
-                for (int q = 0; q < 4; ++q) { hiP[q] = (pk[q] >> 7) & 0x00FF00FFu; loP[q] = pk[q] & 0x007F007Fu; }
-                uint32_t v0 = hiP[0] | (hiP[1] << 8), v1 = loP[0] | (loP[1] << 8);
-                uint32_t v2 = hiP[2] | (hiP[3] << 8), v3 = loP[2] | (loP[3] << 8);
-                if constexpr (MR >= 2) {   // rotate the order of the four stores per lane group: 16-way -> 4-way bank conflicts
-                    const int rot = (lane >> 2) & 3;
-                    if (rot & 1) { const uint32_t tv = v0; v0 = v1; v1 = v2; v2 = v3; v3 = tv; }
-                    if (rot & 2) { uint32_t tv = v0; v0 = v2; v2 = tv; tv = v1; v1 = v3; v3 = tv; }
-                    const uint32_t vv[4] = {v0, v1, v2, v3};
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const int idx = (k + rot) & 3;
-                        *reinterpret_cast<uint32_t *>(dst + (idx & 1) * 8 + (idx >> 1) * (COLS * 8)) = vv[k];
-                    }
-                } else {
-                    *reinterpret_cast<uint32_t *>(dst) = v0;
-                    *reinterpret_cast<uint32_t *>(dst + 8) = v1;
-                    *reinterpret_cast<uint32_t *>(dst + COLS * 8) = v2;
-                    *reinterpret_cast<uint32_t *>(dst + COLS * 8 + 8) = v3;
-                }
-                if ((c & (GL - 1)) == 0)
-                    gtab[(size_t)(c / GL) * MR + m] = make_int2(sum, mx >= 0x7F80u ? 0x7FC00000 : (E - 13) << 23);
-            }
-        }
-    }
+    int base = 0;
+    for (; base + 3 * CH_CONS_THREADS <= total; base += 3 * CH_CONS_THREADS)
+        ch_stage_batch<MR, MPU, 3>(x16, xs, gtab, ppr, total, base, tid, lane, poll, dbg_valid);
+    const int left = (total - base + CH_CONS_THREADS - 1) / CH_CONS_THREADS;   // 0..2 (warp-uniform)
+    if (left == 2) ch_stage_batch<MR, MPU, 2>(x16, xs, gtab, ppr, total, base, tid, lane, poll, dbg_valid);
+    else if (left == 1) ch_stage_batch<MR, MPU, 1>(x16, xs, gtab, ppr, total, base, tid, lane, poll, dbg_valid);
 }
 
 // The row blocks of one linear, stage after stage from the ring; every warp takes two units (wi, wi + 16) of every
@@ -329,8 +359,8 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
         // ---- producer: the CTA's share of every linear's W4T stream, in chain order, as fast as slots come free.
         //      Weights are immutable, so this neither waits for the previous kernel nor for the grid barriers. ----
         if (lane == 0) {
-            int slot = 0, lslot = 0, issued = 0;
-            uint32_t parity = 1u, lpar = 0u;         // first round: slots are free (wait on the phase before the first)
+            int slot = 0;
+            uint32_t parity = 1u;                    // first round: slots are free (wait on the phase before the first)
             for (int o = 0; o < p.n_ops; ++o) {
                 const ChainOp *op = p.ops + o;
                 const int *rb = op->rb;
@@ -339,21 +369,12 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
                 const size_t unit0 = (size_t)R0 * op->UPR;
                 const uint8_t *w = op->qw + unit0 * GV_UNIT_BYTES;
                 const uint8_t *m = op->meta + unit0 * (MPU * META_BYTES);
-                for (int s = 0; s < nst; ++s, ++issued) {
-                    if (issued >= p.max_inflight) {          // stage issued - max_inflight must have landed
-                        gv_mbar_wait(bar_full + 8 * lslot, lpar);
-                        if (++lslot == p.S) { lslot = 0; lpar ^= 1u; }
-                    }
+                for (int s = 0; s < nst; ++s) {
                     gv_mbar_wait(bar_empty + 8 * slot, parity);
                     const uint32_t bar = bar_full + 8 * slot, dst = ring + (uint32_t)slot * (uint32_t)p.slot_stride;
-                    if (p.exp_nometa) {
-                        gv_mbar_expect_tx(bar, STAGE_W);
-                        gv_bulk_g2s(dst, w, STAGE_W, bar);
-                    } else {
-                        gv_mbar_expect_tx(bar, STAGE_W + STAGE_M);
-                        gv_bulk_g2s(dst, w, STAGE_W, bar);
-                        gv_bulk_g2s(dst + STAGE_W, m, STAGE_M, bar);
-                    }
+                    gv_mbar_expect_tx(bar, STAGE_W + STAGE_M);
+                    gv_bulk_g2s(dst, w, STAGE_W, bar);
+                    gv_bulk_g2s(dst + STAGE_W, m, STAGE_M, bar);
                     w += STAGE_W; m += STAGE_M;
                     if (++slot == p.S) { slot = 0; parity ^= 1u; }
                 }
@@ -565,7 +586,7 @@ static int chain_plan(Chain *c) {
     const int64_t stride = 32 * (GV_UNIT_BYTES + c->mpu * META_BYTES);
     int64_t S = (CH_SMEM_MAX - off) / stride;
     if (S < 3) { c->why_not = "activations leave no room for a ring of 3 stages"; return 0; }
-    S = std::min<int64_t>(S, std::min<int64_t>(CH_MAX_STAGES, gv_env_int("W4A16_CHAIN_STAGES", CH_MAX_STAGES)));
+    S = std::min<int64_t>(S, CH_MAX_STAGES);
     const int off_ring = (int)off; off += S * stride;
     c->smem = (int)off;
     c->grid = grid;
@@ -657,8 +678,6 @@ static int chain_plan(Chain *c) {
     p.counter = c->d_counter; p.runs = c->d_runs;
     p.n_barriers = c->n_barriers; p.mbox_stride = mbox_total;
     p.S = (int)S; p.slot_stride = (int)stride;
-    p.exp_nometa = gv_env_int("W4A16_CHAIN_EXP_NOMETA", 0);
-    p.max_inflight = std::max(1, std::min<int>((int)S, gv_env_int("W4A16_CHAIN_INFLIGHT", (int)S)));
     p.off_xs = off_xs; p.off_gtab = off_gtab; p.off_part = off_part; p.off_ring = off_ring;
     p.dbg = c->d_dbg;
     c->persistent = true;
@@ -718,6 +737,28 @@ int w4a16_chain_run(w4a16_chain_t chain, w4a16_stream_t stream) {
         for (int i = 0; i < c->n && !rc; ++i)
             rc = forward_linear(c->lin[i], c->x[i], c->y[i], c->M, reinterpret_cast<cudaStream_t>(stream));
     }
+    if (prev != c->device) cudaSetDevice(prev);
+    return rc;
+}
+
+int w4a16_chain_run_host(w4a16_chain_t chain, const void *x0_host, void *y_last_host, w4a16_stream_t stream) {
+    Chain *c = reinterpret_cast<Chain *>(chain);
+    if (!c) return fail("chain_run_host: null chain");
+    if (!x0_host || !y_last_host) return fail("chain_run_host: null host buffer");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    Linear *first = c->lin.front(), *last = c->lin.back();
+    const size_t xb = (size_t)c->M * first->d.K * sizeof(__nv_bfloat16);
+    const size_t yb = (size_t)c->M * (last->epilogue == W4A16_EPILOGUE_SWIGLU ? last->d.N / 2 : last->d.N) * sizeof(__nv_bfloat16);
+    int prev = 0;
+    cudaGetDevice(&prev);
+    if (prev != c->device) cudaSetDevice(c->device);
+    int rc = 0;
+    if (cudaMemcpyAsync(const_cast<__nv_bfloat16 *>(c->x.front()), x0_host, xb, cudaMemcpyHostToDevice, st) != cudaSuccess)
+        rc = fail("chain_run_host: host-to-device copy of x failed");
+    if (!rc) rc = w4a16_chain_run(chain, stream);
+    if (!rc && cudaMemcpyAsync(y_last_host, c->y.back(), yb, cudaMemcpyDeviceToHost, st) != cudaSuccess)
+        rc = fail("chain_run_host: device-to-host copy of y failed");
+    if (!rc && cudaStreamSynchronize(st) != cudaSuccess) rc = fail("chain_run_host: stream synchronise failed");
     if (prev != c->device) cudaSetDevice(prev);
     return rc;
 }

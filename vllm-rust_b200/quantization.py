@@ -770,6 +770,13 @@ class DecodeChain:
     def run(self) -> None:
         check(lib().w4a16_chain_run(self._c, torch.cuda.current_stream(self._device).cuda_stream))
 
+    def run_host(self, x0_host: torch.Tensor, y_last_host: torch.Tensor) -> None:
+        """run() with HOST (ideally pinned) buffers at the two ends of the chain: H2D, chain, D2H, sync."""
+        with torch.cuda.device(self._device):
+            check(lib().w4a16_chain_run_host(self._c, ctypes.c_void_p(x0_host.data_ptr()),
+                                             ctypes.c_void_p(y_last_host.data_ptr()),
+                                             torch.cuda.current_stream(self._device).cuda_stream))
+
     def debug_stamps(self):
         """[n, CTAs, 8] %globaltimer stamps of the last run (W4A16_GV_DEBUG=1 at creation)."""
         import numpy as np
