@@ -19,6 +19,14 @@
  *     it can be captured in a CUDA graph (replaces OutputPool-backed
  *     marlin_gemm_pooled, marlin_cuda.rs:1655-1753).
  *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream).
+ *   - Re-entrancy: the weights are read-only after load, and every scratch a forward
+ *     uses belongs either to the handle or to the (device, stream) pair, so different
+ *     handles may run concurrently on different streams.  ONE handle runs one forward
+ *     at a time (its calls must be stream-ordered), like the reference's MarlinLinear
+ *     with its workspace tensor (marlin.rs:586-640).  Scratch is grown outside stream
+ *     capture only and an outgrown buffer lives as long as its handle, so a captured
+ *     graph never sees a freed address; inside a capture a too-small scratch is an
+ *     error that names w4a16_reserve.
  *   - There is no CPU fallback.  If no sm_100 device is present every call that
  *     needs one fails loudly.
  */

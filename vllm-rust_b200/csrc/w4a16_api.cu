@@ -86,6 +86,7 @@ static void free_linear(Linear *L) {
     cudaFree(L->qw); cudaFree(L->meta); cudaFree(L->bias); cudaFree(L->perm); cudaFree(L->tickets);
     cudaFree(L->splitk_scratch); cudaFree(L->x_gather); cudaFree(L->stage_x); cudaFree(L->stage_y);
     cudaFree(L->rowpar_f32); cudaFree(L->gv_tab);
+    for (void *q : L->retired) cudaFree(q);
     delete L;
 }
 
@@ -184,18 +185,29 @@ static int nccl_check(int rc, const char *what) {
 }
 constexpr int NCCL_BF16 = 9, NCCL_SUM = 0;
 
-static int ensure_stage(Linear *L, int64_t M) {
+// Scratch that scales with M is grown on demand but never freed before the handle is: a CUDA graph captured earlier may
+// hold the old address, and a call inside a capture must not allocate at all (w4a16_reserve sizes it beforehand).
+static int grow_guard(cudaStream_t stream, const char *what) {
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &cs) == cudaSuccess && cs != cudaStreamCaptureStatusNone)
+        return fail(std::string(what) + ": scratch too small inside a stream capture -- call w4a16_reserve(handle, max_tokens) before capturing");
+    return 0;
+}
+static int ensure_stage(Linear *L, int64_t M, cudaStream_t stream) {
     if (M <= L->stage_cap) return 0;
-    cudaFree(L->stage_x); cudaFree(L->stage_y);
+    if (grow_guard(stream, "forward_host")) return 1;
+    if (L->stage_x) L->retired.push_back(L->stage_x);
+    if (L->stage_y) L->retired.push_back(L->stage_y);
     L->stage_x = L->stage_y = nullptr; L->stage_cap = 0;
     W4_CUDA_OK(cudaMalloc(&L->stage_x, (size_t)M * L->d.K * 2));
     W4_CUDA_OK(cudaMalloc(&L->stage_y, (size_t)M * L->d.N * 2));
     L->stage_cap = M;
     return 0;
 }
-static int ensure_gather(Linear *L, int64_t M) {
+static int ensure_gather(Linear *L, int64_t M, cudaStream_t stream) {
     if (!L->perm || L->perm_external || M <= L->x_gather_cap) return 0;
-    cudaFree(L->x_gather);
+    if (grow_guard(stream, "forward (act-order gather)")) return 1;
+    if (L->x_gather) L->retired.push_back(L->x_gather);
     L->x_gather = nullptr; L->x_gather_cap = 0;
     W4_CUDA_OK(cudaMalloc(&L->x_gather, (size_t)M * L->d.K * 2));
     L->x_gather_cap = M;
@@ -227,7 +239,7 @@ static int forward_local(Linear *L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
     if ((reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(y) & 15))
         return fail("forward: x and y must be 16-byte aligned");
     if (L->perm && !L->perm_external) {  // act-order: tiled row i multiplies x[:, perm[i]]
-        if (ensure_gather(L, M)) return 1;
+        if (ensure_gather(L, M, stream)) return 1;
         if (launch_gather_x(x, L->perm, L->x_gather, M, L->d.K, stream)) return 1;
         x = L->x_gather;
     }
@@ -475,7 +487,7 @@ int w4a16_forward_host(w4a16_handle_t h, const void *x_host, void *y_host, int64
     if (M < 1) return fail("forward_host: M must be >= 1");
     DeviceGuard g(L->device);
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-    if (ensure_stage(L, M)) return 1;
+    if (ensure_stage(L, M, s)) return 1;
     W4_CUDA_OK(cudaMemcpyAsync(L->stage_x, x_host, (size_t)M * L->d.K * 2, cudaMemcpyHostToDevice, s));
     if (w4a16_forward_into(h, L->stage_x, L->stage_y, M, stream)) return 1;
     W4_CUDA_OK(cudaMemcpyAsync(y_host, L->stage_y, (size_t)M * out_width(*L) * 2, cudaMemcpyDeviceToHost, s));
@@ -612,7 +624,7 @@ int w4a16_forward_row_fused(w4a16_handle_t h, const void *x_bf16, void *y_bf16, 
     if (!x_bf16 || !y_bf16) return fail("forward_row_fused: null x or y");
     const __nv_bfloat16 *x = reinterpret_cast<const __nv_bfloat16 *>(x_bf16);
     if (L->perm && !L->perm_external) {
-        if (ensure_gather(L, M)) return 1;
+        if (ensure_gather(L, M, s)) return 1;
         if (launch_gather_x(x, L->perm, L->x_gather, M, L->d.K, s)) return 1;
         x = L->x_gather;
     }
@@ -645,8 +657,8 @@ int w4a16_reserve(w4a16_handle_t h, int64_t max_tokens) {
     if (!L) return fail("reserve: null handle");
     if (max_tokens < 1) return fail("reserve: max_tokens must be >= 1");
     DeviceGuard g(L->device);
-    if (ensure_gather(L, max_tokens)) return 1;
-    return ensure_stage(L, max_tokens);
+    if (ensure_gather(L, max_tokens, nullptr)) return 1;
+    return ensure_stage(L, max_tokens, nullptr);
 }
 
 int w4a16_dequant_into(w4a16_handle_t h, void *w_bf16, w4a16_stream_t stream) {

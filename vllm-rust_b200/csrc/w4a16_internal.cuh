@@ -70,6 +70,8 @@ struct Linear {
     int64_t x_gather_cap = 0;
     __nv_bfloat16 *stage_x = nullptr, *stage_y = nullptr;  // forward_host staging
     int64_t stage_cap = 0;
+    std::vector<void *> retired;   // outgrown scratch buffers: freed with the handle, never earlier (a captured CUDA graph
+                                   // may still hold their addresses)
     float *rowpar_f32 = nullptr;  // unused for now (fp32 all-reduce staging)
     int *gv_tab = nullptr;        // decode stream kernel: per-CTA unit range + row-block sharing table (device)
     int gv_grid = 0, gv_max_slots = 0;
@@ -130,7 +132,7 @@ int gemv_debug_read(unsigned long long *out, int64_t words, unsigned long long *
 int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
                    cudaStream_t stream);
 bool prefill_available();
-int splitk_scratch(int device, size_t need, cudaStream_t stream, float **part, int **tickets);
+int splitk_scratch(int device, size_t need, cudaStream_t stream, float **part, int **tickets);   // per (device, stream)
 constexpr int SPLITK_MAX_TILES = 1024;   // tickets per device
 // skinny GEMM (tcgen05, SS mode: tokens = A via TMA, dequantised weights = B in shared memory): 5 <= M <= 128
 bool skinny_usable(const Linear &L, int64_t M);

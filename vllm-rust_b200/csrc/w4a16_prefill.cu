@@ -30,6 +30,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <mutex>
+#include <vector>
 
 #include "w4a16_dequant.cuh"
 #include "w4a16_epilogue.cuh"
@@ -542,33 +543,40 @@ static int launch_pf(const CUtensorMap &map, const PrefillParams &p, int grid, i
 
 int prefill_token_tile(int64_t M) { return M > 128 ? 256 : M > 64 ? 128 : 64; }
 
-// Split-K scratch: one per device, grown on demand outside stream capture (inside a capture that would need a
-// larger one the launch simply runs unsplit).  Calls that split K on one device must be stream-ordered with each
-// other -- the engine drives all forwards from one task (engine/output_pool.rs:40-43).
+// Split-K scratch (fp32 partials + self-resetting tickets): one per (device, STREAM).  Launches on one stream are ordered,
+// so they may share it; launches on different streams get different scratch and cannot race (re-entrant for
+// read-only weights).  Grown on demand outside stream capture -- inside a capture that would need a larger one the launch
+// simply runs unsplit -- and an outgrown block is never freed: a CUDA graph captured earlier may hold its address.
 constexpr int PF_MAX_SPLIT_TILES = SPLITK_MAX_TILES;
-struct SplitScratch { float *part = nullptr; size_t bytes = 0; int *tickets = nullptr; };
-static SplitScratch g_split[64];
+struct SplitScratch { int device; cudaStream_t stream; float *part = nullptr; size_t bytes = 0; int *tickets = nullptr; };
+static std::vector<SplitScratch> g_split;
 static std::mutex g_split_mu;
 int splitk_scratch(int device, size_t need, cudaStream_t stream, float **part, int **tickets) {
-    if (device < 0 || device >= 64) return 1;
     std::lock_guard<std::mutex> lock(g_split_mu);
-    SplitScratch &s = g_split[device];
-    if (s.bytes < need || !s.tickets) {
+    SplitScratch *s = nullptr;
+    for (SplitScratch &c : g_split)
+        if (c.device == device && c.stream == stream) { s = &c; break; }
+    const bool have = s && s->bytes >= need && s->tickets;
+    if (!have) {
         cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
         if (cudaStreamIsCapturing(stream, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) { *part = nullptr; return 0; }
-        if (!s.tickets) {
-            if (cudaMalloc(&s.tickets, PF_MAX_SPLIT_TILES * sizeof(int)) != cudaSuccess) { s.tickets = nullptr; return 1; }
-            cudaMemset(s.tickets, 0, PF_MAX_SPLIT_TILES * sizeof(int));
+        if (!s) {
+            g_split.push_back(SplitScratch{device, stream});
+            s = &g_split.back();
         }
-        if (s.bytes < need) {
-            cudaDeviceSynchronize();   // nobody may still be reading the old scratch
-            cudaFree(s.part); s.part = nullptr; s.bytes = 0;
+        if (!s->tickets) {
+            if (cudaMalloc(&s->tickets, PF_MAX_SPLIT_TILES * sizeof(int)) != cudaSuccess) { s->tickets = nullptr; cudaGetLastError(); return 1; }
+            cudaMemset(s->tickets, 0, PF_MAX_SPLIT_TILES * sizeof(int));
+        }
+        if (s->bytes < need) {
             const size_t want = std::max<size_t>(need, (size_t)32 << 20);
-            if (cudaMalloc(&s.part, want) != cudaSuccess) { cudaGetLastError(); return 1; }
-            s.bytes = want;
+            float *fresh = nullptr;
+            if (cudaMalloc(&fresh, want) != cudaSuccess) { cudaGetLastError(); return 1; }
+            s->part = fresh;          // the outgrown block stays allocated (see above)
+            s->bytes = want;
         }
     }
-    *part = s.part; *tickets = s.tickets;
+    *part = s->part; *tickets = s->tickets;
     return 0;
 }
 
