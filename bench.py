@@ -456,6 +456,41 @@ def tp_check(P, torch, dist, dev, nccl, peers, rank, world):
     return res
 
 
+def prefill_tp(torch, dist, dev, layer, peaks, world, M=4096, reps=5):
+    """BASELINE config 5 at M = 4096: one tensor-parallel Llama-3-70B layer (qkv / gate_up column-parallel, o / down
+    row-parallel ending in the all-reduce of M x 8192 bf16), stream launches, CUDA events, MAX over ranks per shape.
+    TFLOPS are whole-job (the unsharded flops of the shape over the slowest rank's time)."""
+    points, tot_flops, tot_us = [], 0.0, 0.0
+    stream = torch.cuda.Stream(dev)
+    for name, K, N, Kl, Nl, mode, lin in layer:
+        x = torch.randn((M, Kl), device=dev, dtype=torch.float32).mul_(0.05).to(torch.bfloat16)
+        y = torch.empty((M, Nl), device=dev, dtype=torch.bfloat16)
+        with torch.cuda.stream(stream):
+            for _ in range(2):
+                lin.forward_into(x, y)
+            stream.synchronize()
+            dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(reps):
+                lin.forward_into(x, y)
+            e1.record(stream)
+            stream.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) * 1e3 / reps], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        us = float(t.item())
+        flops = 2.0 * M * K * N
+        tot_flops += flops
+        tot_us += us
+        points.append({"shape": f"{name} {K}->{N}", "parallel": mode, "M": M, "us": round(us, 1),
+                       "TFLOPS_aggregate": round(flops / us / 1e6, 1), "TFLOPS_per_gpu": round(flops / us / 1e6 / world, 1),
+                       "frac_measured_bf16_per_gpu": round(flops / us / 1e6 / world / peaks["bf16_tflops"], 4)})
+        del x, y
+    return {"M": M, "tp": world, "layer_TFLOPS_aggregate": round(tot_flops / tot_us / 1e6, 1),
+            "layer_TFLOPS_per_gpu": round(tot_flops / tot_us / 1e6 / world, 1), "points": points,
+            "allreduce": "ncclAllReduce of M x 8192 bf16 after the row-parallel GEMMs (parallel_layers.rs:295-304)"}
+
+
 def same_workload_1gpu(P, torch, dev, shapes, n_layers, args):
     """The TP workload UNSHARDED on this one GPU (7.1 GB of weights for the 16-layer Llama-3-70B step): ms per step."""
     layers = build_layers(P, torch, [sh[:3] for sh in shapes], n_layers, dev)

@@ -239,6 +239,29 @@ int w4a16_forward_row_fused(w4a16_handle_t h, const void *x_bf16, void *y_bf16, 
 typedef struct w4a16_chain *w4a16_chain_t;
 int w4a16_chain_create(w4a16_chain_t *out, int n, const w4a16_handle_t *handles,
                        const void *const *x_bf16, void *const *y_bf16, int64_t M);
+/* Prologue of a linear inside a chain: the memory-bound ops the reference runs between its
+ * linears -- residual add (add_bf16, activations.cu:99-113; half_add_pooled, qwen3_quantized.rs:1062-1068) and
+ * RMSNorm (rms_norm_bf16, layernorm.cu:59-126; input_layernorm / post_attention_layernorm,
+ * qwen3_quantized.rs:1043-1075) -- done by the chain kernel while it stages the linear's activations:
+ *     h      = bf16(f32(x) + f32(residual))     (h = x when there is no residual)
+ *     normed = bf16(f32(h) * rsqrt(mean(f32(h)^2) + eps) * f32(norm_weight))     -> the linear's input
+ * residual is residual_in (caller's memory) if given, else -- with add_running_residual -- the h of the previous
+ * prologue of the same launch, which the kernel keeps in shared memory.  residual_out / normed_out, if given,
+ * receive h / normed ([M, in_features] bf16).  The sum of squares is taken over the ROUNDED h in fp32 like the
+ * reference's separate kernels do; results equal theirs up to the order of that sum (a bf16 ulp on isolated
+ * elements, tests/test_chain_gpu.py).  norm_weight == NULL: the linear has no prologue.  Chains with prologues
+ * need the persistent kernel (creation fails otherwise) and M <= 4. */
+typedef struct w4a16_chain_prologue {
+    const void *norm_weight;  /* bf16 [in_features], device */
+    const void *residual_in;  /* bf16 [M, in_features] or NULL */
+    void *residual_out;       /* bf16 [M, in_features] or NULL */
+    void *normed_out;         /* bf16 [M, in_features] or NULL (parity hook) */
+    float eps;
+    int add_running_residual;
+} w4a16_chain_prologue;
+int w4a16_chain_create_ex(w4a16_chain_t *out, int n, const w4a16_handle_t *handles,
+                          const void *const *x_bf16, void *const *y_bf16, int64_t M,
+                          const w4a16_chain_prologue *prologues /* [n] or NULL */);
 int w4a16_chain_run(w4a16_chain_t chain, w4a16_stream_t stream);
 /* chain_run with HOST buffers at the two ends: H2D copy of the first linear's x ([M, in_features] bf16), the chain,
  * D2H copy of the last linear's y, stream synchronise -- what one decode step moves between host and device (the

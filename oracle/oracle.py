@@ -343,3 +343,20 @@ def make_activations(M: int, K: int, seed: int = 1) -> np.ndarray:
     """x = bf16(N(0,1)) as bf16 bit patterns."""
     rng = np.random.default_rng(seed)
     return np_f32_to_bf16_bits(rng.normal(0, 1, size=(M, K)).astype(np.float32))
+
+
+# ---- residual add + RMSNorm between the linears (SURVEY 8f-4) -------------------------------------------------------
+def np_add_bf16(a_bits, b_bits):
+    """add_bf16 (kernels/activations.cu:99-113): bf16_rn(f32(a) + f32(b)), elementwise."""
+    return np_f32_to_bf16_bits(np_bf16_bits_to_f32(a_bits) + np_bf16_bits_to_f32(b_bits))
+
+
+def np_rms_norm_bf16(x_bits, w_bits, eps):
+    """rms_norm_bf16 (kernels/layernorm.cu:59-126): variance = sum(f32(x)^2) over the row (float64 here: the kernel's
+    fp32 sum order is thread-strided + tree, so the last bit of inv_rms is not pinned), inv_rms = rsqrt(variance / H + eps)
+    in fp32, out = bf16_rn((f32(x) * inv_rms) * f32(w)) with two fp32 multiplies in that order."""
+    x = np_bf16_bits_to_f32(x_bits)
+    w = np_bf16_bits_to_f32(w_bits)
+    var = (x.astype(np.float64) ** 2).sum(axis=-1, keepdims=True)
+    inv = (1.0 / np.sqrt(var / x.shape[-1] + np.float64(np.float32(eps)))).astype(np.float32)
+    return np_f32_to_bf16_bits((x * inv).astype(np.float32) * w)

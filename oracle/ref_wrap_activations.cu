@@ -12,3 +12,10 @@ extern "C" int ref_silu_and_mul_separate_bf16(void *out, const void *gate, const
                                                                           (const __nv_bfloat16 *)up, d);
     return (int)cudaGetLastError();
 }
+
+// add_bf16 (:99-113): the residual add between the linears (half_add_pooled, qwen3_quantized.rs:1062-1068)
+extern "C" int ref_add_bf16(void *out, const void *a, const void *b, int tokens, int hidden, void *stream) {
+    const int block = hidden < 1024 ? hidden : 1024;
+    add_bf16<<<tokens, block, 0, (cudaStream_t)stream>>>((__nv_bfloat16 *)out, (const __nv_bfloat16 *)a, (const __nv_bfloat16 *)b, hidden);
+    return (int)cudaGetLastError();
+}

@@ -218,3 +218,110 @@ def test_chain_errors(product):
     unloaded = product.AwqConfig.int4(128).create_linear(4096, 256, False, DEV)
     with pytest.raises(product.W4A16Error, match="not loaded"):
         product.DecodeChain([(unloaded, x, y)])
+
+
+# ---- prologues: residual add + RMSNorm inside the chain -------------------------------------------------
+import ctypes
+import os
+
+REF_SO = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "libref_kernels.so")
+
+
+def _ref_norm():
+    if not os.path.exists(REF_SO):
+        return None
+    lib = ctypes.CDLL(REF_SO)
+    if not hasattr(lib, "ref_rms_norm_bf16") or not hasattr(lib, "ref_add_bf16"):
+        return None
+    vp, i = ctypes.c_void_p, ctypes.c_int
+    lib.ref_rms_norm_bf16.argtypes = [vp, vp, vp, ctypes.c_float, i, i, vp]
+    lib.ref_add_bf16.argtypes = [vp, vp, vp, i, i, vp]
+    return lib
+
+
+def _ulp_diff(a_bits, b_bits):
+    """distance in bf16 ulps between two bit patterns of the same sign (monotone integer mapping)."""
+    def key(b):
+        b = b.astype(np.int32)
+        return np.where(b & 0x8000, -(b & 0x7FFF), b & 0x7FFF)
+    return np.abs(key(a_bits) - key(b_bits))
+
+
+@pytest.mark.parametrize("M", [1, 2, 4])
+def test_prologue_residual_rmsnorm_like_the_reference_layer(product, M):
+    """One and a half decoder layers as the reference runs them between attention calls (qwen3_quantized.rs:1043-1075):
+         h1 = o_out_prev + residual0 ; gate_up(post_norm(h1)) -> silu*mul -> down ; h2 = down_out + h1 ;
+         qkv(input_norm(h2)).
+    Chain: [gate_up (prologue: residual_in, norm), down, qkv (prologue: running residual, norm)]."""
+    H, I, g, eps = 4096, 4096, 128, 1e-6
+    rng = np.random.default_rng(7 + M)
+    gu = product.AwqConfig.int4(g).create_linear(H, 2 * I, False, DEV)
+    gu.set_epilogue(product.EPILOGUE_SWIGLU)
+    gu_ck = []
+    for half in range(2):
+        qw, qz, sc, _ = O.make_awq_checkpoint(H, I, g, seed=81 + half)
+        gu.load_part(half * I, {"qweight": t_i32(qw), "qzeros": t_i32(qz), "scales": torch.from_numpy(sc)})
+        gu_ck.append(awq_unpacked(qw, qz, sc))
+    down, down_ck = make_linear(product, I, H, g, seed=83)
+    qkv, qkv_ck = make_linear(product, H, 6144, g, seed=84)
+    attn = t_bf16_from_bits(O.make_activations(M, H, seed=90 + M)).to(DEV)           # o_proj output of the attention block
+    res0 = t_bf16_from_bits(O.make_activations(M, H, seed=95 + M)).to(DEV)           # the layer's residual stream
+    w_post = torch.from_numpy(rng.uniform(0.5, 1.5, H).astype(np.float32)).to(torch.bfloat16).to(DEV)
+    w_in = torch.from_numpy(rng.uniform(0.5, 1.5, H).astype(np.float32)).to(torch.bfloat16).to(DEV)
+    z = lambda n: torch.zeros((M, n), dtype=torch.bfloat16, device=DEV)
+    mid, dn, y_qkv = z(I), z(H), z(6144)
+    h1, n1, h2, n2 = z(H), z(H), z(H), z(H)
+    chain = product.DecodeChain(
+        [(gu, attn, mid), (down, mid, dn), (qkv, dn, y_qkv)],
+        prologues=[{"norm_weight": w_post, "eps": eps, "residual_in": res0, "residual_out": h1, "normed_out": n1},
+                   None,
+                   {"norm_weight": w_in, "eps": eps, "add_running_residual": True, "residual_out": h2, "normed_out": n2}])
+    assert chain.kernel().startswith("chain_imma")
+    for rep in range(2):
+        chain.run()
+        torch.cuda.synchronize()
+        # residual adds: elementwise, bit-exact against the restated add_bf16
+        assert (bits_of(h1) == O.np_add_bf16(bits_of(attn), bits_of(res0))).all()
+        assert (bits_of(h2) == O.np_add_bf16(bits_of(dn), bits_of(h1))).all()
+        # norms: against the restated rms_norm_bf16 (float64 sum) within one bf16 ulp, almost everywhere exact
+        for hbuf, nbuf, w in ((h1, n1, w_post), (h2, n2, w_in)):
+            want = O.np_rms_norm_bf16(bits_of(hbuf), bits_of(w), eps)
+            d = _ulp_diff(bits_of(nbuf), want)
+            assert d.max() <= 1 and (d == 0).mean() > 0.99, (d.max(), (d == 0).mean())
+        # and against the reference's own kernels run on this GPU
+        ref = _ref_norm()
+        if ref is not None:
+            r_h, r_n = z(H), z(H)
+            assert ref.ref_add_bf16(r_h.data_ptr(), attn.data_ptr(), res0.data_ptr(), M, H, None) == 0
+            assert ref.ref_rms_norm_bf16(r_n.data_ptr(), r_h.data_ptr(), w_post.data_ptr(), eps, M, H, None) == 0
+            torch.cuda.synchronize()
+            assert (bits_of(r_h) == bits_of(h1)).all()
+            d = _ulp_diff(bits_of(n1), bits_of(r_n))
+            assert d.max() <= 1 and (d == 0).mean() > 0.99, (d.max(), (d == 0).mean())
+        # the linears consume exactly the normalised rows they report
+        gate = oracle_forward(bits_of(n1), *gu_ck[0], g)
+        up = oracle_forward(bits_of(n1), *gu_ck[1], g)
+        want_mid = O.np_bf16_bits_to_f32(O.np_swiglu_bf16(O.np_f32_to_bf16_bits(gate.astype(np.float32)),
+                                                          O.np_f32_to_bf16_bits(up.astype(np.float32)))).astype(np.float64)
+        got_mid = O.np_bf16_bits_to_f32(bits_of(mid)).astype(np.float64)
+        assert np.abs(got_mid - want_mid).max() <= 2e-2 * np.abs(want_mid).max()
+        assert_close_ref(bits_of(dn), oracle_forward(bits_of(mid), *down_ck[:3], g), "down")
+        assert_close_ref(bits_of(y_qkv), oracle_forward(bits_of(n2), *qkv_ck[:3], g), "qkv after input_layernorm")
+        attn.copy_(t_bf16_from_bits(O.make_activations(M, H, seed=190 + M + rep)).to(DEV))   # next run: new inputs
+
+
+def test_prologue_errors(product):
+    lin, _ = make_linear(product, 4096, 256, 128, seed=5)
+    x = torch.zeros((1, 4096), dtype=torch.bfloat16, device=DEV)
+    y = torch.zeros((1, 256), dtype=torch.bfloat16, device=DEV)
+    w = torch.ones(4096, dtype=torch.bfloat16, device=DEV)
+    with pytest.raises(product.W4A16Error, match="no earlier prologue"):
+        product.DecodeChain([(lin, x, y)], prologues=[{"norm_weight": w, "add_running_residual": True}])
+    with pytest.raises(product.W4A16Error, match="norm_weight"):
+        product.DecodeChain([(lin, x, y)], prologues=[{"norm_weight": w[:128].contiguous()}])
+    with pytest.raises(product.W4A16Error, match="one entry"):
+        product.DecodeChain([(lin, x, y)], prologues=[])
+    small, _ = make_linear(product, 2560, 256, 128, seed=6)          # the persistent kernel does not take K = 2560
+    with pytest.raises(product.W4A16Error, match="persistent kernel"):
+        product.DecodeChain([(small, torch.zeros((1, 2560), dtype=torch.bfloat16, device=DEV), y)],
+                            prologues=[{"norm_weight": torch.ones(2560, dtype=torch.bfloat16, device=DEV)}])

@@ -84,6 +84,15 @@ SIGNATURES = {
     "w4a16_chain_debug_stamps": (_i32, [_vp, _vp, _i64]),
 }
 
+class ChainPrologue(ctypes.Structure):
+    """w4a16_chain_prologue (include/w4a16_b200.h)."""
+    _fields_ = [("norm_weight", _vp), ("residual_in", _vp), ("residual_out", _vp), ("normed_out", _vp),
+                ("eps", ctypes.c_float), ("add_running_residual", _i32)]
+
+
+SIGNATURES["w4a16_chain_create_ex"] = (_i32, [ctypes.POINTER(_vp), _i32, ctypes.POINTER(_vp), ctypes.POINTER(_vp),
+                                               ctypes.POINTER(_vp), _i64, ctypes.POINTER(ChainPrologue)])
+
 _lib = None
 
 

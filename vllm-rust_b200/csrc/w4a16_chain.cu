@@ -50,6 +50,12 @@ struct ChainOp {
     // reach, and only then are the pieces read -- and still validated against the sentinel, because the hint orders nothing.
     unsigned long long *arrive_out;        // this linear's own counter (null without a mailbox)
     const unsigned long long *arrive_in;   // the producer's counter (null without mbox_in)
+    // Prologue (w4a16_chain_prologue): h = x (+ residual), residual := h, the linear consumes rms_norm(h) * norm_w.
+    const __nv_bfloat16 *norm_w;           // [K] gamma, or null: no prologue
+    const __nv_bfloat16 *res_in;           // [M, K] residual read from the caller's memory, or null
+    __nv_bfloat16 *res_out, *normed_out;   // [M, K] h / the normalised row, written by CTA 0; may be null
+    float eps;
+    int add_running;                       // h = x + the residual the previous prologue of the chain left in shared memory
 };
 
 struct ChainParams {
@@ -61,6 +67,7 @@ struct ChainParams {
     long long mbox_stride;         // elements between the two parities of every mailbox (run r uses parity r & 1)
     int S, slot_stride;            // ring stages, bytes per stage slot
     int off_xs, off_gtab, off_part, off_ring;
+    int off_res, off_red;          // prologue: running residual bf16 [M][K], reduction scratch (floats); -1 / unused without one
     unsigned long long *dbg;       // [n_ops][grid][CH_DBG_WORDS] %globaltimer stamps, or null
 };
 
@@ -109,12 +116,79 @@ __device__ __forceinline__ bool ch_has_sentinel(const uint4 &v) {
     return hit != 0;
 }
 
+// One 16-byte piece of x: straight from the caller's buffer, or from a mailbox (re-read until no value is the sentinel).
+__device__ __forceinline__ uint4 ch_load_piece(const uint4 *p, bool poll) {
+    if (!poll) return __ldcg(p);
+    uint4 v = ch_ld_relaxed(p);
+    uint32_t spins = 0;
+    while (ch_has_sentinel(v)) {
+        v = ch_ld_relaxed(p);
+        if (++spins > GV_SPIN_LIMIT) __trap();
+    }
+    return v;
+}
+__device__ __forceinline__ float ch_lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float ch_hi(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }
+__device__ __forceinline__ uint32_t ch_pack(float lo, float hi) {
+    const __nv_bfloat162 b = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t *>(&b);
+}
+
+// Prologue, first pass (the reference's add_bf16 + rms_norm_bf16 between the linears of a layer,
+// qwen3_quantized.rs:1043-1075, activations.cu:99-113, layernorm.cu:59-126): h = bf16(f32(x) + f32(residual)) into the
+// shared-memory residual (and the caller's residual_out, by CTA 0), sum of squares of the ROUNDED h per token in fp32,
+// inv_rms[m] = rsqrt(sum / K + eps) into red[0..MR).  The second pass is the ordinary staging reading h from shared
+// memory and scaling it (ch_stage_batch, `norm`).
+template <int MR>
+__device__ __forceinline__ void ch_prologue_pass1(const ChainOp &op, const uint4 *x16, bool poll, uint4 *res, float *red, int tid,
+                                                  int lane, int warp, bool first_cta) {
+    const int ppr = op.K >> 3, total = op.M * ppr;
+    float ss[MR];
+#pragma unroll
+    for (int m = 0; m < MR; ++m) ss[m] = 0.f;
+    const uint4 *rin = reinterpret_cast<const uint4 *>(op.res_in);
+    uint4 *rout = reinterpret_cast<uint4 *>(op.res_out);
+    for (int i = tid; i < total; i += CH_CONS_THREADS) {
+        uint4 v = ch_load_piece(x16 + i, poll);
+        if (rin || op.add_running) {
+            const uint4 r = rin ? __ldcg(rin + i) : res[i];
+            uint32_t *vw = &v.x;
+            const uint32_t *rw = &r.x;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) vw[q] = ch_pack(ch_lo(vw[q]) + ch_lo(rw[q]), ch_hi(vw[q]) + ch_hi(rw[q]));
+        }
+        res[i] = v;
+        if (rout && first_cta) rout[i] = v;
+        float s = 0.f;
+        const uint32_t *vw = &v.x;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) { const float a = ch_lo(vw[q]), b = ch_hi(vw[q]); s = fmaf(a, a, s); s = fmaf(b, b, s); }
+        const int m = MR == 1 ? 0 : (i >= ppr) + (MR > 2 ? (i >= 2 * ppr) + (i >= 3 * ppr) : 0);
+#pragma unroll
+        for (int k = 0; k < MR; ++k) ss[k] += k == m ? s : 0.f;
+    }
+#pragma unroll
+    for (int m = 0; m < MR; ++m) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) ss[m] += __shfl_xor_sync(0xffffffffu, ss[m], o);
+        if (lane == 0) red[MR + warp * MR + m] = ss[m];
+    }
+    ch_bar_consumers();
+    if (tid < MR) {
+        float t = 0.f;
+        for (int w = 0; w < CH_CONS_WARPS; ++w) t += red[MR + w * MR + tid];   // fixed order: deterministic
+        red[tid] = rsqrtf(t / (float)op.K + op.eps);
+    }
+    ch_bar_consumers();
+}
+
 // One batch of NB 16-byte pieces per thread (pieces base + r * 512 + tid).  poll: x is a mailbox (see ChainOp): every
 // piece is re-read until none of its eight values is the sentinel.  The arithmetic of the NB pieces runs side by side
 // (independent dependency chains), the shared-memory stores follow.
-template <int MR, int MPU, int NB>
+template <int MR, int MPU, int NB, bool NORM>
 __device__ __forceinline__ void ch_stage_batch(const uint4 *x16, uint8_t *xs, int2 *gtab, int ppr, int total, int base, int tid, int lane,
-                                               bool poll, unsigned long long *dbg_valid) {
+                                               bool poll, unsigned long long *dbg_valid, const uint4 *norm_w, const float *inv_rms,
+                                               uint4 *normed_out) {
     constexpr int COLS = 2 * MR;
     constexpr int GL = (GV_UNIT_K / MPU) / 8;
     const uint32_t gmask = (GL >= 32 ? 0xFFFFFFFFu : ((1u << GL) - 1u)) << (lane & ~(GL - 1));
@@ -122,9 +196,27 @@ __device__ __forceinline__ void ch_stage_batch(const uint4 *x16, uint8_t *xs, in
 #pragma unroll
     for (int r = 0; r < NB; ++r) {
         const int i = base + r * CH_CONS_THREADS + tid;
-        v[r] = i < total ? (poll ? ch_ld_relaxed(x16 + i) : __ldcg(x16 + i)) : make_uint4(0, 0, 0, 0);
+        if constexpr (NORM) v[r] = i < total ? x16[i] : make_uint4(0, 0, 0, 0);
+        else v[r] = i < total ? (poll ? ch_ld_relaxed(x16 + i) : __ldcg(x16 + i)) : make_uint4(0, 0, 0, 0);
     }
-    if (poll) {
+    if constexpr (NORM) {   // x16 is the shared-memory residual h of the prologue: the linear consumes bf16(h * inv_rms * gamma)
+#pragma unroll
+        for (int r = 0; r < NB; ++r) {
+            const int i = base + r * CH_CONS_THREADS + tid;
+            if (i < total) {
+                const int m = MR == 1 ? 0 : (i >= ppr) + (MR > 2 ? (i >= 2 * ppr) + (i >= 3 * ppr) : 0);
+                const uint4 gw = __ldg(norm_w + (i - m * ppr));
+                const float inv = inv_rms[m];
+                uint32_t *vw = &v[r].x;
+                const uint32_t *g4 = &gw.x;
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    vw[q] = ch_pack(ch_lo(vw[q]) * inv * ch_lo(g4[q]), ch_hi(vw[q]) * inv * ch_hi(g4[q]));
+                if (normed_out) normed_out[i] = v[r];
+            }
+        }
+    }
+    if (!NORM && poll) {
         uint32_t spins = 0;
         for (;;) {
             bool bad[NB], any = false;
@@ -224,17 +316,18 @@ __device__ __forceinline__ void ch_stage_batch(const uint4 *x16, uint8_t *xs, in
 
 // Activation staging of one linear by the 512 consumer threads: the arithmetic of gemv_imma_kernel (per-(group, token)
 // power-of-two scale, two signed-byte planes in B-fragment order, integer group sums, Inf / NaN poison the group).
-template <int MR, int MPU>
+template <int MR, int MPU, bool NORM = false>
 __device__ __forceinline__ void ch_stage_x(const __nv_bfloat16 *x, uint8_t *xs, int2 *gtab, int M, int K, int tid, int lane, bool poll,
-                                           unsigned long long *dbg_valid) {
+                                           unsigned long long *dbg_valid, const uint4 *norm_w = nullptr, const float *inv_rms = nullptr,
+                                           uint4 *normed_out = nullptr) {
     const int ppr = K >> 3, total = M * ppr;
     const uint4 *x16 = reinterpret_cast<const uint4 *>(x);
     int base = 0;
     for (; base + 3 * CH_CONS_THREADS <= total; base += 3 * CH_CONS_THREADS)
-        ch_stage_batch<MR, MPU, 3>(x16, xs, gtab, ppr, total, base, tid, lane, poll, dbg_valid);
+        ch_stage_batch<MR, MPU, 3, NORM>(x16, xs, gtab, ppr, total, base, tid, lane, poll, dbg_valid, norm_w, inv_rms, normed_out);
     const int left = (total - base + CH_CONS_THREADS - 1) / CH_CONS_THREADS;   // 0..2 (warp-uniform)
-    if (left == 2) ch_stage_batch<MR, MPU, 2>(x16, xs, gtab, ppr, total, base, tid, lane, poll, dbg_valid);
-    else if (left == 1) ch_stage_batch<MR, MPU, 1>(x16, xs, gtab, ppr, total, base, tid, lane, poll, dbg_valid);
+    if (left == 2) ch_stage_batch<MR, MPU, 2, NORM>(x16, xs, gtab, ppr, total, base, tid, lane, poll, dbg_valid, norm_w, inv_rms, normed_out);
+    else if (left == 1) ch_stage_batch<MR, MPU, 1, NORM>(x16, xs, gtab, ppr, total, base, tid, lane, poll, dbg_valid, norm_w, inv_rms, normed_out);
 }
 
 // The row blocks of one linear, stage after stage from the ring; every warp takes two units (wi, wi + 16) of every
@@ -336,7 +429,9 @@ __device__ __forceinline__ void ch_row_blocks(const ChainParams &p, const ChainO
     }
 }
 
-template <int MR, int MPU>
+// PRO: the chain has prologues (w4a16_chain_prologue); a separate instantiation, so that chains of plain linears carry
+// none of it (merely compiling the prologue into the one kernel cost the plain step 6 %: 0.826 -> 0.875 ms).
+template <int MR, int MPU, bool PRO>
 __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams p) {
     extern __shared__ __align__(128) uint8_t ch_smem[];
     uint8_t *xs = ch_smem + p.off_xs;
@@ -400,6 +495,8 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
     int slot = 0;                                         // ring position of the CTA's first stage of the current linear
     uint32_t parity = 0u;
     for (int o = 0; o < p.n_ops; ++o) {
+        // (fetching the next descriptor into shared memory while this linear combines was measured: 0.825 -> 0.864 ms per
+        //  step -- the warp that fetches reaches the end-of-linear barrier late)
         const ChainOp op = p.ops[o];
         const int R0 = __ldg(op.rb + cta), n_slots = __ldg(op.rb + cta + 1) - R0;
         if (op.barrier_before) {
@@ -435,8 +532,23 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
             stamp(o, 4);
             ch_bar_consumers();
         }
-        ch_stage_x<MR, MPU>(poll ? reinterpret_cast<const __nv_bfloat16 *>(op.mbox_in + mb_cur) : op.x, xs, gtab, op.M, op.K, tid, lane, poll,
-                            p.dbg ? p.dbg + ((size_t)o * grid + cta) * CH_DBG_WORDS + 5 : nullptr);
+        const __nv_bfloat16 *xsrc = poll ? reinterpret_cast<const __nv_bfloat16 *>(op.mbox_in + mb_cur) : op.x;
+        bool plain = true;
+        if constexpr (PRO) {
+          if (op.norm_w) {
+            plain = false;
+            uint4 *res = reinterpret_cast<uint4 *>(ch_smem + p.off_res);
+            float *red = reinterpret_cast<float *>(ch_smem + p.off_red);
+            ch_prologue_pass1<MR>(op, reinterpret_cast<const uint4 *>(xsrc), poll, res, red, tid, lane, warp, cta == 0);
+            ch_stage_x<MR, MPU, true>(reinterpret_cast<const __nv_bfloat16 *>(res), xs, gtab, op.M, op.K, tid, lane, false, nullptr,
+                                reinterpret_cast<const uint4 *>(op.norm_w), red,
+                                cta == 0 ? reinterpret_cast<uint4 *>(op.normed_out) : nullptr);
+          }
+        }
+        if (plain) {
+            ch_stage_x<MR, MPU>(xsrc, xs, gtab, op.M, op.K, tid, lane, poll,
+                                p.dbg ? p.dbg + ((size_t)o * grid + cta) * CH_DBG_WORDS + 5 : nullptr);
+        }
         if (poll) {
             // put the sentinel back into the OTHER parity of what was just read: its last readers finished a run ago, its
             // next writers run a run from now (they cannot start before every CTA has passed this point)
@@ -495,6 +607,8 @@ struct Chain {
     std::vector<Linear *> lin;
     std::vector<const __nv_bfloat16 *> x;
     std::vector<__nv_bfloat16 *> y;
+    std::vector<w4a16_chain_prologue> pro;   // per linear; norm_weight == null: none
+    bool has_prologue = false;
     bool persistent = false;       // the chain kernel takes it; otherwise the linears are launched one by one
     std::string why_not;
     ChainOp *d_ops = nullptr;
@@ -509,11 +623,11 @@ struct Chain {
     int MR = 1, mpu = 1, smem = 0, grid = 0;
 };
 
-template <int MR, int MPU>
+template <int MR, int MPU, bool PRO>
 static int chain_launch_t(const Chain &c, cudaStream_t stream, bool pdl) {
     static bool attr_set[64] = {};
     if (c.device >= 0 && c.device < 64 && !attr_set[c.device]) {
-        W4_CUDA_OK(cudaFuncSetAttribute(chain_kernel<MR, MPU>, cudaFuncAttributeMaxDynamicSharedMemorySize, CH_SMEM_MAX));
+        W4_CUDA_OK(cudaFuncSetAttribute(chain_kernel<MR, MPU, PRO>, cudaFuncAttributeMaxDynamicSharedMemorySize, CH_SMEM_MAX));
         attr_set[c.device] = true;
     }
     cudaLaunchConfig_t cfg{};
@@ -526,7 +640,7 @@ static int chain_launch_t(const Chain &c, cudaStream_t stream, bool pdl) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    W4_CUDA_OK(cudaLaunchKernelEx(&cfg, chain_kernel<MR, MPU>, c.prm));
+    W4_CUDA_OK(cudaLaunchKernelEx(&cfg, chain_kernel<MR, MPU, PRO>, c.prm));
     count_launch();
     return 0;
 }
@@ -535,9 +649,14 @@ static int chain_launch(const Chain &c, cudaStream_t stream) {
     const bool pdl = gv_env_int("W4A16_NO_PDL", 0) == 0;
 #define W4_CH(MR_)                                                       \
     do {                                                                 \
-        if (c.mpu == 1) return chain_launch_t<MR_, 1>(c, stream, pdl);   \
-        if (c.mpu == 2) return chain_launch_t<MR_, 2>(c, stream, pdl);   \
-        return chain_launch_t<MR_, 4>(c, stream, pdl);                   \
+        if (c.has_prologue) {                                            \
+            if (c.mpu == 1) return chain_launch_t<MR_, 1, true>(c, stream, pdl);   \
+            if (c.mpu == 2) return chain_launch_t<MR_, 2, true>(c, stream, pdl);   \
+            return chain_launch_t<MR_, 4, true>(c, stream, pdl);         \
+        }                                                                \
+        if (c.mpu == 1) return chain_launch_t<MR_, 1, false>(c, stream, pdl);   \
+        if (c.mpu == 2) return chain_launch_t<MR_, 2, false>(c, stream, pdl);   \
+        return chain_launch_t<MR_, 4, false>(c, stream, pdl);            \
     } while (0)
     switch (c.MR) {
         case 1: W4_CH(1);
@@ -556,7 +675,7 @@ static void chain_free(Chain *c) {
 // Decides whether the persistent kernel takes the chain and builds its device tables.
 static int chain_plan(Chain *c) {
     c->persistent = false;
-    if (gv_env_int("W4A16_NO_CHAIN_KERNEL", 0)) { c->why_not = "disabled by W4A16_NO_CHAIN_KERNEL"; return 0; }
+    if (gv_env_int("W4A16_NO_CHAIN_KERNEL", 0) && !c->has_prologue) { c->why_not = "disabled by W4A16_NO_CHAIN_KERNEL"; return 0; }
     if (c->M > 4) { c->why_not = "more than 4 tokens"; return 0; }
     if (c->n > CH_MAX_OPS) { c->why_not = "too many linears"; return 0; }
     DeviceScratch *ds = nullptr;
@@ -583,6 +702,15 @@ static int chain_plan(Chain *c) {
     off = (off + 15) & ~(int64_t)15;
     const int off_part = (int)off; off += max_slots * CH_CONS_WARPS * 8 * c->MR * 8;
     off = (off + 127) & ~(int64_t)127;
+    int off_res = -1, off_red = -1;
+    if (c->has_prologue) {
+        int64_t proK = 0;
+        for (int i = 0; i < c->n; ++i)
+            if (c->pro[i].norm_weight) proK = std::max(proK, c->lin[i]->d.K);
+        off_res = (int)off; off += c->M * proK * 2;
+        off_red = (int)off; off += (CH_CONS_WARPS + 1) * 4 * sizeof(float);
+        off = (off + 127) & ~(int64_t)127;
+    }
     const int64_t stride = 32 * (GV_UNIT_BYTES + c->mpu * META_BYTES);
     int64_t S = (CH_SMEM_MAX - off) / stride;
     if (S < 3) { c->why_not = "activations leave no room for a ring of 3 stages"; return 0; }
@@ -618,6 +746,28 @@ static int chain_plan(Chain *c) {
                 !(lo_y(i) == lo_y(j) && c->lin[i]->d.N == c->lin[j]->d.N && width(i) == width(j)))
                 barrier[i] = 1;                      // same rows from the same CTA in program order would be fine
             if (overlap(lo_y(i), hi_y(i), lo_x(j), hi_x(j)) && dep[j] < 0) barrier[i] = 1;   // j reads the caller's memory
+        }
+        // prologue buffers: residual_in is read from the caller's memory, residual_out / normed_out are written by CTA 0
+        if (c->has_prologue && !barrier[i]) {
+            const uintptr_t hb = (uintptr_t)(M * c->lin[i]->d.K * 2);
+            auto rng = [&](const void *q, uintptr_t &a, uintptr_t &b) { a = reinterpret_cast<uintptr_t>(q); b = a + (q ? hb : 0); };
+            uintptr_t ri0, ri1, ro0, ro1, no0, no1;
+            rng(c->pro[i].norm_weight ? c->pro[i].residual_in : nullptr, ri0, ri1);
+            rng(c->pro[i].norm_weight ? c->pro[i].residual_out : nullptr, ro0, ro1);
+            rng(c->pro[i].norm_weight ? c->pro[i].normed_out : nullptr, no0, no1);
+            for (int j = 0; j < i && !barrier[i]; ++j) {
+                const uintptr_t hj = (uintptr_t)(M * c->lin[j]->d.K * 2);
+                const void *wj[2] = {c->pro[j].norm_weight ? c->pro[j].residual_out : nullptr, c->pro[j].norm_weight ? c->pro[j].normed_out : nullptr};
+                for (const void *w : wj) {
+                    if (!w) continue;
+                    const uintptr_t w0 = reinterpret_cast<uintptr_t>(w), w1 = w0 + hj;
+                    if (overlap(lo_x(i), hi_x(i), w0, w1) || (ri1 > ri0 && overlap(ri0, ri1, w0, w1))) barrier[i] = 1;   // reads what CTA 0 wrote
+                }
+                if (ri1 > ri0 && overlap(ri0, ri1, lo_y(j), hi_y(j))) barrier[i] = 1;
+                if ((ro1 > ro0 && overlap(ro0, ro1, lo_x(j), hi_x(j)) && dep[j] < 0) ||
+                    (no1 > no0 && overlap(no0, no1, lo_x(j), hi_x(j)) && dep[j] < 0))
+                    barrier[i] = 1;
+            }
         }
         if (barrier[i]) dep[i] = -1;                 // behind a barrier the caller's buffer itself is read
     }
@@ -660,6 +810,13 @@ static int chain_plan(Chain *c) {
         o.mbox_in = dep[i] >= 0 ? c->d_mbox + mbox_off[dep[i]] + (lo_x(i) - lo_y(dep[i])) / 2 : nullptr;
         o.arrive_out = mbox_off[i] >= 0 ? c->d_arrive + (size_t)i * 16 : nullptr;
         o.arrive_in = dep[i] >= 0 ? c->d_arrive + (size_t)dep[i] * 16 : nullptr;
+        const w4a16_chain_prologue &pr = c->pro[i];
+        o.norm_w = reinterpret_cast<const __nv_bfloat16 *>(pr.norm_weight);
+        o.res_in = pr.norm_weight ? reinterpret_cast<const __nv_bfloat16 *>(pr.residual_in) : nullptr;
+        o.res_out = pr.norm_weight ? reinterpret_cast<__nv_bfloat16 *>(pr.residual_out) : nullptr;
+        o.normed_out = pr.norm_weight ? reinterpret_cast<__nv_bfloat16 *>(pr.normed_out) : nullptr;
+        o.eps = pr.eps;
+        o.add_running = pr.norm_weight && !pr.residual_in && pr.add_running_residual;
     }
     W4_CUDA_OK(cudaMemcpy(c->d_rb, rb.data(), rb.size() * sizeof(int), cudaMemcpyHostToDevice));
     W4_CUDA_OK(cudaMalloc(&c->d_ops, ops.size() * sizeof(ChainOp)));
@@ -679,6 +836,7 @@ static int chain_plan(Chain *c) {
     p.n_barriers = c->n_barriers; p.mbox_stride = mbox_total;
     p.S = (int)S; p.slot_stride = (int)stride;
     p.off_xs = off_xs; p.off_gtab = off_gtab; p.off_part = off_part; p.off_ring = off_ring;
+    p.off_res = off_res; p.off_red = off_red;
     p.dbg = c->d_dbg;
     c->persistent = true;
     return 0;
@@ -693,6 +851,11 @@ using namespace w4;
 extern "C" {
 
 int w4a16_chain_create(w4a16_chain_t *out, int n, const w4a16_handle_t *handles, const void *const *x, void *const *y, int64_t M) {
+    return w4a16_chain_create_ex(out, n, handles, x, y, M, nullptr);
+}
+
+int w4a16_chain_create_ex(w4a16_chain_t *out, int n, const w4a16_handle_t *handles, const void *const *x, void *const *y, int64_t M,
+                          const w4a16_chain_prologue *prologues) {
     if (!out) return fail("chain_create: null out");
     *out = nullptr;
     if (n < 1 || !handles || !x || !y) return fail("chain_create: need at least one linear and its x / y pointers");
@@ -713,6 +876,34 @@ int w4a16_chain_create(w4a16_chain_t *out, int n, const w4a16_handle_t *handles,
         c->lin.push_back(L);
         c->x.push_back(reinterpret_cast<const __nv_bfloat16 *>(x[i]));
         c->y.push_back(reinterpret_cast<__nv_bfloat16 *>(y[i]));
+        w4a16_chain_prologue pr{};
+        if (prologues) pr = prologues[i];
+        if (pr.norm_weight) {
+            c->has_prologue = true;
+            const void *ptrs[4] = {pr.norm_weight, pr.residual_in, pr.residual_out, pr.normed_out};
+            for (const void *q : ptrs)
+                if (reinterpret_cast<uintptr_t>(q) & 15) { chain_free(c); return fail("chain_create: prologue buffers must be 16-byte aligned"); }
+            if (!(pr.eps >= 0.f)) { chain_free(c); return fail("chain_create: prologue eps must be >= 0"); }
+            if (L->perm && !L->perm_external) { chain_free(c); return fail("chain_create: a prologue on an act-order linear is not supported"); }
+        }
+        c->pro.push_back(pr);
+    }
+    if (c->has_prologue) {
+        // the running residual lives in shared memory between the prologues of one launch: it needs one width and a first
+        // prologue that does not ask for it
+        int64_t k_run = -1;
+        bool have_running = false;
+        for (int i = 0; i < n; ++i) {
+            const w4a16_chain_prologue &pr = c->pro[i];
+            if (!pr.norm_weight) continue;
+            if (!pr.residual_in && pr.add_running_residual) {
+                if (!have_running) { chain_free(c); return fail("chain_create: add_running_residual at position " + std::to_string(i) + " but no earlier prologue in this chain"); }
+                if (c->lin[i]->d.K != k_run) { chain_free(c); return fail("chain_create: the running residual changes width at position " + std::to_string(i)); }
+            }
+            have_running = true;
+            k_run = c->lin[i]->d.K;
+        }
+        if (M > 4) { chain_free(c); return fail("chain_create: prologues need M <= 4 (the persistent kernel)"); }
     }
     int prev = 0;
     cudaGetDevice(&prev);
@@ -720,6 +911,11 @@ int w4a16_chain_create(w4a16_chain_t *out, int n, const w4a16_handle_t *handles,
     const int rc = chain_plan(c);
     cudaSetDevice(prev);
     if (rc) { chain_free(c); return 1; }
+    if (c->has_prologue && !c->persistent) {
+        const std::string why = c->why_not;
+        chain_free(c);
+        return fail("chain_create: prologues need the persistent kernel, which does not take this chain (" + why + ")");
+    }
     *out = reinterpret_cast<w4a16_chain_t>(c);
     return 0;
 }

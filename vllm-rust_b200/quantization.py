@@ -729,7 +729,10 @@ class DecodeChain:
     what linear i wrote.  Where the shapes allow it run() is ONE persistent launch (`kernel()` == "chain_imma"),
     otherwise the chain calls the linears one by one."""
 
-    def __init__(self, steps: Sequence):
+    def __init__(self, steps: Sequence, prologues: Optional[Sequence] = None):
+        """prologues: per step None or a dict {norm_weight, eps, residual_in, residual_out, normed_out,
+        add_running_residual}: residual add + RMSNorm done by the chain kernel while it stages that linear's input
+        (input_layernorm / post_attention_layernorm + the residual adds of qwen3_quantized.rs:1043-1075)."""
         steps = list(steps)
         if not steps:
             raise W4A16Error("DecodeChain: need at least one (linear, x, y) step")
@@ -749,7 +752,30 @@ class DecodeChain:
             hs[i], xs[i], ys[i] = inner._h, x.data_ptr(), y.data_ptr()
         self._device = steps[0][1].device
         self._c = ctypes.c_void_p()
-        check(lib().w4a16_chain_create(ctypes.byref(self._c), n, hs, xs, ys, m))
+        pro = None
+        if prologues is not None:
+            from ._lib import ChainPrologue
+            if len(prologues) != n:
+                raise W4A16Error("DecodeChain: prologues must have one entry (or None) per step")
+            pro = (ChainPrologue * n)()
+            self._keep_pro = prologues
+            for i, pr in enumerate(prologues):
+                if pr is None:
+                    continue
+                k = steps[i][1].shape[1]
+                w = pr["norm_weight"]
+                if w.dtype != torch.bfloat16 or w.numel() != k or not w.is_cuda or not w.is_contiguous():
+                    raise W4A16Error(f"DecodeChain: norm_weight of step {i} must be a contiguous CUDA bf16 tensor [{k}]")
+                pro[i].norm_weight = w.data_ptr()
+                for key in ("residual_in", "residual_out", "normed_out"):
+                    t = pr.get(key)
+                    if t is not None:
+                        if t.dtype != torch.bfloat16 or tuple(t.shape) != (m, k) or not t.is_cuda or not t.is_contiguous():
+                            raise W4A16Error(f"DecodeChain: {key} of step {i} must be a contiguous CUDA bf16 tensor [{m}, {k}]")
+                        setattr(pro[i], key, t.data_ptr())
+                pro[i].eps = float(pr.get("eps", 1e-6))
+                pro[i].add_running_residual = int(bool(pr.get("add_running_residual", False)))
+        check(lib().w4a16_chain_create_ex(ctypes.byref(self._c), n, hs, xs, ys, m, pro))
         self._n, self._m = n, m
 
     def __del__(self):
