@@ -96,6 +96,26 @@ __device__ __forceinline__ int ch_redux_add(int v, uint32_t mask) {
     asm volatile("redux.sync.add.s32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(mask));
     return r;
 }
+// Group = GL aligned lanes.  redux.sync with a partial member mask goes through a slow divergent path (the uniform
+// datapath reduces whole warps), so 16-lane groups use two FULL-warp reductions over inputs masked to one half each.
+template <int GL>
+__device__ __forceinline__ uint32_t ch_group_max(uint32_t v, uint32_t gmask, int lane) {
+    if constexpr (GL == 16) {
+        const uint32_t lo = ch_redux_max(lane < 16 ? v : 0u, 0xFFFFFFFFu), hi = ch_redux_max(lane < 16 ? 0u : v, 0xFFFFFFFFu);
+        return lane < 16 ? lo : hi;
+    } else {
+        return ch_redux_max(v, gmask);
+    }
+}
+template <int GL>
+__device__ __forceinline__ int ch_group_add(int v, uint32_t gmask, int lane) {
+    if constexpr (GL == 16) {
+        const int lo = ch_redux_add(lane < 16 ? v : 0, 0xFFFFFFFFu), hi = ch_redux_add(lane < 16 ? 0 : v, 0xFFFFFFFFu);
+        return lane < 16 ? lo : hi;
+    } else {
+        return ch_redux_add(v, gmask);
+    }
+}
 // a value can never be the sentinel: 0xFFFF (a NaN) is stored as the canonical NaN 0x7FFF
 __device__ __forceinline__ void ch_mbox_store(unsigned short *p, __nv_bfloat16 v) {
     unsigned short b = __bfloat16_as_ushort(v);
@@ -258,7 +278,7 @@ __device__ __forceinline__ void ch_stage_batch(const uint4 *x16, uint8_t *xs, in
         mxA[r] = mx;
     }
 #pragma unroll
-    for (int r = 0; r < NB; ++r) mxA[r] = ch_redux_max(mxA[r], gmask);   // over the GL lanes that hold the group
+    for (int r = 0; r < NB; ++r) mxA[r] = ch_group_max<GL>(mxA[r], gmask, lane);   // over the GL lanes that hold the group
 #pragma unroll
     for (int r = 0; r < NB; ++r) {
         const uint32_t w4[4] = {v[r].x, v[r].y, v[r].z, v[r].w};
@@ -277,7 +297,7 @@ __device__ __forceinline__ void ch_stage_batch(const uint4 *x16, uint8_t *xs, in
         sumA[r] = sum;
     }
 #pragma unroll
-    for (int r = 0; r < NB; ++r) sumA[r] = ch_redux_add(sumA[r], gmask);
+    for (int r = 0; r < NB; ++r) sumA[r] = ch_group_add<GL>(sumA[r], gmask, lane);
 #pragma unroll
     for (int r = 0; r < NB; ++r) {
         const int i = base + r * CH_CONS_THREADS + tid;
