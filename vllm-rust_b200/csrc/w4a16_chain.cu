@@ -26,7 +26,8 @@ namespace w4 {
 constexpr int CH_CONS_WARPS = 16;                     // consumer warps: 2 units each = one 32-unit stage per iteration
 constexpr int CH_UPW = 2;
 constexpr int CH_CONS_THREADS = CH_CONS_WARPS * 32;   // 512
-constexpr int CH_THREADS = CH_CONS_THREADS + 32;      // + the producer warp
+constexpr int CH_THREADS = CH_CONS_THREADS + 128;     // + the producer warp group (one working warp; setmaxnreg moves whole groups of 4)
+constexpr int CH_REGS_PRODUCER = 24, CH_REGS_CONSUMER = 112;   // after the role split (launched with 96 each)
 constexpr int CH_MAX_STAGES = 8;
 constexpr int CH_SMEM_MAX = 227 * 1024;
 constexpr int CH_MAX_OPS = 4096;
@@ -449,6 +450,117 @@ __device__ __forceinline__ void ch_row_blocks(const ChainParams &p, const ChainO
     }
 }
 
+// K = 4096, group size 128 (one stage = one row block; the warp meets the same two k-units in every stage, so its B
+// fragments live in registers): NS stages per call.  Two stages side by side double the independent IMMA chains and the
+// loads in flight per warp and halve the barrier round trips -- a stage passes through the CTA in ~0.5 us when taken one
+// by one, which is what a linear whose weights already sit in the ring (qkv, o, the head of gate_up) is bound by.
+template <int MR, int NS>
+__device__ __forceinline__ void ch_hoist_stages(const ChainParams &p, int wi, int lane, uint32_t ring, uint32_t bar_full, uint32_t bar_empty,
+                                                uint32_t gt_l, const uint32_t (&bq)[CH_UPW][4][2], float2 *part, int s, int &slot,
+                                                uint32_t &parity) {
+    constexpr uint32_t STAGE_W = 32 * GV_UNIT_BYTES;
+    constexpr uint32_t GU = MR * 8;
+    const int g = lane >> 2, t = lane & 3;
+    const uint32_t offW = (uint32_t)(wi * GV_UNIT_BYTES + lane * 16);
+    const uint32_t offM = STAGE_W + (uint32_t)(wi * META_BYTES);
+    uint32_t w[NS][CH_UPW][8], s2[NS][CH_UPW], zb[NS][CH_UPW];
+#pragma unroll
+    for (int n = 0; n < NS; ++n) {
+        const uint32_t sb = ring + (uint32_t)slot * (uint32_t)p.slot_stride;
+        if (n == 0) gv_mbar_wait(bar_full + 8 * slot, parity);      // the caller has seen the later stages complete
+#pragma unroll
+        for (int j = 0; j < CH_UPW; ++j) {
+            const uint32_t sw = sb + offW + (uint32_t)(CH_CONS_WARPS * j * GV_UNIT_BYTES), sm = sb + offM + (uint32_t)(CH_CONS_WARPS * j * META_BYTES);
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[n][j][0]), "=r"(w[n][j][1]), "=r"(w[n][j][2]), "=r"(w[n][j][3]) : "r"(sw));
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4+512];" : "=r"(w[n][j][4]), "=r"(w[n][j][5]), "=r"(w[n][j][6]), "=r"(w[n][j][7]) : "r"(sw));
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(s2[n][j]) : "r"(sm + 4 * g));
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(zb[n][j]) : "r"(sm + META_ZERO_OFF + g));
+        }
+        __syncwarp();
+        if (lane == 0) ch_mbar_arrive(bar_empty + 8 * slot);
+        if (++slot == p.S) { slot = 0; parity ^= 1u; }
+    }
+    int acc[NS][CH_UPW][4];
+#pragma unroll
+    for (int n = 0; n < NS; ++n)
+#pragma unroll
+        for (int j = 0; j < CH_UPW; ++j)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[n][j][q] = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int n = 0; n < NS; ++n)
+#pragma unroll
+            for (int j = 0; j < CH_UPW; ++j) {
+                const uint32_t wa = w[n][j][2 * i], wb = w[n][j][2 * i + 1];
+                ch_imma(acc[n][j], wa & 0x0F0F0F0Fu, wa, wb & 0x0F0F0F0Fu, wb, bq[j][i][0], bq[j][i][1]);
+            }
+    int X[CH_UPW];
+    float e2[CH_UPW];
+#pragma unroll
+    for (int j = 0; j < CH_UPW; ++j) {
+        int e2b;
+        asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(X[j]), "=r"(e2b) : "r"(gt_l + (uint32_t)(wi + CH_CONS_WARPS * j) * GU));
+        e2[j] = __int_as_float(e2b);
+    }
+#pragma unroll
+    for (int n = 0; n < NS; ++n) {
+        float y0 = 0.f, y1 = 0.f;
+#pragma unroll
+        for (int j = 0; j < CH_UPW; ++j) {
+            const int tg = acc[n][j][0] * 128 + acc[n][j][1];
+            const int tr = acc[n][j][2] * 128 + acc[n][j][3];
+            const int ug = tg - (int)(zb[n][j] & 0x0Fu) * X[j];
+            const int ug8 = tr - tg - (int)(zb[n][j] & 0xF0u) * X[j];          // 16 * (row g+8 - z8 * X)
+            const float slo = __uint_as_float(s2[n][j] << 16) * e2[j];
+            const float shi = __uint_as_float(s2[n][j] & 0xFFFF0000u) * (e2[j] * 0.0625f);
+            y0 = fmaf(slo, (float)ug, y0);
+            y1 = fmaf(shi, (float)ug8, y1);
+        }
+        if (t < MR) part[(((size_t)(s + n) * CH_CONS_WARPS + wi) * 8 + g) * MR + t] = make_float2(y0, y1);
+    }
+}
+
+template <int MR>
+__device__ __forceinline__ void ch_row_blocks_hoist(const ChainParams &p, int n_slots, int wi, int lane, uint32_t ring, uint32_t bar_full,
+                                                    uint32_t bar_empty, uint32_t xs_u32, uint32_t gtab_u32, float2 *part, int &slot,
+                                                    uint32_t &parity) {
+    constexpr int COLS = 2 * MR;
+    constexpr uint32_t XU = 4 * 4 * COLS * 8;
+    const int g = lane >> 2, t = lane & 3;
+    const uint32_t xs_l = xs_u32 + (uint32_t)((t * COLS + (g & (COLS - 1))) * 8);
+    const uint32_t gt_l = gtab_u32 + (uint32_t)((t & (MR - 1)) * 8);
+    const bool b_lane = COLS >= 8 || g < COLS;
+    uint32_t bq[CH_UPW][4][2];
+#pragma unroll
+    for (int j = 0; j < CH_UPW; ++j) {
+        const uint32_t xk = xs_l + (uint32_t)(wi + CH_CONS_WARPS * j) * XU;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            bq[j][i][0] = 0; bq[j][i][1] = 0;
+            if (b_lane) asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(bq[j][i][0]), "=r"(bq[j][i][1]) : "r"(xk + (uint32_t)(i * 4 * COLS * 8)));
+        }
+    }
+    int s = 0;
+    while (s < n_slots) {
+        bool two = false;
+        if (s + 1 < n_slots) {               // is the stage after this one in the ring already?  (warp-uniform answer)
+            int nslot = slot + 1;
+            uint32_t npar = parity;
+            if (nslot == p.S) { nslot = 0; npar ^= 1u; }
+            two = __all_sync(0xffffffffu, gv_mbar_try_wait(bar_full + 8 * nslot, npar) != 0);
+        }
+        if (two) {
+            ch_hoist_stages<MR, 2>(p, wi, lane, ring, bar_full, bar_empty, gt_l, bq, part, s, slot, parity);
+            s += 2;
+        } else {
+            ch_hoist_stages<MR, 1>(p, wi, lane, ring, bar_full, bar_empty, gt_l, bq, part, s, slot, parity);
+            s += 1;
+        }
+    }
+}
+
 // PRO: the chain has prologues (w4a16_chain_prologue); a separate instantiation, so that chains of plain linears carry
 // none of it (merely compiling the prologue into the one kernel cost the plain step 6 %: 0.826 -> 0.875 ms).
 template <int MR, int MPU, bool PRO>
@@ -470,7 +582,9 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
     }
     __syncthreads();
 
-    if (warp == CH_CONS_WARPS) {
+    if (warp >= CH_CONS_WARPS) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(CH_REGS_PRODUCER));
+        if (warp > CH_CONS_WARPS) return;      // the group's other three warps only hand their registers back
         // ---- producer: the CTA's share of every linear's W4T stream, in chain order, as fast as slots come free.
         //      Weights are immutable, so this neither waits for the previous kernel nor for the grid barriers. ----
         if (lane == 0) {
@@ -499,6 +613,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
     }
 
     // ---- consumers ----
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(CH_REGS_CONSUMER));
     const int wi = warp;
     auto stamp = [&](int o, int i) {
         if (p.dbg && tid == 0) {
@@ -580,7 +695,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
         ch_bar_consumers();
         stamp(o, 1);
         if (MPU == 1 && op.hoist)
-            ch_row_blocks<MR, MPU, MPU == 1>(p, op, n_slots, wi, lane, ring, bar_full, bar_empty, gv_smem_u32(xs), gv_smem_u32(gtab), part, slot, parity);
+            ch_row_blocks_hoist<MR>(p, n_slots, wi, lane, ring, bar_full, bar_empty, gv_smem_u32(xs), gv_smem_u32(gtab), part, slot, parity);
         else
             ch_row_blocks<MR, MPU, false>(p, op, n_slots, wi, lane, ring, bar_full, bar_empty, gv_smem_u32(xs), gv_smem_u32(gtab), part, slot, parity);
         ch_bar_consumers();
