@@ -1,4 +1,2 @@
 #!/bin/bash
-timeout 900 python -m pytest tests/test_chain_gpu.py -x -q 2>&1 | tail -2
-timeout 300 python tools/decode_ab.py --api chain --chain --cfg "" --cfg "A=1" 2>&1 | grep "\[ab\] "
-timeout 300 python tools/chain_timeline.py 2>&1 | grep -A8 "^-- qkv\|^-- gate_up\|whole"
+timeout 500 python tools/decode_ab.py --api chain --chain --cfg "W4A16_CHAIN_L2PF=6" --cfg "W4A16_CHAIN_L2PF=8" --cfg "W4A16_CHAIN_L2PF=12" --cfg "W4A16_CHAIN_L2PF=16" --cfg "W4A16_CHAIN_L2PF=24" --cfg "W4A16_CHAIN_L2PF=48" 2>&1 | grep "\[ab\] W"

@@ -67,6 +67,7 @@ struct ChainParams {
     int n_barriers;                // grid barriers per run
     long long mbox_stride;         // elements between the two parities of every mailbox (run r uses parity r & 1)
     int S, slot_stride;            // ring stages, bytes per stage slot
+    int l2pf;                      // stages the L2 prefetcher runs ahead of the ring's producer (0: off)
     int off_xs, off_gtab, off_part, off_ring;
     int off_res, off_red;          // prologue: running residual bf16 [M][K], reduction scratch (floats); -1 / unused without one
     unsigned long long *dbg;       // [n_ops][grid][CH_DBG_WORDS] %globaltimer stamps, or null
@@ -577,6 +578,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
 
     if (tid == 0) {
         for (int s = 0; s < p.S; ++s) { gv_mbar_init(bar_full + 8 * s, 1); gv_mbar_init(bar_empty + 8 * s, CH_CONS_WARPS); }
+        *reinterpret_cast<volatile int *>(ch_smem + 2 * 8 * CH_MAX_STAGES) = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -584,11 +586,40 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
 
     if (warp >= CH_CONS_WARPS) {
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(CH_REGS_PRODUCER));
-        if (warp > CH_CONS_WARPS) return;      // the group's other three warps only hand their registers back
+        volatile int *issued = reinterpret_cast<volatile int *>(ch_smem + 2 * 8 * CH_MAX_STAGES);   // stages the producer has issued
+        if (warp == CH_CONS_WARPS + 1 && lane == 0 && p.l2pf > 0) {
+            // ---- L2 prefetcher: the ring is all the shared memory there is (25 MB chip-wide), and while the short linears
+            //      (qkv, o) sit in their hand-overs it is full and HBM idles.  This warp asks L2 for the `l2pf` stages beyond
+            //      the one the producer issued last, paced by the producer's progress so that only a few MB are outstanding
+            //      chip-wide (one-shot prefetches of tens of MB are dropped, profiles/r2_l2_prefetch_negative.md). ----
+            int q = 0;
+            for (int o = 0; o < p.n_ops; ++o) {
+                const ChainOp *op = p.ops + o;
+                const int R0 = __ldg(op->rb + cta), R1 = __ldg(op->rb + cta + 1);
+                const int nst = (R1 - R0) * op->spr;
+                const size_t unit0 = (size_t)R0 * op->UPR;
+                const uint8_t *w = op->qw + unit0 * GV_UNIT_BYTES;
+                const uint8_t *m = op->meta + unit0 * (MPU * META_BYTES);
+                for (int s = 0; s < nst; ++s, ++q) {
+                    uint32_t spins = 0;
+                    while (q >= *issued + p.l2pf) {
+                        __nanosleep(64);
+                        if (++spins > GV_SPIN_LIMIT) __trap();
+                    }
+                    if (q >= *issued) {        // still ahead of the ring: otherwise the real copy is already on its way
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(w), "r"(STAGE_W) : "memory");
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(m), "r"(STAGE_M) : "memory");
+                    }
+                    w += STAGE_W; m += STAGE_M;
+                }
+            }
+            return;
+        }
+        if (warp > CH_CONS_WARPS) return;      // the group's other warps only hand their registers back
         // ---- producer: the CTA's share of every linear's W4T stream, in chain order, as fast as slots come free.
         //      Weights are immutable, so this neither waits for the previous kernel nor for the grid barriers. ----
         if (lane == 0) {
-            int slot = 0;
+            int slot = 0, count = 0;
             uint32_t parity = 1u;                    // first round: slots are free (wait on the phase before the first)
             for (int o = 0; o < p.n_ops; ++o) {
                 const ChainOp *op = p.ops + o;
@@ -606,6 +637,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
                     gv_bulk_g2s(dst + STAGE_W, m, STAGE_M, bar);
                     w += STAGE_W; m += STAGE_M;
                     if (++slot == p.S) { slot = 0; parity ^= 1u; }
+                    *issued = ++count;
                 }
             }
         }
@@ -830,7 +862,7 @@ static int chain_plan(Chain *c) {
     }
     c->mpu = 128 / gs;
     c->MR = c->M <= 1 ? 1 : c->M <= 2 ? 2 : 4;
-    int64_t off = 2 * 8 * CH_MAX_STAGES;
+    int64_t off = 2 * 8 * CH_MAX_STAGES + 16;        // mbarriers + the producer's progress counter
     off = (off + 127) & ~(int64_t)127;
     const int off_xs = (int)off; off += maxK * 2 * c->MR;
     const int off_gtab = (int)off; off += (maxK / gs) * c->MR * 8;
@@ -970,6 +1002,7 @@ static int chain_plan(Chain *c) {
     p.counter = c->d_counter; p.runs = c->d_runs;
     p.n_barriers = c->n_barriers; p.mbox_stride = mbox_total;
     p.S = (int)S; p.slot_stride = (int)stride;
+    p.l2pf = std::max(0, gv_env_int("W4A16_CHAIN_L2PF", 6));   // measured on the Qwen3-8B step: 0 / 2 / 4 / 6 / 8 / 12 / 16 stages -> 0.776 / 0.756 / 0.737 / 0.732 / 0.728 / 0.847 / 1.013 ms
     p.off_xs = off_xs; p.off_gtab = off_gtab; p.off_part = off_part; p.off_ring = off_ring;
     p.off_res = off_res; p.off_red = off_red;
     p.dbg = c->d_dbg;
