@@ -325,8 +325,7 @@ int64_t w4a16_weight_bytes(w4a16_handle_t h);  /* resident bytes of the repacked
 uint64_t w4a16_kernel_launches(void);
 /* Name of the kernel the dispatcher picks for M tokens ("decode_nt1", "prefill_umma", ...). */
 const char *w4a16_kernel_for(w4a16_handle_t h, int64_t M);
-/* Override dispatch for experiments: "auto" | "decode" | "prefill" | "skinny" (the SS-mode tcgen05 kernel,
- * M <= 128, where it applies).  Returns non-zero if unknown. */
+/* Override dispatch for tests: "auto" | "decode" (M <= 32 kernels) | "prefill" (tcgen05 kernel).  Non-zero if unknown. */
 int w4a16_set_dispatch(const char *mode);
 
 /* Profiling hook (W4A16_GV_DEBUG=1 in the environment): the decode kernel stamps %globaltimer per CTA

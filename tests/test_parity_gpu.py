@@ -145,7 +145,7 @@ def test_awq_forward_group_sizes_and_bias(product, g, M):
     assert_close_ref(run_forward(lin, xb), oracle_forward(xb, q, z, sb, g if g > 0 else K, bias_f32=bias), f"g={g}")
 
 
-@pytest.mark.parametrize("dispatch", ["decode", "prefill", "skinny"])
+@pytest.mark.parametrize("dispatch", ["decode", "prefill"])
 @pytest.mark.parametrize("M", [5, 17, 32, 64, 128])
 def test_forced_dispatch_every_kernel_family(product, dispatch, M):
     """Every kernel family on the same inputs (auto picks one per M; the others must agree with the oracle too).
@@ -162,21 +162,17 @@ def test_forced_dispatch_every_kernel_family(product, dispatch, M):
     assert_close_ref(got, oracle_forward(xb, q, z, sb, g), f"{dispatch} M={M}")
 
 
-@pytest.mark.parametrize("g,K,N,M", [(32, 512, 192, 33), (64, 1024, 320, 128), (-1, 512, 192, 7), (128, 512, 40960, 9)])
-def test_skinny_kernel_groups_bias_tail_and_many_tiles(product, g, K, N, M):
-    """The SS-mode tcgen05 kernel (opt-in): group sizes, bias, a partial last 256-feature tile (N % 256 != 0),
-    and more tiles than SMs (N = 40960: persistent CTAs run several tiles through both accumulator buffers)."""
+@pytest.mark.parametrize("g,K,N,M", [(32, 512, 192, 33), (64, 1024, 320, 128), (-1, 512, 192, 37), (128, 512, 40960, 40)])
+def test_prefill_kernel_groups_bias_tail_and_many_tiles(product, g, K, N, M):
+    """The tcgen05 kernel at few tokens: group sizes, per-channel scales, bias, a half-full last 128-feature tile
+    (N % 128 != 0), and more tiles than SMs (N = 40960: persistent CTAs run several tiles); deterministic."""
     lin, (qweight, qzeros, scales, bias) = make_awq_layer(product, K, N, g, seed=3 + M, bias=True)
     q, z, sb = awq_unpacked(qweight, qzeros, scales)
     xb = O.make_activations(M, K, seed=7)
-    product.set_dispatch("skinny")
-    try:
-        assert lin.kernel_for(M) == "skinny_umma_ss"
-        got = run_forward(lin, xb)
-        again = run_forward(lin, xb)
-    finally:
-        product.set_dispatch("auto")
-    assert_close_ref(got, oracle_forward(xb, q, z, sb, g if g > 0 else K, bias_f32=bias), f"skinny g={g} N={N}")
+    assert lin.kernel_for(M) == "prefill_umma"
+    got = run_forward(lin, xb)
+    again = run_forward(lin, xb)
+    assert_close_ref(got, oracle_forward(xb, q, z, sb, g if g > 0 else K, bias_f32=bias), f"prefill g={g} N={N}")
     assert (got == again).all()   # split-K partials are summed in slice order: deterministic
 
 

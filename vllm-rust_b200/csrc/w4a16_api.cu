@@ -218,14 +218,12 @@ static int ensure_gather(Linear *L, int64_t M, cudaStream_t stream) {
 // above -> the prefill kernel (tcgen05; split-K fills the machine at few tokens).  Measured on the Qwen3-8B shapes:
 // at M = 32 the prefill kernel takes 19 / 15 / 47 / 26 us against 23 / 28 / 74 / 48 us for the decode kernel, at
 // M = 16 the decode kernel still wins (13 / 12 / 35 / 23 against 19 / 15 / 46 / 25 us).
-// "skinny" forces the experimental SS-mode tcgen05 kernel (w4a16_skinny.cu) where it applies.
-enum { ROUTE_DECODE = 0, ROUTE_SKINNY = 1, ROUTE_PREFILL = 2 };
+enum { ROUTE_DECODE = 0, ROUTE_PREFILL = 2 };
 static int env_int_api(const char *name, int dflt) { const char *v = getenv(name); return v ? atoi(v) : dflt; }
 static int pick_route(const Linear &L, int64_t M) {
     if (g_dispatch == "prefill") return ROUTE_PREFILL;
     if (g_dispatch == "decode") return ROUTE_DECODE;
     static const int decode_max = std::min<int>((int)DECODE_MAX_M, env_int_api("W4A16_DECODE_MAX_M", 16));
-    if (g_dispatch == "skinny") return skinny_usable(L, M) ? ROUTE_SKINNY : (M > decode_max ? ROUTE_PREFILL : ROUTE_DECODE);
     return M > decode_max ? ROUTE_PREFILL : ROUTE_DECODE;
 }
 
@@ -244,7 +242,6 @@ static int forward_local(Linear *L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
         x = L->x_gather;
     }
     const int route = pick_route(*L, M);
-    if (route == ROUTE_SKINNY) return launch_skinny(*L, x, y, M, add_bias, stream);
     if (route == ROUTE_PREFILL) return launch_prefill(*L, x, y, M, add_bias, stream);
     for (int64_t m0 = 0; m0 < M; m0 += DECODE_MAX_M) {
         int64_t mm = std::min<int64_t>(DECODE_MAX_M, M - m0);
@@ -719,7 +716,6 @@ int64_t w4a16_weight_bytes(w4a16_handle_t h) {
 const char *w4a16_kernel_for(w4a16_handle_t h, int64_t M) {
     if (!h) return "none";
     const int route = pick_route(*reinterpret_cast<Linear *>(h), M);
-    if (route == ROUTE_SKINNY) return "skinny_umma_ss";
     if (route == ROUTE_PREFILL) return "prefill_umma";
     return decode_kernel_name(*reinterpret_cast<Linear *>(h), std::min<int64_t>(M, DECODE_MAX_M));
 }
@@ -733,7 +729,7 @@ int w4a16_debug_stamps(uint64_t *out, int64_t words, uint64_t *launches) {
 int w4a16_set_dispatch(const char *mode) {
     if (!mode) return fail("set_dispatch: null mode");
     std::string m(mode);
-    if (m != "auto" && m != "decode" && m != "prefill" && m != "skinny") return fail("set_dispatch: unknown mode '" + m + "'");
+    if (m != "auto" && m != "decode" && m != "prefill") return fail("set_dispatch: unknown mode '" + m + "'");
     g_dispatch = m;
     return 0;
 }

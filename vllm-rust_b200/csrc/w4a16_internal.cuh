@@ -134,9 +134,5 @@ int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
 bool prefill_available();
 int splitk_scratch(int device, size_t need, cudaStream_t stream, float **part, int **tickets);   // per (device, stream)
 constexpr int SPLITK_MAX_TILES = 1024;   // tickets per device
-// skinny GEMM (tcgen05, SS mode: tokens = A via TMA, dequantised weights = B in shared memory): 5 <= M <= 128
-bool skinny_usable(const Linear &L, int64_t M);
-int launch_skinny(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
-                  cudaStream_t stream);
 
 }  // namespace w4
