@@ -119,6 +119,36 @@ __device__ __forceinline__ uint32_t gv_pack4(int b0, int b1, int b2, int b3) {
     return (uint32_t)(b0 & 0xFF) | ((uint32_t)(b1 & 0xFF) << 8) | ((uint32_t)(b2 & 0xFF) << 16) | ((uint32_t)(b3 & 0xFF) << 24);
 }
 
+// Reductions over an aligned group of GL lanes (activation staging: the lanes that hold one quantisation group).
+// 16-lane groups use two FULL-warp redux.sync over inputs masked to one half each (a partial member mask sends
+// redux.sync down a slow divergent path; the shuffle tree costs 4 dependent SHFL + op per reduction).
+template <int GL>
+__device__ __forceinline__ uint32_t gv_group_max(uint32_t v, int lane) {
+    if constexpr (GL == 16) {
+        uint32_t lo, hi;
+        asm volatile("redux.sync.max.u32 %0, %1, 0xffffffff;" : "=r"(lo) : "r"(lane < 16 ? v : 0u));
+        asm volatile("redux.sync.max.u32 %0, %1, 0xffffffff;" : "=r"(hi) : "r"(lane < 16 ? 0u : v));
+        return lane < 16 ? lo : hi;
+    } else {
+#pragma unroll
+        for (int o = GL / 2; o > 0; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+        return v;
+    }
+}
+template <int GL>
+__device__ __forceinline__ int gv_group_add(int v, int lane) {
+    if constexpr (GL == 16) {
+        int lo, hi;
+        asm volatile("redux.sync.add.s32 %0, %1, 0xffffffff;" : "=r"(lo) : "r"(lane < 16 ? v : 0));
+        asm volatile("redux.sync.add.s32 %0, %1, 0xffffffff;" : "=r"(hi) : "r"(lane < 16 ? 0 : v));
+        return lane < 16 ? lo : hi;
+    } else {
+#pragma unroll
+        for (int o = GL / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        return v;
+    }
+}
+
 inline int gv_env_int(const char *name, int dflt) {
     const char *v = getenv(name);
     return v && *v ? atoi(v) : dflt;

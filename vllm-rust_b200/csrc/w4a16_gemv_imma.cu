@@ -159,8 +159,7 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 4 ? 2 : 1) gemv_imma_kernel(
                 uint32_t mx = 0;
 #pragma unroll
                 for (int q = 0; q < 4; ++q) mx = max(mx, max(w4[q] & 0x7FFFu, (w4[q] >> 16) & 0x7FFFu));
-#pragma unroll
-                for (int o = GL / 2; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+                mx = gv_group_max<GL>(mx, lane);
                 int E = (int)(mx >> 7);                                  // biased exponent of the group's max |x|
                 E = min(max(E, 14), 254);
                 const float scale = __int_as_float((267 - E) << 23);     // max|x| lands in [2^13, 2^14)
@@ -175,8 +174,7 @@ __global__ void __launch_bounds__(GV_THREADS, MR <= 4 ? 2 : 1) gemv_imma_kernel(
                     pk[q] = __byte_perm(__float_as_uint(lo), __float_as_uint(hi), 0x5410);
                     sum = __dp2a_lo((int)pk[q], 0x0101, sum);
                 }
-#pragma unroll
-                for (int o = GL / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                sum = gv_group_add<GL>(sum, lane);
                 if (i < total) {
                     const int m = MR == 1 ? 0 : MR > 4 ? i / ppr : (i >= ppr) + (MR > 2 ? (i >= 2 * ppr) + (i >= 3 * ppr) : 0);
                     const int c = i - m * ppr;                           // token, piece within the row
@@ -600,8 +598,10 @@ int launch_gemv_imma_peer(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16
         if (!gemv_imma_peer_usable(L, M, *peer)) return fail("launch_gemv_imma: shape not supported by the fused all-reduce epilogue");
         p.peer = *peer;
     }
-    // a launch with the fused exchange is not launched programmatically early either (experiment switch: bit 1)
-    const bool pdl = gv_env_int("W4A16_NO_PDL", 0) == 0 && (!peer || gv_env_int("W4A16_FUSED_PDL_ATTR", 0));
+    // A launch with the fused exchange is launched programmatically early (its weight prefetch runs under the previous
+    // kernel) from 4 ranks on, where the shards are a few microseconds long: Llama-3-70B step at TP = 2 / 4 / 8 without ->
+    // with the attribute 0.972 -> 1.078 / 0.723 -> 0.713 / 0.632 -> 0.598 ms.  It never releases ITS dependents early.
+    const bool pdl = gv_env_int("W4A16_NO_PDL", 0) == 0 && (!peer || gv_env_int("W4A16_FUSED_PDL_ATTR", peer->world >= 4 ? 1 : 0));
     const bool reg = (L.d.K % (32 * GV_UNIT_K)) == 0 && gv_env_int("W4A16_GV_REG", 1);
 #define W4_GI3(MR_, MPU_, FUSED_)                                                      \
     do {                                                                               \

@@ -106,8 +106,7 @@ __global__ void __launch_bounds__(G2_THREADS, 2) gemv_imma2_kernel(const GemvPar
                 uint32_t mx = 0;
 #pragma unroll
                 for (int q = 0; q < 4; ++q) mx = max(mx, max(w4[q] & 0x7FFFu, (w4[q] >> 16) & 0x7FFFu));
-#pragma unroll
-                for (int o = GL / 2; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+                mx = gv_group_max<GL>(mx, lane);
                 if (p.dbg && tid == 0 && base == 0 && r == 0) {   // stamp 6: the first activation load has arrived
                     unsigned long long tt;
                     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt));
@@ -125,8 +124,7 @@ __global__ void __launch_bounds__(G2_THREADS, 2) gemv_imma2_kernel(const GemvPar
                     pk[q] = __byte_perm(__float_as_uint(lo), __float_as_uint(hi), 0x5410);
                     sum = __dp2a_lo((int)pk[q], 0x0101, sum);
                 }
-#pragma unroll
-                for (int o = GL / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                sum = gv_group_add<GL>(sum, lane);
                 if (i < total) {
                     const int m = MR == 1 ? 0 : (i >= ppr) + (MR > 2 ? (i >= 2 * ppr) + (i >= 3 * ppr) : 0);
                     const int c = i - m * ppr;
