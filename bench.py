@@ -377,6 +377,7 @@ def run_gpu(args):
         if not args.quick:
             out["prefill"] = prefill_point(out["sweep"], peaks)
             out["prefill_sustained"] = prefill_sustained(P, torch, dev, peaks, local)
+            out["layer_chain"] = layer_chain(P, torch, dev, peaks)
             out["config1"] = config1(P, torch, dev, peaks)
             out["gptq_act_order"] = gptq_act_order(P, torch, dev, peaks)
             out["reference_gpu"] = reference_gpu(torch, dev, peaks)
@@ -618,6 +619,65 @@ def config1(P, torch, dev, peaks):
     out = {"shape": f"{name} {K}->{N}", "M": 1, "gpu_us": round(us, 2), "gpu_GBps": round(gbs, 1),
            "gpu_frac_measured_hbm": round(gbs / peaks["hbm_gbs"], 3), "kernel": lins[0].kernel_for(1), "copies": copies}
     out["cpu"] = cpu_time_shapes([(K, N)], reps=3)
+    return out
+
+
+def layer_chain(P, torch, dev, peaks, n_layers=36, Ms=(1, 2, 4)):
+    """SURVEY 8f-1 + 8f-4 together: the Qwen3-8B decoder layer MINUS attention as the engine would chain it.  Per layer
+    [o_proj (x = the attention output, a static buffer), gate/up as ONE SwiGLU handle with the post-attention residual
+    add + RMSNorm as its prologue, down_proj, next layer's fused qkv with residual add + input RMSNorm as its prologue];
+    attention itself sits between qkv and o (it is not part of this library), so every layer is one DecodeChain and a
+    step is n_layers launches (one CUDA graph).  Same weight bytes as the headline step; the residual stream, the norms
+    and silu*mul never leave the kernel."""
+    H, I, QKV = 4096, 12288, 6144
+    cfg = P.AwqConfig.int4(GROUP)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(99)
+    layers = []
+    for li in range(n_layers):
+        o = cfg.create_linear(H, H, False, dev)
+        o.load_weights(rand_awq(torch, H, H, dev, gen))
+        gu = cfg.create_linear(H, 2 * I, False, dev)
+        gu.set_epilogue(P.EPILOGUE_SWIGLU)
+        for half in range(2):
+            gu.load_part(half * I, rand_awq(torch, H, I, dev, gen))
+        down = cfg.create_linear(I, H, False, dev)
+        down.load_weights(rand_awq(torch, I, H, dev, gen))
+        qkv = cfg.create_linear(H, QKV, False, dev)
+        qkv.load_weights(rand_awq(torch, H, QKV, dev, gen))
+        w_post = (torch.rand(H, device=dev, generator=gen) + 0.5).to(torch.bfloat16)
+        w_in = (torch.rand(H, device=dev, generator=gen) + 0.5).to(torch.bfloat16)
+        layers.append((o, gu, down, qkv, w_post, w_in))
+    step_bytes = n_layers * sum(algo_bytes(1, K, N) for _, K, N in QWEN3_8B)
+    out = {"workload": f"{n_layers} x [o, gate_up+SwiGLU (post-attention add + RMSNorm prologue), down, qkv (add + input RMSNorm "
+                       "prologue)], one DecodeChain launch per layer, attention output and residual stream as static inputs",
+           "points": []}
+    for M in Ms:
+        z = lambda n: torch.zeros((M, n), device=dev, dtype=torch.bfloat16)
+        attn = (torch.randn((M, H), device=dev) * 0.05).to(torch.bfloat16)
+        resid = (torch.randn((M, H), device=dev) * 0.05).to(torch.bfloat16)
+        y_o, y_gu, y_dn, y_qkv, r_mid, r_out = z(H), z(I), z(H), z(QKV), z(H), z(H)
+        chains = []
+        try:
+          for o, gu, down, qkv, w_post, w_in in layers:
+            chains.append(P.DecodeChain(
+                [(o, attn, y_o), (gu, y_o, y_gu), (down, y_gu, y_dn), (qkv, y_dn, y_qkv)],
+                prologues=[None, {"norm_weight": w_post, "residual_in": resid, "residual_out": r_mid, "eps": 1e-6},
+                           None, {"norm_weight": w_in, "add_running_residual": True, "residual_out": r_out, "eps": 1e-6}]))
+        except P.W4A16Error as e:      # e.g. M = 4: four tokens x K = 12288 staged + the residual leave no room for the ring
+            out["points"].append({"M": M, "unsupported": str(e)})
+            del chains
+            continue
+        kern = chains[0].kernel()
+
+        def fn():
+            for c in chains:
+                c.run()
+        us = time_launches(torch, dev, fn, 1, target_ms=20.0, max_reps=40)
+        gbs = step_bytes / (us * 1e-6) / 1e9
+        out["points"].append({"M": M, "ms_per_step": round(us / 1e3, 4), "GBps": round(gbs, 1), "kernel": kern,
+                              "frac_measured_hbm": round(gbs / peaks["hbm_gbs"], 4), "launches_per_step": n_layers})
+        del chains
     return out
 
 

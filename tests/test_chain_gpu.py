@@ -325,3 +325,28 @@ def test_prologue_errors(product):
     with pytest.raises(product.W4A16Error, match="persistent kernel"):
         product.DecodeChain([(small, torch.zeros((1, 2560), dtype=torch.bfloat16, device=DEV), y)],
                             prologues=[{"norm_weight": torch.ones(2560, dtype=torch.bfloat16, device=DEV)}])
+
+
+def test_chain_of_gptq_formats(product):
+    """The resident layout is format-agnostic: GPTQ with stored zeros and symmetric GPTQ (q - 8) linears in one chain
+    with an AWQ one, each against its oracle."""
+    from helpers import gptq_unpacked
+    g, M = 128, 2
+    qw, qz, sc, _ = O.make_gptq_checkpoint(4096, 512, g, seed=21)
+    zp = product.GptqConfig(4, g, False).create_linear(4096, 512, False, DEV)
+    zp.load_weights({"qweight": t_i32(qw), "qzeros": t_i32(qz), "scales": torch.from_numpy(sc)})
+    zp_ck = gptq_unpacked(qw, qz, sc)
+    qw2, _, sc2, _ = O.make_gptq_checkpoint(4096, 768, g, seed=22)
+    sym = product.MarlinConfig.gptq_int4(g).create_linear(4096, 768, False, DEV)
+    sym.load_weights({"qweight": t_i32(qw2), "scales": torch.from_numpy(sc2)})
+    sym_ck = gptq_unpacked(qw2, None, sc2)
+    awq, awq_ck = make_linear(product, 4096, 256, g, seed=23)
+    xs = [t_bf16_from_bits(O.make_activations(M, 4096, seed=30 + i)).to(DEV) for i in range(3)]
+    ys = [torch.zeros((M, n), dtype=torch.bfloat16, device=DEV) for n in (512, 768, 256)]
+    chain = product.DecodeChain([(zp, xs[0], ys[0]), (sym, xs[1], ys[1]), (awq, xs[2], ys[2])])
+    assert chain.kernel().startswith("chain_imma")
+    chain.run()
+    torch.cuda.synchronize()
+    assert_close_ref(bits_of(ys[0]), oracle_forward(bits_of(xs[0]), *zp_ck, g), "gptq zero-point")
+    assert_close_ref(bits_of(ys[1]), oracle_forward(bits_of(xs[1]), sym_ck[0], None, sym_ck[2], g, zero_mode=1), "gptq symmetric")
+    assert_close_ref(bits_of(ys[2]), oracle_forward(bits_of(xs[2]), *awq_ck[:3], g), "awq")
