@@ -176,20 +176,42 @@ def test_ping_pong_buffers_get_barriers(product, M):
         assert float((want - got.float()).abs().max()) <= 0.05 * scale    # six linears of compounding bf16 roundings
 
 
+@pytest.mark.parametrize("M", [1, 4])
+def test_any_k_multiple_of_128(product, M):
+    """in_features that are not multiples of 4096 (Qwen3-4B: 2560 / 9728; tensor-parallel shards: 1024, 3584): stages of 32
+    units cross row-block boundaries and the last stage of a linear is short."""
+    g = 128
+    shapes = [(2560, 6144), (1024, 4096), (9728, 2560), (3584, 512), (128, 256), (4096 + 128, 320)]
+    lins, cks, xs, ys = [], [], [], []
+    for i, (K, N) in enumerate(shapes):
+        lin, ck = make_linear(product, K, N, g, seed=60 + i, bias=(i % 2 == 1))
+        lins.append(lin); cks.append(ck)
+        xs.append(t_bf16_from_bits(O.make_activations(M, K, seed=70 + i)).to(DEV))
+        ys.append(torch.full((M, N), float("nan"), dtype=torch.bfloat16, device=DEV))
+    chain = product.DecodeChain(list(zip(lins, xs, ys)))
+    assert chain.kernel().startswith("chain_imma")
+    for rep in range(2):
+        chain.run()
+        torch.cuda.synchronize()
+        for i, (K, N) in enumerate(shapes):
+            q, z, sb, b = cks[i]
+            assert_close_ref(bits_of(ys[i]), oracle_forward(bits_of(xs[i]), q, z, sb, g, bias_f32=b), f"K={K} N={N} M={M}")
+
+
 def test_fallback_per_linear(product):
-    M, g = 2, 128
-    a, (q, z, sb, _) = make_linear(product, 2560, 512, g, seed=1)      # K not a multiple of 4096
-    b, _ = make_linear(product, 4096, 512, g, seed=2)
-    xa = t_bf16_from_bits(O.make_activations(M, 2560, seed=1)).to(DEV)
+    M = 2
+    a, (q, z, sb, _) = make_linear(product, 4096, 512, 64, seed=1)       # group size 64 ...
+    b, _ = make_linear(product, 4096, 512, 128, seed=2)                  # ... and 128 in one chain: not taken
+    xa = t_bf16_from_bits(O.make_activations(M, 4096, seed=1)).to(DEV)
     xb = t_bf16_from_bits(O.make_activations(M, 4096, seed=2)).to(DEV)
     ya = torch.zeros((M, 512), dtype=torch.bfloat16, device=DEV)
     yb = torch.zeros((M, 512), dtype=torch.bfloat16, device=DEV)
     chain = product.DecodeChain([(a, xa, ya), (b, xb, yb)])
-    assert chain.kernel().startswith("per_linear") and "4096" in chain.kernel()
+    assert chain.kernel().startswith("per_linear") and "group sizes" in chain.kernel()
     chain.run()
     torch.cuda.synchronize()
     assert (bits_of(ya) == bits_of(a.forward(xa))).all() and (bits_of(yb) == bits_of(b.forward(xb))).all()
-    assert_close_ref(bits_of(ya), oracle_forward(bits_of(xa), q, z, sb, g), "fallback")
+    assert_close_ref(bits_of(ya), oracle_forward(bits_of(xa), q, z, sb, 64), "fallback")
     # more than 4 tokens: also per linear
     x8 = t_bf16_from_bits(O.make_activations(8, 4096, seed=3)).to(DEV)
     y8 = torch.zeros((8, 512), dtype=torch.bfloat16, device=DEV)
@@ -321,10 +343,10 @@ def test_prologue_errors(product):
         product.DecodeChain([(lin, x, y)], prologues=[{"norm_weight": w[:128].contiguous()}])
     with pytest.raises(product.W4A16Error, match="one entry"):
         product.DecodeChain([(lin, x, y)], prologues=[])
-    small, _ = make_linear(product, 2560, 256, 128, seed=6)          # the persistent kernel does not take K = 2560
+    other, _ = make_linear(product, 4096, 256, 64, seed=6)           # mixed group sizes: the persistent kernel declines
     with pytest.raises(product.W4A16Error, match="persistent kernel"):
-        product.DecodeChain([(small, torch.zeros((1, 2560), dtype=torch.bfloat16, device=DEV), y)],
-                            prologues=[{"norm_weight": torch.ones(2560, dtype=torch.bfloat16, device=DEV)}])
+        product.DecodeChain([(lin, x, y), (other, x, torch.zeros((1, 256), dtype=torch.bfloat16, device=DEV))],
+                            prologues=[{"norm_weight": w}, None])
 
 
 def test_chain_of_gptq_formats(product):

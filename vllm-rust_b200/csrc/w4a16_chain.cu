@@ -39,7 +39,7 @@ struct ChainOp {
     __nv_bfloat16 *y;
     const int *rb;             // [grid + 1]: CTA c owns row blocks [rb[c], rb[c + 1])
     int M, K, N, UPR;
-    int spr;                   // 32-unit stages per row block = K / 4096
+    int spr;                   // K / 4096 when K is a multiple of 4096 (a stage = a whole 4096-k slab of one row block), else 0
     int swiglu, hoist;
     int barrier_before;        // a grid-wide barrier separates this linear from the one before it (hazards the mailboxes do not cover)
     // Mailboxes: y of a linear that a later linear of the chain reads is ALSO stored into a chain-owned copy whose
@@ -345,7 +345,7 @@ __device__ __forceinline__ void ch_stage_x(const __nv_bfloat16 *x, uint8_t *xs, 
     const int ppr = K >> 3, total = M * ppr;
     const uint4 *x16 = reinterpret_cast<const uint4 *>(x);
     int base = 0;
-    for (; base + 3 * CH_CONS_THREADS <= total; base += 3 * CH_CONS_THREADS)
+    for (; total - base > 2 * CH_CONS_THREADS; base += 3 * CH_CONS_THREADS)   // (the batch guards pieces past the end)
         ch_stage_batch<MR, MPU, 3, NORM>(x16, xs, gtab, ppr, total, base, tid, lane, poll, dbg_valid, norm_w, inv_rms, normed_out);
     const int left = (total - base + CH_CONS_THREADS - 1) / CH_CONS_THREADS;   // 0..2 (warp-uniform)
     if (left == 2) ch_stage_batch<MR, MPU, 2, NORM>(x16, xs, gtab, ppr, total, base, tid, lane, poll, dbg_valid, norm_w, inv_rms, normed_out);
@@ -449,6 +449,107 @@ __device__ __forceinline__ void ch_row_blocks(const ChainParams &p, const ChainO
         }
         if (t < MR) part[(((size_t)s * CH_CONS_WARPS + wi) * 8 + g) * MR + t] = make_float2(y0, y1);
     }
+}
+
+// General path (any K % 128 == 0): the CTA's share of the linear is the unit range [R0 * UPR, R1 * UPR) of the W4T stream
+// (a unit = 128 k of one 16-row block), cut into stages of 32 consecutive units whatever the row blocks are; the last
+// stage may be short.  Warp wi takes units wi and wi + 16 of every stage; a unit's row block and k position follow from
+// its index, its partial sums are added to the warp's entry of that row block in `part` (zeroed by the caller) whenever
+// the row block changes -- for K >= 4096 that is once per several stages.
+template <int MR, int MPU>
+__device__ __forceinline__ void ch_row_blocks_general(const ChainParams &p, const ChainOp &op, int n_slots, int wi, int lane,
+                                              uint32_t ring, uint32_t bar_full, uint32_t bar_empty, uint32_t xs_u32, uint32_t gtab_u32,
+                                              float2 *part, int &slot, uint32_t &parity) {
+    constexpr int COLS = 2 * MR;
+    constexpr int IPG = 4 / MPU;
+    constexpr uint32_t STAGE_W = 32 * GV_UNIT_BYTES;
+    constexpr uint32_t XU = 4 * 4 * COLS * 8;  // bytes of B fragments per unit
+    constexpr uint32_t GU = MPU * MR * 8;      // bytes of group table per unit
+    const int g = lane >> 2, t = lane & 3;
+    const uint32_t xs_l = xs_u32 + (uint32_t)((t * COLS + (g & (COLS - 1))) * 8);
+    const uint32_t gt_l = gtab_u32 + (uint32_t)((t & (MR - 1)) * 8);
+    const bool b_lane = COLS >= 8 || g < COLS;   // only the lanes of the data columns need real B values
+    const uint32_t offW = (uint32_t)(wi * GV_UNIT_BYTES + lane * 16);
+    const uint32_t offM = STAGE_W + (uint32_t)(wi * MPU * META_BYTES);
+    const int UPR = op.UPR, n_units = n_slots * UPR, nst = (n_units + 31) >> 5;
+    float y0 = 0.f, y1 = 0.f;                  // rows g / g+8 of row block `cur`, token slot t
+    int cur = -1;
+    auto flush = [&]() {
+        if (cur >= 0 && t < MR) {
+            float2 *e = part + (((size_t)cur * CH_CONS_WARPS + wi) * 8 + g) * MR + t;
+            float2 v = *e;
+            v.x += y0; v.y += y1;
+            *e = v;
+        }
+    };
+    for (int s = 0; s < nst; ++s) {
+        const uint32_t sb = ring + (uint32_t)slot * (uint32_t)p.slot_stride;
+        gv_mbar_wait(bar_full + 8 * slot, parity);
+        uint32_t w[CH_UPW][8], s2[CH_UPW][MPU], zb[CH_UPW][MPU];
+        bool valid[CH_UPW];
+#pragma unroll
+        for (int j = 0; j < CH_UPW; ++j) {
+            valid[j] = 32 * s + wi + CH_CONS_WARPS * j < n_units;      // warp-uniform
+            if (valid[j]) {
+                const uint32_t sw = sb + offW + (uint32_t)(CH_CONS_WARPS * j * GV_UNIT_BYTES), sm = sb + offM + (uint32_t)(CH_CONS_WARPS * j * MPU * META_BYTES);
+                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]) : "r"(sw));
+                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4+512];" : "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7]) : "r"(sw));
+#pragma unroll
+                for (int h = 0; h < MPU; ++h) {
+                    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(s2[j][h]) : "r"(sm + h * META_BYTES + 4 * g));
+                    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(zb[j][h]) : "r"(sm + h * META_BYTES + META_ZERO_OFF + g));
+                }
+            }
+        }
+        __syncwarp();                       // every lane holds its words: the slot may be refilled
+        if (lane == 0) ch_mbar_arrive(bar_empty + 8 * slot);
+        int rl[CH_UPW], ku[CH_UPW];          // row block (slot) and k position of each unit
+        int acc[CH_UPW][MPU][4];
+#pragma unroll
+        for (int j = 0; j < CH_UPW; ++j) {
+            const int ul = 32 * s + wi + CH_CONS_WARPS * j;          // unit index inside the CTA's range
+            rl[j] = ul / UPR;
+            ku[j] = ul - rl[j] * UPR;
+#pragma unroll
+            for (int h = 0; h < MPU; ++h)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) acc[j][h][q] = 0;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+#pragma unroll
+            for (int j = 0; j < CH_UPW; ++j) {                        // the units' IMMA chains interleaved
+                if (!valid[j]) continue;
+                const uint32_t wa = w[j][2 * i], wb = w[j][2 * i + 1];
+                uint32_t b0 = 0, b1 = 0;
+                if (b_lane)
+                    asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(b0), "=r"(b1) : "r"(xs_l + (uint32_t)ku[j] * XU + (uint32_t)(i * 4 * COLS * 8)));
+                // rows g: the low nibbles; rows g+8: the RAW bytes 16 q[g+8] + q[g] (rows g are subtracted afterwards)
+                ch_imma(acc[j][i / IPG], wa & 0x0F0F0F0Fu, wa, wb & 0x0F0F0F0Fu, wb, b0, b1);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < CH_UPW; ++j) {
+            if (!valid[j]) continue;
+            if (rl[j] != cur) { flush(); cur = rl[j]; y0 = 0.f; y1 = 0.f; }
+#pragma unroll
+            for (int h = 0; h < MPU; ++h) {
+                int X, e2b;
+                asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(X), "=r"(e2b) : "r"(gt_l + (uint32_t)ku[j] * GU + (uint32_t)(h * MR * 8)));
+                const float e2 = __int_as_float(e2b);
+                const int tg = acc[j][h][0] * 128 + acc[j][h][1];
+                const int tr = acc[j][h][2] * 128 + acc[j][h][3];
+                const int ug = tg - (int)(zb[j][h] & 0x0Fu) * X;
+                const int ug8 = tr - tg - (int)(zb[j][h] & 0xF0u) * X;          // 16 * (row g+8 - z8 * X)
+                const float slo = __uint_as_float(s2[j][h] << 16) * e2;
+                const float shi = __uint_as_float(s2[j][h] & 0xFFFF0000u) * (e2 * 0.0625f);
+                y0 = fmaf(slo, (float)ug, y0);
+                y1 = fmaf(shi, (float)ug8, y1);
+            }
+        }
+        if (++slot == p.S) { slot = 0; parity ^= 1u; }
+    }
+    flush();
 }
 
 // K = 4096, group size 128 (one stage = one row block; the warp meets the same two k-units in every stage, so its B
@@ -564,7 +665,9 @@ __device__ __forceinline__ void ch_row_blocks_hoist(const ChainParams &p, int n_
 
 // PRO: the chain has prologues (w4a16_chain_prologue); a separate instantiation, so that chains of plain linears carry
 // none of it (merely compiling the prologue into the one kernel cost the plain step 6 %: 0.826 -> 0.875 ms).
-template <int MR, int MPU, bool PRO>
+// GEN: some linear of the chain has an in_features that is not a multiple of 4096 (its stages cross row-block boundaries);
+// again a separate instantiation: with the general loop compiled in, the Qwen3-8B step lost 14 % (0.732 -> 0.849 ms).
+template <int MR, int MPU, bool PRO, bool GEN>
 __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams p) {
     extern __shared__ __align__(128) uint8_t ch_smem[];
     uint8_t *xs = ch_smem + p.off_xs;
@@ -596,19 +699,20 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
             for (int o = 0; o < p.n_ops; ++o) {
                 const ChainOp *op = p.ops + o;
                 const int R0 = __ldg(op->rb + cta), R1 = __ldg(op->rb + cta + 1);
-                const int nst = (R1 - R0) * op->spr;
+                const int n_units = (R1 - R0) * op->UPR, nst = (n_units + 31) >> 5;
                 const size_t unit0 = (size_t)R0 * op->UPR;
                 const uint8_t *w = op->qw + unit0 * GV_UNIT_BYTES;
                 const uint8_t *m = op->meta + unit0 * (MPU * META_BYTES);
                 for (int s = 0; s < nst; ++s, ++q) {
+                    const uint32_t cnt = (uint32_t)min(32, n_units - 32 * s);
                     uint32_t spins = 0;
                     while (q >= *issued + p.l2pf) {
                         __nanosleep(64);
                         if (++spins > GV_SPIN_LIMIT) __trap();
                     }
                     if (q >= *issued) {        // still ahead of the ring: otherwise the real copy is already on its way
-                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(w), "r"(STAGE_W) : "memory");
-                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(m), "r"(STAGE_M) : "memory");
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(w), "r"(cnt * GV_UNIT_BYTES) : "memory");
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(m), "r"(cnt * (MPU * META_BYTES)) : "memory");
                     }
                     w += STAGE_W; m += STAGE_M;
                 }
@@ -625,16 +729,18 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
                 const ChainOp *op = p.ops + o;
                 const int *rb = op->rb;
                 const int R0 = __ldg(rb + cta), R1 = __ldg(rb + cta + 1);
-                const int nst = (R1 - R0) * op->spr;
+                const int n_units = (R1 - R0) * op->UPR, nst = (n_units + 31) >> 5;
                 const size_t unit0 = (size_t)R0 * op->UPR;
                 const uint8_t *w = op->qw + unit0 * GV_UNIT_BYTES;
                 const uint8_t *m = op->meta + unit0 * (MPU * META_BYTES);
                 for (int s = 0; s < nst; ++s) {
                     gv_mbar_wait(bar_empty + 8 * slot, parity);
                     const uint32_t bar = bar_full + 8 * slot, dst = ring + (uint32_t)slot * (uint32_t)p.slot_stride;
-                    gv_mbar_expect_tx(bar, STAGE_W + STAGE_M);
-                    gv_bulk_g2s(dst, w, STAGE_W, bar);
-                    gv_bulk_g2s(dst + STAGE_W, m, STAGE_M, bar);
+                    const uint32_t cnt = (uint32_t)min(32, n_units - 32 * s);          // the last stage of a linear may be short
+                    const uint32_t bw = cnt * GV_UNIT_BYTES, bm = cnt * (MPU * META_BYTES);
+                    gv_mbar_expect_tx(bar, bw + bm);
+                    gv_bulk_g2s(dst, w, bw, bar);
+                    gv_bulk_g2s(dst + STAGE_W, m, bm, bar);
                     w += STAGE_W; m += STAGE_M;
                     if (++slot == p.S) { slot = 0; parity ^= 1u; }
                     *issued = ++count;
@@ -724,12 +830,16 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
             for (int i = cta + tid * grid; i < pieces; i += grid * CH_CONS_THREADS)
                 dst[i] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
         }
+        if (GEN && !(MPU == 1 && op.hoist) && op.spr == 0)      // the general path accumulates into `part`
+            for (int i = tid; i < n_slots * CH_CONS_WARPS * 8 * MR; i += CH_CONS_THREADS) part[i] = make_float2(0.f, 0.f);
         ch_bar_consumers();
         stamp(o, 1);
         if (MPU == 1 && op.hoist)
             ch_row_blocks_hoist<MR>(p, n_slots, wi, lane, ring, bar_full, bar_empty, gv_smem_u32(xs), gv_smem_u32(gtab), part, slot, parity);
-        else
+        else if (!GEN || op.spr > 0)
             ch_row_blocks<MR, MPU, false>(p, op, n_slots, wi, lane, ring, bar_full, bar_empty, gv_smem_u32(xs), gv_smem_u32(gtab), part, slot, parity);
+        else if constexpr (GEN)
+            ch_row_blocks_general<MR, MPU>(p, op, n_slots, wi, lane, ring, bar_full, bar_empty, gv_smem_u32(xs), gv_smem_u32(gtab), part, slot, parity);
         ch_bar_consumers();
         stamp(o, 2);
         // combine the 16 warps of every row block (fixed tree: deterministic) and write y
@@ -776,6 +886,7 @@ struct Chain {
     std::vector<__nv_bfloat16 *> y;
     std::vector<w4a16_chain_prologue> pro;   // per linear; norm_weight == null: none
     bool has_prologue = false;
+    bool general_k = false;        // some in_features is not a multiple of 4096
     bool persistent = false;       // the chain kernel takes it; otherwise the linears are launched one by one
     std::string why_not;
     ChainOp *d_ops = nullptr;
@@ -790,11 +901,11 @@ struct Chain {
     int MR = 1, mpu = 1, smem = 0, grid = 0;
 };
 
-template <int MR, int MPU, bool PRO>
+template <int MR, int MPU, bool PRO, bool GEN>
 static int chain_launch_t(const Chain &c, cudaStream_t stream, bool pdl) {
     static bool attr_set[64] = {};
     if (c.device >= 0 && c.device < 64 && !attr_set[c.device]) {
-        W4_CUDA_OK(cudaFuncSetAttribute(chain_kernel<MR, MPU, PRO>, cudaFuncAttributeMaxDynamicSharedMemorySize, CH_SMEM_MAX));
+        W4_CUDA_OK(cudaFuncSetAttribute(chain_kernel<MR, MPU, PRO, GEN>, cudaFuncAttributeMaxDynamicSharedMemorySize, CH_SMEM_MAX));
         attr_set[c.device] = true;
     }
     cudaLaunchConfig_t cfg{};
@@ -807,23 +918,27 @@ static int chain_launch_t(const Chain &c, cudaStream_t stream, bool pdl) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    W4_CUDA_OK(cudaLaunchKernelEx(&cfg, chain_kernel<MR, MPU, PRO>, c.prm));
+    W4_CUDA_OK(cudaLaunchKernelEx(&cfg, chain_kernel<MR, MPU, PRO, GEN>, c.prm));
     count_launch();
     return 0;
 }
 
 static int chain_launch(const Chain &c, cudaStream_t stream) {
     const bool pdl = gv_env_int("W4A16_NO_PDL", 0) == 0;
-#define W4_CH(MR_)                                                       \
-    do {                                                                 \
-        if (c.has_prologue) {                                            \
-            if (c.mpu == 1) return chain_launch_t<MR_, 1, true>(c, stream, pdl);   \
-            if (c.mpu == 2) return chain_launch_t<MR_, 2, true>(c, stream, pdl);   \
-            return chain_launch_t<MR_, 4, true>(c, stream, pdl);         \
-        }                                                                \
-        if (c.mpu == 1) return chain_launch_t<MR_, 1, false>(c, stream, pdl);   \
-        if (c.mpu == 2) return chain_launch_t<MR_, 2, false>(c, stream, pdl);   \
-        return chain_launch_t<MR_, 4, false>(c, stream, pdl);            \
+#define W4_CH4(MR_, MPU_)                                                                   \
+    do {                                                                                    \
+        if (c.has_prologue) {                                                               \
+            if (c.general_k) return chain_launch_t<MR_, MPU_, true, true>(c, stream, pdl);  \
+            return chain_launch_t<MR_, MPU_, true, false>(c, stream, pdl);                  \
+        }                                                                                   \
+        if (c.general_k) return chain_launch_t<MR_, MPU_, false, true>(c, stream, pdl);     \
+        return chain_launch_t<MR_, MPU_, false, false>(c, stream, pdl);                     \
+    } while (0)
+#define W4_CH(MR_)                        \
+    do {                                  \
+        if (c.mpu == 1) W4_CH4(MR_, 1);   \
+        if (c.mpu == 2) W4_CH4(MR_, 2);   \
+        W4_CH4(MR_, 4);                   \
     } while (0)
     switch (c.MR) {
         case 1: W4_CH(1);
@@ -831,6 +946,7 @@ static int chain_launch(const Chain &c, cudaStream_t stream) {
         default: W4_CH(4);
     }
 #undef W4_CH
+#undef W4_CH4
 }
 
 static void chain_free(Chain *c) {
@@ -851,13 +967,13 @@ static int chain_plan(Chain *c) {
     int gs = 0;
     int64_t maxK = 0, max_slots = 1;
     for (Linear *L : c->lin) {
-        if (L->d.K % (32 * GV_UNIT_K)) { c->why_not = "in_features not a multiple of 4096"; return 0; }
         if (L->d.gs != 32 && L->d.gs != 64 && L->d.gs != 128) { c->why_not = "group size not 32 / 64 / 128"; return 0; }
         if (gs && L->d.gs != gs) { c->why_not = "mixed group sizes"; return 0; }
         if (L->perm && !L->perm_external) { c->why_not = "act-order linear (activation gather)"; return 0; }
         if (L->d.NR * (L->d.K / GV_UNIT_K) >= ((int64_t)1 << 30)) { c->why_not = "linear too large"; return 0; }
         gs = L->d.gs;
         maxK = std::max(maxK, L->d.K);
+        if (L->d.K % (32 * GV_UNIT_K)) c->general_k = true;
         max_slots = std::max<int64_t>(max_slots, (L->d.NR + grid - 1) / grid);
     }
     c->mpu = 128 / gs;
@@ -968,7 +1084,7 @@ static int chain_plan(Chain *c) {
         o.rb = c->d_rb + (size_t)i * (grid + 1);
         o.M = (int)c->M; o.K = (int)L->d.K; o.N = (int)L->d.N;
         o.UPR = (int)(L->d.K / GV_UNIT_K);
-        o.spr = o.UPR / 32;
+        o.spr = o.UPR % 32 == 0 ? o.UPR / 32 : 0;
         o.swiglu = L->epilogue == W4A16_EPILOGUE_SWIGLU;
         o.hoist = o.spr == 1 && c->mpu == 1;
         o.barrier_before = barrier[i];
