@@ -262,6 +262,14 @@ typedef struct w4a16_chain_prologue {
 int w4a16_chain_create_ex(w4a16_chain_t *out, int n, const w4a16_handle_t *handles,
                           const void *const *x_bf16, void *const *y_bf16, int64_t M,
                           const w4a16_chain_prologue *prologues /* [n] or NULL */);
+/* Tensor-parallel chains: with a peer group attached (w4a16_peer_*, see below), every ROW shard of the chain finishes
+ * with the all-reduce of RowParallelLinear::forward (parallel_layers.rs:295-311) INSIDE the launch: its epilogue stores
+ * the rank's fp32 partial sums into every peer's symmetric buffer over NVLink, polls its own buffer until every rank's
+ * words have arrived (the data are their own flags), sums them in rank order (bit-identical on every rank), adds the
+ * bias and hands the bf16 result to the next linear through the chain's mailbox -- no NCCL call, no kernel boundary.
+ * Without a peer group a ROW shard writes its partial sum.  All ranks must build the same chain and run it the same
+ * number of times (SPMD); call once after creation, before the first run.  Not combined with prologues yet. */
+int w4a16_chain_set_peer(w4a16_chain_t chain, w4a16_peer_t peer);
 int w4a16_chain_run(w4a16_chain_t chain, w4a16_stream_t stream);
 /* chain_run with HOST buffers at the two ends: H2D copy of the first linear's x ([M, in_features] bf16), the chain,
  * D2H copy of the last linear's y, stream synchronise -- what one decode step moves between host and device (the

@@ -77,6 +77,7 @@ SIGNATURES = {
     "w4a16_set_dispatch": (_i32, [ctypes.c_char_p]),
     "w4a16_debug_stamps": (_i32, [_vp, _i64, ctypes.POINTER(_u64)]),
     "w4a16_chain_create": (_i32, [ctypes.POINTER(_vp), _i32, ctypes.POINTER(_vp), ctypes.POINTER(_vp), ctypes.POINTER(_vp), _i64]),
+    "w4a16_chain_set_peer": (_i32, [_vp, _vp]),
     "w4a16_chain_run": (_i32, [_vp, _vp]),
     "w4a16_chain_run_host": (_i32, [_vp, _vp, _vp, _vp]),
     "w4a16_chain_destroy": (_i32, [_vp]),

@@ -533,6 +533,23 @@ struct PeerCtx {
     uint32_t *epoch_dev = nullptr;   // [0] launch counter, [1] finished-CTA ticket (device, this rank only)
 };
 
+// The device-side view of an attached peer group, for callers outside this file (the chain kernel's all-reduce).
+extern "C++" {
+namespace w4 {
+int peer_make_view(void *peer, PeerView *v) {
+    PeerCtx *c = reinterpret_cast<PeerCtx *>(peer);
+    if (!c) return fail("peer group: null");
+    if (!c->attached) return fail("peer group: buffers not attached");
+    *v = PeerView{};
+    for (int r = 0; r < c->world; ++r) v->base[r] = c->base[r];
+    v->world = c->world; v->rank = c->rank; v->cap = c->cap;
+    v->flags = 0u;
+    v->epoch_ptr = c->epoch_dev; v->ticket = reinterpret_cast<int *>(c->epoch_dev + 1);
+    return 0;
+}
+}  // namespace w4
+}  // extern "C++"
+
 int w4a16_peer_create(w4a16_peer_t *out, int rank, int world_size, int64_t max_partial_floats) {
     if (!out) return fail("peer_create: null out");
     if (world_size < 2 || world_size > PEER_MAX_WORLD) return fail("peer_create: world_size must be in 2..8");

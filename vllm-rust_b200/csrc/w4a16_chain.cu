@@ -57,6 +57,7 @@ struct ChainOp {
     __nv_bfloat16 *res_out, *normed_out;   // [M, K] h / the normalised row, written by CTA 0; may be null
     float eps;
     int add_running;                       // h = x + the residual the previous prologue of the chain left in shared memory
+    int exchange;                          // row-parallel shard with a peer group: 1-based index among the chain's all-reduces, else 0
 };
 
 struct ChainParams {
@@ -71,6 +72,8 @@ struct ChainParams {
     int off_xs, off_gtab, off_part, off_ring;
     int off_res, off_red;          // prologue: running residual bf16 [M][K], reduction scratch (floats); -1 / unused without one
     unsigned long long *dbg;       // [n_ops][grid][CH_DBG_WORDS] %globaltimer stamps, or null
+    PeerView peer;                 // tensor-parallel group (w4a16_chain_set_peer); world <= 1: none
+    int n_exchange;                // all-reduces per run
 };
 
 __device__ __forceinline__ void ch_imma(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
@@ -667,7 +670,10 @@ __device__ __forceinline__ void ch_row_blocks_hoist(const ChainParams &p, int n_
 // none of it (merely compiling the prologue into the one kernel cost the plain step 6 %: 0.826 -> 0.875 ms).
 // GEN: some linear of the chain has an in_features that is not a multiple of 4096 (its stages cross row-block boundaries);
 // again a separate instantiation: with the general loop compiled in, the Qwen3-8B step lost 14 % (0.732 -> 0.849 ms).
-template <int MR, int MPU, bool PRO, bool GEN>
+// TP: row-parallel linears of the chain all-reduce their partial sums over the peers' symmetric buffers inside their
+// epilogue (the exchange of gemv_imma_kernel<.., FUSED>, w4a16_gemv_imma.cu: every rank stores its fp32 partials into
+// slot [epoch % 3][rank] of every rank, polls its own slots until no word is the sentinel, sums in rank order).
+template <int MR, int MPU, bool PRO, bool GEN, bool TP>
 __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams p) {
     extern __shared__ __align__(128) uint8_t ch_smem[];
     uint8_t *xs = ch_smem + p.off_xs;
@@ -763,6 +769,8 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
     asm volatile("griddepcontrol.wait;" ::: "memory");   // the first x may come from the previous kernel; and the
     // previous run of this chain (which may have released this launch early) has stored `runs` only now
     const unsigned int run = p.n_ops > 1 ? __ldcg(p.runs) : 0u;
+    uint32_t ep_base = 0u;
+    if constexpr (TP) ep_base = __ldcg(p.peer.epoch_ptr);      // stored by the last CTA of the previous launch on this rank
     unsigned long long bar_count = (unsigned long long)run * (unsigned long long)p.n_barriers;   // barriers passed so far
     const long long mb_cur = (run & 1u) ? p.mbox_stride : 0, mb_nxt = (run & 1u) ? 0 : p.mbox_stride;
     int slot = 0;                                         // ring position of the CTA's first stage of the current linear
@@ -852,6 +860,20 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
             v.x += __shfl_xor_sync(0xffffffffu, v.x, 1); v.y += __shfl_xor_sync(0xffffffffu, v.y, 1);
             v.x += __shfl_xor_sync(0xffffffffu, v.x, 2); v.y += __shfl_xor_sync(0xffffffffu, v.y, 2);
             const int tok = e % MR, n0 = (R0 + sl) * 16 + e / MR;
+            if constexpr (TP) {
+                if (op.exchange) {          // this rank's partials into slot [epoch % 3][rank] of EVERY rank (lane q serves peers q, q + 4)
+                    uint32_t bx = __float_as_uint(v.x), by = __float_as_uint(v.y);
+                    if (bx == PEER_EMPTY) bx = 0u;
+                    if (by == PEER_EMPTY) by = 0u;
+                    const size_t cur_off = (size_t)((ep_base + (uint32_t)op.exchange) % 3u) * ((size_t)p.peer.world * p.peer.cap);
+                    for (int r = q; r < p.peer.world && tok < op.M; r += 4) {
+                        uint32_t *dst = reinterpret_cast<uint32_t *>(p.peer.base[r] + cur_off + (size_t)p.peer.rank * p.peer.cap);
+                        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(dst + (size_t)n0 * PEER_TOK + tok), "r"(bx) : "memory");
+                        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(dst + (size_t)(n0 + 8) * PEER_TOK + tok), "r"(by) : "memory");
+                    }
+                    continue;
+                }
+            }
             if (q == 0 && tok < op.M) {
                 const float b0 = op.bias ? __bfloat162float(op.bias[n0]) : 0.f;
                 const float b1 = op.bias ? __bfloat162float(op.bias[n0 + 8]) : 0.f;
@@ -870,11 +892,71 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
                 }
             }
         }
+        if constexpr (TP) {
+            if (op.exchange) {
+                // poll this rank's slots until every source's word has arrived, sum in rank order (bit-identical on every
+                // rank), + bias, bf16, into y and the mailbox; the consumed words become the sentinel again
+                const size_t cur_off = (size_t)((ep_base + (uint32_t)op.exchange) % 3u) * ((size_t)p.peer.world * p.peer.cap);
+                const float *own = p.peer.base[p.peer.rank & (PEER_MAX_WORLD - 1)];
+                unsigned short *mb = op.mbox_out ? op.mbox_out + mb_cur : nullptr;
+                unsigned long long t0;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+                for (int it = tid; it < n_slots * 16 * MR; it += CH_CONS_THREADS) {
+                    const int tok = it % MR, n = R0 * 16 + it / MR;
+                    if (tok >= op.M) continue;
+                    const uint32_t *srcw = reinterpret_cast<const uint32_t *>(own + cur_off) + (size_t)n * PEER_TOK + tok;
+                    uint32_t wv[PEER_MAX_WORLD];
+                    uint32_t spins = 0;
+                    for (;;) {
+                        bool all = true;
+#pragma unroll
+                        for (int r = 0; r < PEER_MAX_WORLD; ++r) {
+                            wv[r] = 0u;
+                            if (r < p.peer.world)
+                                asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(wv[r]) : "l"(srcw + (size_t)r * p.peer.cap) : "memory");
+                        }
+#pragma unroll
+                        for (int r = 0; r < PEER_MAX_WORLD; ++r) all = all && wv[r] != PEER_EMPTY;
+                        if (all) break;
+                        if ((++spins & 1023u) == 0) {
+                            unsigned long long t1;
+                            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                            if (t1 - t0 > 20000000000ull) __trap();   // 20 s: a peer never arrived -- fail loudly instead of hanging
+                        }
+                    }
+                    float acc = 0.f;
+#pragma unroll
+                    for (int r = 0; r < PEER_MAX_WORLD; ++r) {
+                        if (r < p.peer.world) {
+                            acc += __uint_as_float(wv[r]);
+                            const_cast<uint32_t *>(srcw)[(size_t)r * p.peer.cap] = PEER_EMPTY;
+                        }
+                    }
+                    const float bsv = op.bias ? __bfloat162float(op.bias[n]) : 0.f;
+                    const __nv_bfloat16 r = __float2bfloat16_rn(acc + bsv);
+                    op.y[(size_t)tok * op.N + n] = r;
+                    if (mb) ch_mbox_store(mb + (size_t)tok * op.N + n, r);
+                }
+            }
+        }
         ch_bar_consumers();   // part / xs are free again; this CTA's y stores precede whatever thread 0 releases next
         if (op.arrive_out && tid == 0) asm volatile("red.relaxed.gpu.global.add.u64 [%0], 1;" ::"l"(op.arrive_out) : "memory");
         stamp(o, 3);
     }
     if (p.n_ops > 1 && cta == 0 && tid == 0) *p.runs = run + 1u;   // everybody read `runs` before the first barrier
+    if constexpr (TP) {
+        // the last CTA of this launch to finish advances the rank's exchange epoch (every CTA read it after its
+        // griddepcontrol.wait; the next launch reads it after ITS wait)
+        if (tid == 0 && p.n_exchange > 0) {
+            __threadfence();
+            const int prev = atomicAdd(p.peer.ticket, 1);
+            if (prev == (int)gridDim.x - 1) {
+                *p.peer.ticket = 0;
+                *p.peer.epoch_ptr = ep_base + (uint32_t)p.n_exchange;
+                __threadfence();
+            }
+        }
+    }
 }
 
 // ---- host side ------------------------------------------------------------------------------------------------------
@@ -887,6 +969,8 @@ struct Chain {
     std::vector<w4a16_chain_prologue> pro;   // per linear; norm_weight == null: none
     bool has_prologue = false;
     bool general_k = false;        // some in_features is not a multiple of 4096
+    std::vector<ChainOp> h_ops;    // host copy of the device table (w4a16_chain_set_peer edits it)
+    std::vector<int> dep, barrier; // per linear: producer whose mailbox it reads (-1: none), grid barrier in front of it
     bool persistent = false;       // the chain kernel takes it; otherwise the linears are launched one by one
     std::string why_not;
     ChainOp *d_ops = nullptr;
@@ -901,11 +985,11 @@ struct Chain {
     int MR = 1, mpu = 1, smem = 0, grid = 0;
 };
 
-template <int MR, int MPU, bool PRO, bool GEN>
+template <int MR, int MPU, bool PRO, bool GEN, bool TP>
 static int chain_launch_t(const Chain &c, cudaStream_t stream, bool pdl) {
     static bool attr_set[64] = {};
     if (c.device >= 0 && c.device < 64 && !attr_set[c.device]) {
-        W4_CUDA_OK(cudaFuncSetAttribute(chain_kernel<MR, MPU, PRO, GEN>, cudaFuncAttributeMaxDynamicSharedMemorySize, CH_SMEM_MAX));
+        W4_CUDA_OK(cudaFuncSetAttribute(chain_kernel<MR, MPU, PRO, GEN, TP>, cudaFuncAttributeMaxDynamicSharedMemorySize, CH_SMEM_MAX));
         attr_set[c.device] = true;
     }
     cudaLaunchConfig_t cfg{};
@@ -918,21 +1002,25 @@ static int chain_launch_t(const Chain &c, cudaStream_t stream, bool pdl) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    W4_CUDA_OK(cudaLaunchKernelEx(&cfg, chain_kernel<MR, MPU, PRO, GEN>, c.prm));
+    W4_CUDA_OK(cudaLaunchKernelEx(&cfg, chain_kernel<MR, MPU, PRO, GEN, TP>, c.prm));
     count_launch();
     return 0;
 }
 
 static int chain_launch(const Chain &c, cudaStream_t stream) {
     const bool pdl = gv_env_int("W4A16_NO_PDL", 0) == 0;
-#define W4_CH4(MR_, MPU_)                                                                   \
-    do {                                                                                    \
-        if (c.has_prologue) {                                                               \
-            if (c.general_k) return chain_launch_t<MR_, MPU_, true, true>(c, stream, pdl);  \
-            return chain_launch_t<MR_, MPU_, true, false>(c, stream, pdl);                  \
-        }                                                                                   \
-        if (c.general_k) return chain_launch_t<MR_, MPU_, false, true>(c, stream, pdl);     \
-        return chain_launch_t<MR_, MPU_, false, false>(c, stream, pdl);                     \
+#define W4_CH4(MR_, MPU_)                                                                          \
+    do {                                                                                           \
+        if (c.prm.n_exchange > 0) {   /* tensor-parallel chains: no prologues (rejected at set_peer) */ \
+            if (c.general_k) return chain_launch_t<MR_, MPU_, false, true, true>(c, stream, pdl);  \
+            return chain_launch_t<MR_, MPU_, false, false, true>(c, stream, pdl);                  \
+        }                                                                                          \
+        if (c.has_prologue) {                                                                      \
+            if (c.general_k) return chain_launch_t<MR_, MPU_, true, true, false>(c, stream, pdl);  \
+            return chain_launch_t<MR_, MPU_, true, false, false>(c, stream, pdl);                  \
+        }                                                                                          \
+        if (c.general_k) return chain_launch_t<MR_, MPU_, false, true, false>(c, stream, pdl);     \
+        return chain_launch_t<MR_, MPU_, false, false, false>(c, stream, pdl);                     \
     } while (0)
 #define W4_CH(MR_)                        \
     do {                                  \
@@ -1100,10 +1188,12 @@ static int chain_plan(Chain *c) {
         o.normed_out = pr.norm_weight ? reinterpret_cast<__nv_bfloat16 *>(pr.normed_out) : nullptr;
         o.eps = pr.eps;
         o.add_running = pr.norm_weight && !pr.residual_in && pr.add_running_residual;
+        o.exchange = 0;
     }
     W4_CUDA_OK(cudaMemcpy(c->d_rb, rb.data(), rb.size() * sizeof(int), cudaMemcpyHostToDevice));
     W4_CUDA_OK(cudaMalloc(&c->d_ops, ops.size() * sizeof(ChainOp)));
     W4_CUDA_OK(cudaMemcpy(c->d_ops, ops.data(), ops.size() * sizeof(ChainOp), cudaMemcpyHostToDevice));
+    c->h_ops = ops; c->dep = dep; c->barrier = barrier;
     W4_CUDA_OK(cudaMalloc(&c->d_counter, sizeof(unsigned long long)));
     W4_CUDA_OK(cudaMemset(c->d_counter, 0, sizeof(unsigned long long)));
     W4_CUDA_OK(cudaMalloc(&c->d_runs, sizeof(unsigned int)));
@@ -1122,11 +1212,13 @@ static int chain_plan(Chain *c) {
     p.off_xs = off_xs; p.off_gtab = off_gtab; p.off_part = off_part; p.off_ring = off_ring;
     p.off_res = off_res; p.off_red = off_red;
     p.dbg = c->d_dbg;
+    p.peer = PeerView{}; p.n_exchange = 0;
     c->persistent = true;
     return 0;
 }
 
 int forward_linear(Linear *L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, cudaStream_t stream);   // w4a16_api.cu
+int peer_make_view(void *peer, PeerView *v);                                                             // w4a16_api.cu
 
 }  // namespace w4
 
@@ -1204,6 +1296,56 @@ int w4a16_chain_create_ex(w4a16_chain_t *out, int n, const w4a16_handle_t *handl
     return 0;
 }
 
+int w4a16_chain_set_peer(w4a16_chain_t chain, w4a16_peer_t peer) {
+    Chain *c = reinterpret_cast<Chain *>(chain);
+    if (!c) return fail("chain_set_peer: null chain");
+    if (!c->persistent) return fail("chain_set_peer: the persistent kernel does not take this chain (" + c->why_not + "); use w4a16_forward_row_fused per linear");
+    if (c->has_prologue) return fail("chain_set_peer: prologues and the fused all-reduce are not combined yet");
+    PeerView v{};
+    if (peer_make_view(peer, &v)) return 1;
+    int n_ex = 0, prev_ex = -1;
+    std::vector<ChainOp> ops = c->h_ops;
+    std::vector<int> barrier = c->barrier;
+    for (int i = 0; i < c->n; ++i) {
+        Linear *L = c->lin[i];
+        ops[i].exchange = 0;
+        if (L->tp_mode != W4A16_TP_ROW || L->tp_size <= 1) continue;
+        if (L->tp_size != v.world || L->tp_rank != v.rank) return fail("chain_set_peer: peer group does not match the shard at position " + std::to_string(i));
+        if (L->epilogue != W4A16_EPILOGUE_NONE) return fail("chain_set_peer: a row-parallel linear cannot carry an epilogue");
+        if ((uint64_t)L->d.N * PEER_TOK > v.cap) return fail("chain_set_peer: peer buffers too small for out_features " + std::to_string(L->d.N));
+        ops[i].exchange = ++n_ex;
+        ops[i].bias = L->has_bias ? L->bias : nullptr;          // added after the reduce (parallel_layers.rs:305-311)
+        // Three rotating buffers are enough only if no CTA of this rank can start this all-reduce before every CTA has
+        // finished the previous one: that holds when a chain of hand-overs (mailboxes or a barrier) links the two.
+        if (prev_ex >= 0) {
+            bool linked = false;
+            for (int k = i; k > prev_ex;) {
+                if (barrier[k]) { linked = true; break; }
+                if (c->dep[k] < 0) break;
+                k = c->dep[k];
+                if (k == prev_ex) { linked = true; break; }
+                if (k < prev_ex) break;
+            }
+            if (!linked) barrier[i] = 1;
+        }
+        prev_ex = i;
+    }
+    int n_bar = 0;
+    for (int i = 0; i < c->n; ++i) { ops[i].barrier_before = barrier[i]; n_bar += barrier[i]; }
+    int prev = 0;
+    cudaGetDevice(&prev);
+    if (prev != c->device) cudaSetDevice(c->device);
+    const cudaError_t e = cudaMemcpy(c->d_ops, ops.data(), ops.size() * sizeof(ChainOp), cudaMemcpyHostToDevice);
+    if (prev != c->device) cudaSetDevice(prev);
+    if (e != cudaSuccess) return fail(std::string("chain_set_peer: ") + cudaGetErrorString(e));
+    c->h_ops = ops; c->barrier = barrier;
+    c->n_barriers = n_bar;
+    c->prm.n_barriers = n_bar;
+    c->prm.peer = v;
+    c->prm.n_exchange = n_ex;
+    return 0;
+}
+
 int w4a16_chain_run(w4a16_chain_t chain, w4a16_stream_t stream) {
     Chain *c = reinterpret_cast<Chain *>(chain);
     if (!c) return fail("chain_run: null chain");
@@ -1248,7 +1390,8 @@ const char *w4a16_chain_kernel(w4a16_chain_t chain) {
     if (!c) return "";
     static thread_local std::string s;
     if (c->persistent) {
-        s = "chain_imma (" + std::to_string(c->n_mailboxes) + " mailboxes, " + std::to_string(c->n_barriers) + " barriers)";
+        s = "chain_imma (" + std::to_string(c->n_mailboxes) + " mailboxes, " + std::to_string(c->n_barriers) + " barriers" +
+            (c->prm.n_exchange ? ", " + std::to_string(c->prm.n_exchange) + " fused all-reduces" : std::string()) + ")";
         return s.c_str();
     }
     s = "per_linear (" + c->why_not + ")";

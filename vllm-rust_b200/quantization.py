@@ -729,7 +729,7 @@ class DecodeChain:
     what linear i wrote.  Where the shapes allow it run() is ONE persistent launch (`kernel()` == "chain_imma"),
     otherwise the chain calls the linears one by one."""
 
-    def __init__(self, steps: Sequence, prologues: Optional[Sequence] = None):
+    def __init__(self, steps: Sequence, prologues: Optional[Sequence] = None, peers=None):
         """prologues: per step None or a dict {norm_weight, eps, residual_in, residual_out, normed_out,
         add_running_residual}: residual add + RMSNorm done by the chain kernel while it stages that linear's input
         (input_layernorm / post_attention_layernorm + the residual adds of qwen3_quantized.rs:1043-1075)."""
@@ -776,6 +776,9 @@ class DecodeChain:
                 pro[i].eps = float(pr.get("eps", 1e-6))
                 pro[i].add_running_residual = int(bool(pr.get("add_running_residual", False)))
         check(lib().w4a16_chain_create_ex(ctypes.byref(self._c), n, hs, xs, ys, m, pro))
+        if peers is not None:   # tensor-parallel: the ROW shards all-reduce inside the launch (parallel.PeerGroup)
+            self._peers = peers
+            check(lib().w4a16_chain_set_peer(self._c, peers.ptr()))
         self._n, self._m = n, m
 
     def __del__(self):
