@@ -310,10 +310,17 @@ def run_gpu(args):
     # N = 1 headline: the same 144 linears as ONE DecodeChain (w4a16_chain_run, one persistent launch per step) with the
     # model's data flow -- every linear reads what the previous one wrote, so the order is a true dependency
     chain, chain_kernel, launch = None, None, "cuda-graph replay" if graph is not None else "stream launches"
-    if world == 1 and args.api == "chain":
-        chain = P.DecodeChain(chain_steps(torch, layers, M, dev))
-        chain_kernel = chain.kernel()
-        if not chain_kernel.startswith("chain_imma"):
+    if args.api == "chain" and (world == 1 or peers is not None):
+        # N > 1: one chain per rank over its shards; the row shards all-reduce inside the launch (w4a16_chain_set_peer).
+        # Creation is collective-safe: every rank takes the same branch (same shapes, same peer group state).
+        try:
+            chain = P.DecodeChain(chain_steps(torch, layers, M, dev), peers=peers if world > 1 else None)
+            chain_kernel = chain.kernel()
+            if not chain_kernel.startswith("chain_imma"):
+                chain = None
+        except P.W4A16Error as e:
+            if rank == 0:
+                print(f"bench: chain unavailable ({e}); per-linear launches", file=sys.stderr)
             chain = None
     if chain is not None:
         cgraph = None
@@ -343,7 +350,10 @@ def run_gpu(args):
                    "launch": launch, "pdl": os.environ.get("W4A16_NO_PDL", "0") == "0",
                    "data_flow": ("every linear reads the previous linear's output (bench.chain_steps): true dependencies"
                                  if chain is not None else "static x per shape"),
-                   "allreduce": (None if world == 1 else "fused GEMV epilogue over NVLink peer memory (one kernel, no NCCL launch)"
+                   "allreduce": (None if world == 1 else
+                                 "inside the chain launch: row shards exchange fp32 partials over NVLink peer memory (no NCCL launch)"
+                                 if chain is not None else
+                                 "fused GEMV epilogue over NVLink peer memory (one kernel per linear, no NCCL launch)"
                                  if peers is not None else "ncclAllReduce after the GEMV")},
         "gpu_launches": int(launches_per_step * args.steps),
         "clocks": clk,
@@ -452,6 +462,38 @@ def tp_check(P, torch, dist, dev, nccl, peers, rank, world):
                                  "bit_identical_across_ranks": bool(same), "all_ranks_ok": flags[0].item() == 0})
             res["ok"] = res["ok"] and flags[0].item() == 0
         res["fused_path"] = fused.kernel_for(1) if peers is not None else "ncclAllReduce (no peer group)"
+        if peers is not None:
+            # the chain kernel's in-launch all-reduce: [column shard -> row shard] as one DecodeChain, the row shard's
+            # output against the oracle of the full linear applied to the gathered input, and across ranks
+            Nc = 1024 * world
+            qw2, qz2, sc2, _ = O.make_awq_checkpoint(K, Nc, g, seed=8)
+            col = P.ColumnParallelW4A16Linear(cfg, K, Nc, False, nccl, dev)
+            col.load_weights({"qweight": t_i32(qw2).to(dev), "qzeros": t_i32(qz2).to(dev), "scales": torch.from_numpy(sc2 * np.float16(0.2)).to(dev)})
+            qw3, qz3, sc3, _ = O.make_awq_checkpoint(Nc, N, g, seed=9)
+            q3, z3, sb3 = awq_unpacked(qw3, qz3, sc3)
+            row = P.RowParallelW4A16Linear(cfg, Nc, N, False, nccl, dev)
+            row.load_weights({"qweight": t_i32(qw3).to(dev), "qzeros": t_i32(qz3).to(dev), "scales": torch.from_numpy(sc3).to(dev)})
+            xc = t_bf16_from_bits(O.make_activations(1, K, seed=60)).to(dev)
+            mid = torch.zeros((1, Nc // world), dtype=torch.bfloat16, device=dev)
+            yc = torch.full((1, N), float("nan"), dtype=torch.bfloat16, device=dev)
+            ch = P.DecodeChain([(col, xc, mid), (row, mid, yc)], peers=peers)
+            for _ in range(4):
+                ch.run()
+            torch.cuda.synchronize()
+            parts = [torch.empty_like(mid) for _ in range(world)]
+            dist.all_gather(parts, mid)
+            want = oracle_forward(bits_of(torch.cat(parts, dim=1)), q3, z3, sb3, g)
+            ec = float(np.abs(O.np_bf16_bits_to_f32(bits_of(yc)).astype(np.float64) - want).max()) / float(np.abs(want).max())
+            ys = [torch.empty_like(yc) for _ in range(world)]
+            dist.all_gather(ys, yc)
+            same = all(torch.equal(o.view(torch.int16), yc.view(torch.int16)) for o in ys)
+            flags = torch.tensor([0 if (np.isfinite(ec) and ec <= 1e-2 and same) else 1, int(min(ec, 1e3) * 1e6) if np.isfinite(ec) else 10**9],
+                                 device=dev, dtype=torch.int64)
+            dist.all_reduce(flags, op=dist.ReduceOp.MAX)
+            res["chain"] = {"kernel": ch.kernel(), "row_shard_vs_oracle_max_rel": round(flags[1].item() / 1e6, 6),
+                            "bit_identical_across_ranks": bool(same), "all_ranks_ok": flags[0].item() == 0}
+            res["ok"] = res["ok"] and flags[0].item() == 0
+            del ch
     except Exception as e:   # noqa: BLE001
         res["ok"], res["error"] = False, repr(e)
     return res
