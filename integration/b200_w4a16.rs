@@ -277,6 +277,33 @@ impl DecodeChain {
         check(unsafe { ffi::w4a16_chain_create(&mut c, steps.len() as c_int, hs.as_ptr(), xs.as_ptr(), ys.as_ptr(), m as i64) })?;
         Ok(Self { c, device, _keep: steps.iter().map(|s| (s.1.clone(), s.2.clone())).collect() })
     }
+    /// Same, with the residual adds and RMSNorms between the linears done inside the launch (`prologues[i]` for linear i;
+    /// `norm_weight` null = none): input_layernorm / post_attention_layernorm + half_add_pooled of
+    /// qwen3_quantized.rs:1043-1075.  The tensors behind the raw pointers must outlive the chain.
+    pub fn with_prologues(steps: &[(&B200W4A16Linear, Tensor, Tensor)], m: usize, prologues: &[ffi::W4a16ChainPrologue]) -> Result<Self> {
+        let device = steps.first().map(|s| s.0.device.clone()).ok_or_else(|| candle_core::Error::Msg("empty chain".into()))?;
+        if prologues.len() != steps.len() {
+            candle_core::bail!("DecodeChain: one prologue entry per step");
+        }
+        let hs: Vec<_> = steps.iter().map(|s| s.0.raw()).collect();
+        let mut xs = Vec::with_capacity(steps.len());
+        let mut ys = Vec::with_capacity(steps.len());
+        for (_, x, y) in steps {
+            xs.push(dev_ptr(x)?);
+            ys.push(dev_ptr(y)? as *mut c_void);
+        }
+        let mut c = std::ptr::null_mut();
+        check(unsafe {
+            ffi::w4a16_chain_create_ex(&mut c, steps.len() as c_int, hs.as_ptr(), xs.as_ptr(), ys.as_ptr(), m as i64, prologues.as_ptr())
+        })?;
+        Ok(Self { c, device, _keep: steps.iter().map(|s| (s.1.clone(), s.2.clone())).collect() })
+    }
+    /// Tensor parallel: the ROW shards of the chain all-reduce inside the launch over the group's NVLink buffers
+    /// (replaces the ncclAllReduce of RowParallelLinear::forward, parallel_layers.rs:295-311).  SPMD: every rank builds
+    /// the same chain and runs it the same number of times.
+    pub fn set_peer(&self, peer: &PeerGroup) -> Result<()> {
+        check(unsafe { ffi::w4a16_chain_set_peer(self.c, peer.raw()) })
+    }
     pub fn run(&self) -> Result<()> {
         check(unsafe { ffi::w4a16_chain_run(self.c, stream_ptr(&self.device)?) })
     }
