@@ -1,3 +1,2 @@
 #!/bin/bash
-timeout 900 python -m pytest tests/test_chain_gpu.py -x -q 2>&1 | tail -12
-timeout 300 python tools/decode_ab.py --api chain --chain --cfg "" 2>&1 | grep "\[ab\] "
+timeout 400 python tools/decode_ab.py --cfg "" --cfg "W4A16_GV_L2PF=2" --cfg "W4A16_GV_L2PF=4" --cfg "W4A16_GV_L2PF=8" --cfg "W4A16_GV_L2PF=16" 2>&1 | grep "\[ab\] "

@@ -1,9 +1,6 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 python bench.py > gpurun_out/k_bench.json 2> gpurun_out/k_bench.err; echo "bench rc=$?"; tail -c 400 gpurun_out/k_bench.err
-python - <<'PY'
-import json
-d=json.load(open('gpurun_out/k_bench.json'))
-print(d['value'], d['ms_per_step'], d['per_linear_api']['ms_per_step'], d['e2e']['value'])
-print(json.dumps(d.get('layer_chain'))[:1500])
-PY
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -6
+timeout 1800 python -m pytest tests -m gpu -q -x > gpurun_out/l_all.log 2>&1
+echo "pytest rc=$?" >> gpurun_out/l_all.log
+tail -5 gpurun_out/l_all.log
