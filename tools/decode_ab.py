@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """A/B of launch-time switches on the headline decode step (Qwen3-8B, 36 layers x 4 linears, M tokens): the layers are
 built once; for every configuration the environment is set, the step is captured into a fresh CUDA graph (the switches
-are read at launch, i.e. at capture) and timed.  A development probe, not a test.
+are read at launch, i.e. at capture) and timed.  A development probe, not a test.  Tuning knobs are compiled out of the
+shipped library: build it with `make -C vllm-rust_b200/csrc EXTRA_NVFLAGS=-DW4A16_EXPERIMENT_ENV` first.
     python tools/decode_ab.py --cfg "W4A16_L2PF=0" --cfg "W4A16_L2PF=1" --cfg "W4A16_L2PF=2,W4A16_L2PF_HOPS=2"
 """
 import argparse

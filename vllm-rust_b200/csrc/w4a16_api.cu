@@ -223,7 +223,7 @@ static int env_int_api(const char *name, int dflt) { const char *v = getenv(name
 static int pick_route(const Linear &L, int64_t M) {
     if (g_dispatch == "prefill") return ROUTE_PREFILL;
     if (g_dispatch == "decode") return ROUTE_DECODE;
-    static const int decode_max = std::min<int>((int)DECODE_MAX_M, env_int_api("W4A16_DECODE_MAX_M", 16));
+    static const int decode_max = std::min<int>((int)DECODE_MAX_M, exp_env_int("W4A16_DECODE_MAX_M", 16));
     return M > decode_max ? ROUTE_PREFILL : ROUTE_DECODE;
 }
 
@@ -629,7 +629,7 @@ int w4a16_forward_row_fused(w4a16_handle_t h, const void *x_bf16, void *y_bf16, 
     PeerView v{};
     for (int r = 0; r < c->world; ++r) v.base[r] = c->base[r];
     v.world = c->world; v.rank = c->rank; v.cap = c->cap;
-    v.flags = env_int_api("W4A16_FUSED_EARLY_PDL", 0) ? 1u : 0u;
+    v.flags = exp_env_int("W4A16_FUSED_EARLY_PDL", 0) ? 1u : 0u;
     v.epoch_ptr = c->epoch_dev; v.ticket = reinterpret_cast<int *>(c->epoch_dev + 1);
     // Every rank takes the same branch: the test depends on shape, M and the group only.  The launch counter lives
     // in device memory, so the fused kernel can be captured into a CUDA graph and replayed.

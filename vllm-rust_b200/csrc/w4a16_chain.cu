@@ -1103,7 +1103,7 @@ static int chain_plan(Chain *c) {
     auto hi_y = [&](int i) { return lo_y(i) + (uintptr_t)(M * width(i) * 2); };
     auto overlap = [](uintptr_t a0, uintptr_t a1, uintptr_t b0, uintptr_t b1) { return a0 < b1 && b0 < a1; };
     std::vector<int> dep(n, -1), barrier(n, 0);
-    const bool no_mbox = gv_env_int("W4A16_CHAIN_NO_MAILBOX", 0) != 0;
+    const bool no_mbox = exp_env_int("W4A16_CHAIN_NO_MAILBOX", 0) != 0;
     for (int i = 1; i < n; ++i) {
         for (int j = i - 1; j >= 0; --j) {
             if (!overlap(lo_x(i), hi_x(i), lo_y(j), hi_y(j))) continue;
@@ -1208,7 +1208,7 @@ static int chain_plan(Chain *c) {
     p.counter = c->d_counter; p.runs = c->d_runs;
     p.n_barriers = c->n_barriers; p.mbox_stride = mbox_total;
     p.S = (int)S; p.slot_stride = (int)stride;
-    p.l2pf = std::max(0, gv_env_int("W4A16_CHAIN_L2PF", 6));   // measured on the Qwen3-8B step: 0 / 2 / 4 / 6 / 8 / 12 / 16 stages -> 0.776 / 0.756 / 0.737 / 0.732 / 0.728 / 0.847 / 1.013 ms
+    p.l2pf = std::max(0, exp_env_int("W4A16_CHAIN_L2PF", 6));   // measured on the Qwen3-8B step: 0 / 2 / 4 / 6 / 8 / 12 / 16 stages -> 0.776 / 0.756 / 0.737 / 0.732 / 0.728 / 0.847 / 1.013 ms
     p.off_xs = off_xs; p.off_gtab = off_gtab; p.off_part = off_part; p.off_ring = off_ring;
     p.off_res = off_res; p.off_red = off_red;
     p.dbg = c->d_dbg;

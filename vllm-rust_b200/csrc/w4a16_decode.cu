@@ -313,7 +313,7 @@ static DecodeCfg pick_cfg(const Linear &L, int sm_count) {
     int ctas_x = NR / WR;
     int sc = 1;
     while (ctas_x * sc < 2 * sm_count && (U / (WK * sc * 2)) >= 2 && sc < 16) sc *= 2;
-    int ov_wk = env_int("W4A16_DECODE_WK_SHIFT", -1), ov_sc = env_int("W4A16_DECODE_SC", -1);
+    int ov_wk = exp_env_int("W4A16_DECODE_WK_SHIFT", -1), ov_sc = exp_env_int("W4A16_DECODE_SC", -1);
     if (ov_wk >= 1 && ov_wk <= 3) wk_shift = ov_wk;
     if (ov_sc >= 1 && ov_sc <= 64) sc = ov_sc;
     WK = 1 << wk_shift;

@@ -558,8 +558,8 @@ int gemv_build_table(Linear &L, int sm_count) {
     const int64_t UPR = L.d.K / GV_UNIT_K, UT = L.d.NR * UPR;
     L.gv_grid = 0;
     if (UT >= (int64_t)1 << 30) return 0;   // the register-ring kernel takes it
-    int grid = (int)std::min<int64_t>(UT, (int64_t)sm_count * gv_env_int("W4A16_GEMV_CTAS_PER_SM", 1));
-    const int align = gv_env_int("W4A16_GEMV_ALIGN", 1);   // 1: ranges of whole row blocks (no shared row blocks, coarser balance)
+    int grid = (int)std::min<int64_t>(UT, (int64_t)sm_count * exp_env_int("W4A16_GEMV_CTAS_PER_SM", 1));
+    const int align = exp_env_int("W4A16_GEMV_ALIGN", 1);   // 1: ranges of whole row blocks (no shared row blocks, coarser balance)
     // fewer row blocks than SMs but at least half as many: one row block per CTA beats sharing row blocks across CTAs
     if (align && L.d.NR < grid && 2 * L.d.NR >= grid) grid = (int)L.d.NR;
     const int64_t q = UT / grid, r = UT % grid;
@@ -624,7 +624,7 @@ static GemvPlan gemv_plan(const Linear &L, int64_t M) {
     int64_t S = (budget - fixed) / stage;
     if (S < 3) { budget = GV_SMEM_FULL_SM; S = (budget - fixed) / stage; }
     if (S < 2) return pl;                                            // x does not fit: the register-ring kernel takes it
-    S = std::min<int64_t>(S, std::min<int64_t>(GV_MAX_STAGES, gv_env_int("W4A16_GEMV_STAGES", GV_MAX_STAGES)));
+    S = std::min<int64_t>(S, std::min<int64_t>(GV_MAX_STAGES, exp_env_int("W4A16_GEMV_STAGES", GV_MAX_STAGES)));
     pl.S = (int)S;
     pl.off_wring = (int)off; off += S * GV_STAGE_W_BYTES;
     pl.off_mring = (int)off; off += S * pl.stage_m_bytes;
@@ -634,7 +634,7 @@ static GemvPlan gemv_plan(const Linear &L, int64_t M) {
 }
 
 bool gemv_stream_usable(const Linear &L, int64_t M) {
-    if (gv_env_int("W4A16_NO_GEMV_STREAM", 0)) return false;
+    if (exp_env_int("W4A16_NO_GEMV_STREAM", 0)) return false;
     return gemv_plan(L, M).ok;
 }
 
@@ -687,7 +687,7 @@ int launch_gemv_stream(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y
     p.P = pl.P;
     p.n_stages_ring = pl.S;
     p.fast = L.gv_aligned && (L.d.K % (GV_UNIT_K * GV_STAGE_UNITS) == 0) && pl.stage_m_bytes != 0 &&
-             gv_env_int("W4A16_GEMV_FAST", 1);
+             exp_env_int("W4A16_GEMV_FAST", 1);
     p.stage_m_bytes = pl.stage_m_bytes;
     p.off_xs = pl.off_xs; p.off_gtab = pl.off_gtab; p.off_flags = pl.off_flags; p.off_part = pl.off_part;
     p.off_wring = pl.off_wring; p.off_mring = pl.off_mring;

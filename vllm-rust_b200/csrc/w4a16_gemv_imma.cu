@@ -525,7 +525,7 @@ static ImmaPlan imma_plan(const Linear &L, int64_t M) {
     int64_t D = (GV_SMEM_2CTA - off) / depth;
     if (D < 2) D = (GV_SMEM_FULL_SM - off) / depth;                  // large K x M: one CTA per SM
     if (D < 2) return pl;
-    D = std::min<int64_t>(D, std::min<int64_t>(pl.MR > 4 ? 2 : 3, gv_env_int("W4A16_GEMV_STAGES", 3)));
+    D = std::min<int64_t>(D, std::min<int64_t>(pl.MR > 4 ? 2 : 3, exp_env_int("W4A16_GEMV_STAGES", 3)));
     if (D < 2) D = 2;
     pl.S = (int)D;
     pl.stage_m_bytes = 0;
@@ -537,7 +537,7 @@ static ImmaPlan imma_plan(const Linear &L, int64_t M) {
 }
 
 bool gemv_imma_usable(const Linear &L, int64_t M) {
-    if (gv_env_int("W4A16_NO_GEMV_IMMA", 0)) return false;
+    if (exp_env_int("W4A16_NO_GEMV_IMMA", 0)) return false;
     return imma_plan(L, M).ok;
 }
 
@@ -601,8 +601,8 @@ int launch_gemv_imma_peer(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16
     // A launch with the fused exchange is launched programmatically early (its weight prefetch runs under the previous
     // kernel) from 4 ranks on, where the shards are a few microseconds long: Llama-3-70B step at TP = 2 / 4 / 8 without ->
     // with the attribute 0.972 -> 1.078 / 0.723 -> 0.713 / 0.632 -> 0.598 ms.  It never releases ITS dependents early.
-    const bool pdl = gv_env_int("W4A16_NO_PDL", 0) == 0 && (!peer || gv_env_int("W4A16_FUSED_PDL_ATTR", peer->world >= 4 ? 1 : 0));
-    const bool reg = (L.d.K % (32 * GV_UNIT_K)) == 0 && gv_env_int("W4A16_GV_REG", 1);
+    const bool pdl = gv_env_int("W4A16_NO_PDL", 0) == 0 && (!peer || exp_env_int("W4A16_FUSED_PDL_ATTR", peer->world >= 4 ? 1 : 0));
+    const bool reg = (L.d.K % (32 * GV_UNIT_K)) == 0 && exp_env_int("W4A16_GV_REG", 1);
 #define W4_GI3(MR_, MPU_, FUSED_)                                                      \
     do {                                                                               \
         if (reg) {                                                                     \

@@ -367,7 +367,7 @@ static Imma2Plan imma2_plan(const Linear &L, int64_t M) {
 }
 
 bool gemv_imma2_usable(const Linear &L, int64_t M) {
-    if (gv_env_int("W4A16_NO_GEMV_IMMA2", 0)) return false;
+    if (exp_env_int("W4A16_NO_GEMV_IMMA2", 0)) return false;
     return imma2_plan(L, M).ok;
 }
 

@@ -5,6 +5,7 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include <atomic>
 #include <string>
@@ -28,6 +29,32 @@ int fail(const std::string &msg);  // sets the error, returns 1
 
 extern std::atomic<uint64_t> g_kernel_launches;
 inline void count_launch() { g_kernel_launches.fetch_add(1, std::memory_order_relaxed); }
+
+// ---- environment switches -----------------------------------------------------
+// The library reads a handful of DOCUMENTED variables at run time: W4A16_GV_DEBUG (per-CTA timing stamps), W4A16_NO_PDL
+// (no programmatic launches), W4A16_NO_FUSED_AR / W4A16_NO_CHAIN_KERNEL (fall back to NCCL / to per-linear launches),
+// W4A16_IMMA8 (opt-in two-token-tile GEMV, parity-tested).  Every tuning / experiment knob (kernel selection, stage
+// counts, split-K model constants, prefetch distance ...) is compiled out of the shipped library and only read when it
+// is built with -DW4A16_EXPERIMENT_ENV (make EXTRA_NVFLAGS=-DW4A16_EXPERIMENT_ENV): the tools under tools/ say when
+// they need that.
+inline int exp_env_int(const char *name, int dflt) {
+#ifdef W4A16_EXPERIMENT_ENV
+    const char *v = getenv(name);
+    return v && *v ? atoi(v) : dflt;
+#else
+    (void)name;
+    return dflt;
+#endif
+}
+inline double exp_env_double(const char *name, double dflt) {
+#ifdef W4A16_EXPERIMENT_ENV
+    const char *v = getenv(name);
+    return v && *v ? atof(v) : dflt;
+#else
+    (void)name;
+    return dflt;
+#endif
+}
 
 // ---- per-device facts ----------------------------------------------------------
 struct DeviceScratch {

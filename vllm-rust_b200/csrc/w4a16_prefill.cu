@@ -609,9 +609,9 @@ int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
         // qkv / o at M = 64 (split wins by 8-11 us), M = 128 (by ~4 us) and M = 256 (split LOSES 9-14 us).
         int ks = 1;
         {
-            static const int forced = getenv("W4A16_PF_KSPLIT") ? atoi(getenv("W4A16_PF_KSPLIT")) : 0;
-            static const int c_fix = getenv("W4A16_PF_KSPLIT_FIX") ? atoi(getenv("W4A16_PF_KSPLIT_FIX")) : 6;
-            static const double c_row = getenv("W4A16_PF_KSPLIT_ROW") ? atof(getenv("W4A16_PF_KSPLIT_ROW")) : 0.06;
+            static const int forced = exp_env_int("W4A16_PF_KSPLIT", 0);
+            static const int c_fix = exp_env_int("W4A16_PF_KSPLIT_FIX", 6);
+            static const double c_row = exp_env_double("W4A16_PF_KSPLIT_ROW", 0.06);
             const int rows = (int)std::min<int64_t>(M, TM);
             const int cands[6] = {1, 2, 3, 4, 6, 8};
             double best = -1;
@@ -625,7 +625,7 @@ int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
             }
             if (forced > 0 && kblks % (2 * forced) == 0) ks = forced;
         }
-        static const bool off = getenv("W4A16_PF_NO_SPLITK") && atoi(getenv("W4A16_PF_NO_SPLITK"));
+        static const bool off = exp_env_int("W4A16_PF_NO_SPLITK", 0) != 0;
         if (ks > 1 && !off && nm <= PF_MAX_SPLIT_TILES) {
             float *part = nullptr; int *tickets = nullptr;
             if (splitk_scratch(L.device, (size_t)ks * M * L.d.N * sizeof(float), stream, &part, &tickets) == 0 && part) {
@@ -634,7 +634,7 @@ int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
         }
         p.kblks_tile = kblks / p.ksplit;
     }
-    { const char *dv = getenv("W4A16_PF_DEBUG"); p.debug = dv ? atoi(dv) : 0; }
+    p.debug = exp_env_int("W4A16_PF_DEBUG", 0);
     static unsigned long long *dbg_buf = nullptr;
     p.dbg = nullptr;
     if (p.debug & 4) {
@@ -647,7 +647,7 @@ int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
     const int grid = std::min(ntiles, L.scratch->sm_count);
     const int gps = gs == 32 ? 2 : 1;
     // pairs of CTAs share every x tile (TMA multicast) when the two n-tiles of a pair exist for every m-tile
-    static const bool no_cl2 = getenv("W4A16_PF_NO_CLUSTER") && atoi(getenv("W4A16_PF_NO_CLUSTER"));
+    static const bool no_cl2 = exp_env_int("W4A16_PF_NO_CLUSTER", 0) != 0;
     bool cl2 = TM == 256 && p.ksplit == 1 && (p.n_tiles % 2) == 0 && grid >= 2 && !no_cl2 && !(p.debug & 3);
 
     int rc = 2;
