@@ -392,6 +392,23 @@ def run_gpu(args):
             out["gptq_act_order"] = gptq_act_order(P, torch, dev, peaks)
             out["reference_gpu"] = reference_gpu(torch, dev, peaks)
             out["cpu_baseline"] = cpu_baseline()
+    elif chain is not None:
+        # end to end at N > 1: every rank feeds its chain from pinned host memory and reads the last linear's output back
+        # (w4a16_chain_run_host: H2D, the tensor-parallel chain, D2H, sync); SPMD, wall clock, MAX over ranks
+        hx = torch.randn((M, layers[0][3])).mul_(0.05).to(torch.bfloat16).pin_memory()
+        hy = torch.empty((M, layers[-1][4]), dtype=torch.bfloat16).pin_memory()
+        n_e2e = max(3, min(args.steps, 20))
+        chain.run_host(hx, hy)
+        dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(n_e2e):
+            chain.run_host(hx, hy)
+        dt = torch.tensor([(time.perf_counter() - t0) / n_e2e], device=dev, dtype=torch.float64)
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            out["e2e"] = {"value": round(step_bytes / float(dt.item()) / 1e9, 1), "unit": "GB/s", "ms_per_step": round(float(dt.item()) * 1e3, 3),
+                          "h2d_bytes_per_step": int(hx.numel() * 2) * world, "d2h_bytes_per_step": int(hy.numel() * 2) * world,
+                          "api": "w4a16_chain_run_host on every rank (pinned host x in, y of the last linear out, sync per step); max over ranks"}
     elif rank == 0:
         out["e2e"] = {"value": None, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
                       "note": "host-buffer path measured at N=1 only"}
@@ -543,6 +560,10 @@ def same_workload_1gpu(P, torch, dev, shapes, n_layers, args):
     def step():
         for name, K, N, Kl, Nl, mode, lin in layers:
             lin.forward_into(xs[K], ys[N])
+    if args.api == "chain":    # the same API the N > 1 headline uses: one DecodeChain launch per step
+        chain = P.DecodeChain(chain_steps(torch, layers, 1, dev))
+        if chain.kernel().startswith("chain_imma"):
+            step = chain.run
     us = time_launches(torch, dev, step, 1, target_ms=30.0, max_reps=30)
     return round(us / 1e3, 4)
 
