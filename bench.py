@@ -375,6 +375,21 @@ def run_gpu(args):
                        "frac_of_spec_8TBs": round(achieved / 8000.0, 4),
                        "algorithmic_bytes_per_launch": int(per_launch_bytes)}
     if rank == 0 and world == 1:
+        if chain is not None:
+            # the same step with 2 and 4 tokens (multi-token decode): widths that agree are real hand-overs (o -> gate_up,
+            # down -> next qkv), the others (qkv -> o, gate_up -> down: the model has attention / silu*mul there) read
+            # their own static x and are not ordered against their predecessor -- an upper-side figure, not the headline
+            out["chain_m"] = []
+            for Mm in (2, 4):
+                try:
+                    cm = P.DecodeChain(chain_steps(torch, layers, Mm, dev))
+                    us = time_launches(torch, dev, cm.run, 1, target_ms=20.0, max_reps=40)
+                    sb = sum(algo_bytes(Mm, K, N) for _, K, N, *_ in layers)
+                    out["chain_m"].append({"M": Mm, "ms_per_step": round(us / 1e3, 4), "GBps": round(sb / (us * 1e-6) / 1e9, 1),
+                                           "frac_measured_hbm": round(sb / (us * 1e-6) / 1e9 / peaks["hbm_gbs"], 4), "kernel": cm.kernel()})
+                    del cm
+                except P.W4A16Error as e:
+                    out["chain_m"].append({"M": Mm, "unsupported": str(e)})
         if not args.quick:
             if chain is not None:
                 out["e2e"] = e2e_chain(P, torch, dev, chain, layers, args)

@@ -1,7 +1,11 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 1800 python -m pytest tests -m gpu -q -x > gpurun_out/l_all.log 2>&1
-echo "pytest rc=$?" >> gpurun_out/l_all.log
-tail -4 gpurun_out/l_all.log
-timeout 900 python bench.py --quick > gpurun_out/s_bench.json 2> gpurun_out/s_bench.err; echo "bench rc=$?"
-grep -o '"value": [0-9.]*, "unit": "GB/s", "n_gpus": 1, "steps": [0-9]*, "warmup": [0-9]*, "ms_per_step": [0-9.]*' gpurun_out/s_bench.json
+timeout 900 python -m pytest tests/test_chain_gpu.py -q -x 2>&1 | tail -2
+timeout 900 python bench.py > gpurun_out/k_bench.json 2> gpurun_out/k_bench.err; echo "bench rc=$?"; tail -c 300 gpurun_out/k_bench.err
+python - <<'PY'
+import json
+d=json.load(open('gpurun_out/k_bench.json'))
+print(d['value'], d['ms_per_step'], d['per_linear_api']['ms_per_step'], d['e2e']['value'])
+print(json.dumps(d.get('chain_m')))
+print([ (p.get('M'), p.get('ms_per_step')) for p in d['layer_chain']['points']])
+PY

@@ -1084,7 +1084,7 @@ static int chain_plan(Chain *c) {
     }
     const int64_t stride = 32 * (GV_UNIT_BYTES + c->mpu * META_BYTES);
     int64_t S = (CH_SMEM_MAX - off) / stride;
-    if (S < 3) { c->why_not = "activations leave no room for a ring of 3 stages"; return 0; }
+    if (S < 2) { c->why_not = "activations leave no room for a ring of 2 stages"; return 0; }
     S = std::min<int64_t>(S, CH_MAX_STAGES);
     const int off_ring = (int)off; off += S * stride;
     c->smem = (int)off;
