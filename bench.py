@@ -787,7 +787,38 @@ def gptq_act_order(P, torch, dev, peaks):
                          "kernel": lins[0].kernel_for(M)})
         del lins
         torch.cuda.empty_cache()
-    return {"workload": "Qwen3-4B GPTQ int4 g128, act-order g_idx (random permutation of groups)", "points": rows}
+    # the whole decode step of the model as one DecodeChain: 36 layers x (qkv, o, gate_up, down), every linear gathering
+    # its act-order x from the previous linear's mailbox inside the launch; the same step as per-linear launches beside it
+    step = {"layers": 36, "points": []}
+    layers = []
+    for li in range(36):
+        for name, K, N in QWEN3_4B_GPTQ:
+            lin = cfg.create_linear(K, N, False, dev)
+            lin.load_weights(rand_gptq_act_order(torch, K, N, dev))
+            lin.reserve(4)
+            layers.append((name, K, N, K, N, None, lin))
+    for M in (1, 2, 4):
+        sb = sum(algo_bytes(M, K, N) for _, K, N, *_ in layers)
+        steps = chain_steps(torch, layers, M, dev)
+        pt = {"M": M}
+        try:
+            ch = P.DecodeChain(steps)
+            us = time_launches(torch, dev, ch.run, 1, target_ms=20.0, max_reps=40)
+            pt.update({"chain_ms_per_step": round(us / 1e3, 4), "chain_GBps": round(sb / (us * 1e-6) / 1e9, 1),
+                       "chain_frac_measured_hbm": round(sb / (us * 1e-6) / 1e9 / peaks["hbm_gbs"], 4), "kernel": ch.kernel()})
+            del ch
+        except P.W4A16Error as e:
+            pt["chain_unsupported"] = str(e)
+
+        def per_linear():
+            for lin, x, y in steps:
+                lin.forward_into(x, y)
+        us = time_launches(torch, dev, per_linear, 1, target_ms=20.0, max_reps=40)
+        pt.update({"per_linear_ms_per_step": round(us / 1e3, 4), "per_linear_GBps": round(sb / (us * 1e-6) / 1e9, 1)})
+        step["points"].append(pt)
+    del layers
+    torch.cuda.empty_cache()
+    return {"workload": "Qwen3-4B GPTQ int4 g128, act-order g_idx (random permutation of groups)", "points": rows, "decode_step": step}
 
 
 def reference_gpu(torch, dev, peaks):

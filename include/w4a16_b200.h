@@ -223,8 +223,9 @@ int w4a16_forward_row_fused(w4a16_handle_t h, const void *x_bf16, void *y_bf16, 
  * graph (engine/cuda_graph.rs).  A chain is that fixed sequence for M <= 4 tokens as one
  * object: linear i reads x[i] and writes y[i], in order, and linear i+1 may read what
  * linear i wrote (x[i+1] == y[i], or any overlap).  Where the shapes allow it (one group
- * size of 32 / 64 / 128 for all linears, no act-order gather, M <= 4 and the staged
- * activations leaving room for the weight ring) chain_run is ONE persistent launch: one CTA per SM streams every linear's weights
+ * size of 32 / 64 / 128 for all linears, M <= 4 and the staged activations leaving room
+ * for the weight ring; act-order linears included: their gather happens inside the
+ * launch) chain_run is ONE persistent launch: one CTA per SM streams every linear's weights
  * through one shared-memory ring that stays full across the boundaries between linears, and
  * consecutive linears are separated by a grid-wide barrier.  Otherwise chain_run makes the
  * n w4a16_forward_into calls itself (w4a16_chain_kernel tells which).  Results: those of

@@ -372,3 +372,40 @@ def test_chain_of_gptq_formats(product):
     assert_close_ref(bits_of(ys[0]), oracle_forward(bits_of(xs[0]), *zp_ck, g), "gptq zero-point")
     assert_close_ref(bits_of(ys[1]), oracle_forward(bits_of(xs[1]), sym_ck[0], None, sym_ck[2], g, zero_mode=1), "gptq symmetric")
     assert_close_ref(bits_of(ys[2]), oracle_forward(bits_of(xs[2]), *awq_ck[:3], g), "awq")
+
+
+@pytest.mark.parametrize("shared", [False, True])
+@pytest.mark.parametrize("M", [1, 3])
+def test_act_order_linears_in_a_chain(product, M, shared):
+    """GPTQ act-order (g_idx): the chain does the gather of x[:, perm] itself (BASELINE config 4 shapes, scaled down).
+    Linear 0 reads the chain's input: the grid gathers it once into an ingest mailbox.  Linear 1 reads linear 0's output:
+    alone (shared=False) its producer scatters into the mailbox in linear 1's order; together with a second act-order
+    reader of the same output (shared=True) both gather from the shared mailbox into ingest mailboxes of their own."""
+    from helpers import gptq_unpacked
+    g = 128
+    shapes = [(2560, 4096), (4096, 2560)] + ([(4096, 1024)] if shared else [])
+    rng = np.random.default_rng(11)
+    lins, cks = [], []
+    for i, (K, N) in enumerate(shapes):
+        qw, qz, sc, _ = O.make_gptq_checkpoint(K, N, g, seed=90 + i)
+        sc = (sc * np.float16(0.3)).astype(np.float16)
+        g_idx = rng.permutation(np.repeat(np.arange(K // g, dtype=np.int32), g)).astype(np.int32)
+        lin = product.GptqConfig(4, g, True).create_linear(K, N, False, DEV)
+        lin.load_weights({"qweight": t_i32(qw), "qzeros": t_i32(qz), "scales": torch.from_numpy(sc), "g_idx": torch.from_numpy(g_idx)})
+        lins.append(lin)
+        cks.append(gptq_unpacked(qw, qz, sc) + (g_idx,))
+    x0 = torch.zeros((M, 2560), dtype=torch.bfloat16, device=DEV)
+    y0 = torch.zeros((M, 4096), dtype=torch.bfloat16, device=DEV)
+    y1 = torch.zeros((M, 2560), dtype=torch.bfloat16, device=DEV)
+    y2 = torch.zeros((M, 1024), dtype=torch.bfloat16, device=DEV)
+    steps = [(lins[0], x0, y0), (lins[1], y0, y1)] + ([(lins[2], y0, y2)] if shared else [])
+    chain = product.DecodeChain(steps)
+    assert chain.kernel() == "chain_imma (1 mailboxes, 0 barriers)", chain.kernel()
+    for rep in range(4):                       # both parities of every mailbox, twice
+        x0.copy_(t_bf16_from_bits(O.make_activations(M, 2560, seed=120 + rep)).to(DEV))
+        chain.run()
+        torch.cuda.synchronize()
+        outs = [(x0, y0), (y0, y1)] + ([(y0, y2)] if shared else [])
+        for i, (xin, yout) in enumerate(outs):
+            q, z, sb, gi = cks[i]
+            assert_close_ref(bits_of(yout), oracle_forward(bits_of(xin), q, z, sb, g, g_idx=gi), f"act-order linear {i} rep {rep}")

@@ -1,5 +1,2 @@
 #!/bin/bash
-for m in 2 4; do
-timeout 300 python tools/decode_ab.py --m $m --api chain --chain --cfg "" 2>&1 | grep "\[ab\] "
-timeout 300 python tools/decode_ab.py --m $m --cfg "" 2>&1 | grep "\[ab\] "
-done
+timeout 900 python -m pytest tests/test_chain_gpu.py -x -q 2>&1 | tail -8

@@ -58,6 +58,21 @@ struct ChainOp {
     float eps;
     int add_running;                       // h = x + the residual the previous prologue of the chain left in shared memory
     int exchange;                          // row-parallel shard with a peer group: 1-based index among the chain's all-reduces, else 0
+    const int32_t *perm;                   // host-side bookkeeping only (act-order permutation before it becomes scatter / ingest)
+    // The (single) reader of this linear's mailbox is an act-order linear: columns [sc_off, sc_off + sc_len) of the mailbox
+    // are stored in THE READER'S tiled order (column sc_off + c at sc_off + scatter[c]), so that it reads a gathered row
+    // sequentially -- the gather costs one index load per produced element instead of 148 CTAs gathering the whole row.
+    const int32_t *scatter;
+    int sc_off, sc_len;
+    // An act-order linear whose x does NOT come from a mailbox it owns alone (the chain's input, a shared mailbox, a
+    // buffer behind a barrier): the grid gathers x[:, perm] ONCE, every CTA a slice, into this chain-owned mailbox
+    // (ingest_perm = the permutation, ingest_src = where x really is), and then reads it like any other mailbox.
+    const int32_t *ingest_perm;
+    const unsigned short *ingest_src;      // parity-0 address if ingest_src_mbox, else the caller's buffer
+    int ingest_src_mbox;
+    const unsigned long long *ingest_src_arrive;
+    unsigned short *ingest;                // parity-0 address of the gathered copy (== mbox_in of this linear)
+    unsigned long long *ingest_arrive;     // (== arrive_in of this linear)
 };
 
 struct ChainParams {
@@ -120,6 +135,11 @@ __device__ __forceinline__ int ch_group_add(int v, uint32_t gmask, int lane) {
     } else {
         return ch_redux_add(v, gmask);
     }
+}
+// column of a mailbox row where output column `col` goes (see ChainOp::scatter)
+__device__ __forceinline__ int ch_mbox_col(const int32_t *scatter, int sc_off, int sc_len, int col) {
+    const int c = col - sc_off;
+    return scatter && c >= 0 && c < sc_len ? sc_off + __ldg(scatter + c) : col;
 }
 // a value can never be the sentinel: 0xFFFF (a NaN) is stored as the canonical NaN 0x7FFF
 __device__ __forceinline__ void ch_mbox_store(unsigned short *p, __nv_bfloat16 v) {
@@ -210,7 +230,9 @@ __device__ __forceinline__ void ch_prologue_pass1(const ChainOp &op, const uint4
 // One batch of NB 16-byte pieces per thread (pieces base + r * 512 + tid).  poll: x is a mailbox (see ChainOp): every
 // piece is re-read until none of its eight values is the sentinel.  The arithmetic of the NB pieces runs side by side
 // (independent dependency chains), the shared-memory stores follow.
-template <int MR, int MPU, int NB, bool NORM>
+// MODE 0: x from the caller's buffer / a mailbox; 1: x16 is the shared-memory residual of a prologue, scaled by
+// inv_rms * gamma on the way.
+template <int MR, int MPU, int NB, int MODE>
 __device__ __forceinline__ void ch_stage_batch(const uint4 *x16, uint8_t *xs, int2 *gtab, int ppr, int total, int base, int tid, int lane,
                                                bool poll, unsigned long long *dbg_valid, const uint4 *norm_w, const float *inv_rms,
                                                uint4 *normed_out) {
@@ -221,10 +243,10 @@ __device__ __forceinline__ void ch_stage_batch(const uint4 *x16, uint8_t *xs, in
 #pragma unroll
     for (int r = 0; r < NB; ++r) {
         const int i = base + r * CH_CONS_THREADS + tid;
-        if constexpr (NORM) v[r] = i < total ? x16[i] : make_uint4(0, 0, 0, 0);
+        if constexpr (MODE != 0) v[r] = i < total ? x16[i] : make_uint4(0, 0, 0, 0);
         else v[r] = i < total ? (poll ? ch_ld_relaxed(x16 + i) : __ldcg(x16 + i)) : make_uint4(0, 0, 0, 0);
     }
-    if constexpr (NORM) {   // x16 is the shared-memory residual h of the prologue: the linear consumes bf16(h * inv_rms * gamma)
+    if constexpr (MODE == 1) {   // x16 is the shared-memory residual h of the prologue: the linear consumes bf16(h * inv_rms * gamma)
 #pragma unroll
         for (int r = 0; r < NB; ++r) {
             const int i = base + r * CH_CONS_THREADS + tid;
@@ -241,7 +263,7 @@ __device__ __forceinline__ void ch_stage_batch(const uint4 *x16, uint8_t *xs, in
             }
         }
     }
-    if (!NORM && poll) {
+    if (MODE == 0 && poll) {
         uint32_t spins = 0;
         for (;;) {
             bool bad[NB], any = false;
@@ -341,7 +363,7 @@ __device__ __forceinline__ void ch_stage_batch(const uint4 *x16, uint8_t *xs, in
 
 // Activation staging of one linear by the 512 consumer threads: the arithmetic of gemv_imma_kernel (per-(group, token)
 // power-of-two scale, two signed-byte planes in B-fragment order, integer group sums, Inf / NaN poison the group).
-template <int MR, int MPU, bool NORM = false>
+template <int MR, int MPU, int MODE = 0>
 __device__ __forceinline__ void ch_stage_x(const __nv_bfloat16 *x, uint8_t *xs, int2 *gtab, int M, int K, int tid, int lane, bool poll,
                                            unsigned long long *dbg_valid, const uint4 *norm_w = nullptr, const float *inv_rms = nullptr,
                                            uint4 *normed_out = nullptr) {
@@ -349,10 +371,10 @@ __device__ __forceinline__ void ch_stage_x(const __nv_bfloat16 *x, uint8_t *xs, 
     const uint4 *x16 = reinterpret_cast<const uint4 *>(x);
     int base = 0;
     for (; total - base > 2 * CH_CONS_THREADS; base += 3 * CH_CONS_THREADS)   // (the batch guards pieces past the end)
-        ch_stage_batch<MR, MPU, 3, NORM>(x16, xs, gtab, ppr, total, base, tid, lane, poll, dbg_valid, norm_w, inv_rms, normed_out);
+        ch_stage_batch<MR, MPU, 3, MODE>(x16, xs, gtab, ppr, total, base, tid, lane, poll, dbg_valid, norm_w, inv_rms, normed_out);
     const int left = (total - base + CH_CONS_THREADS - 1) / CH_CONS_THREADS;   // 0..2 (warp-uniform)
-    if (left == 2) ch_stage_batch<MR, MPU, 2, NORM>(x16, xs, gtab, ppr, total, base, tid, lane, poll, dbg_valid, norm_w, inv_rms, normed_out);
-    else if (left == 1) ch_stage_batch<MR, MPU, 1, NORM>(x16, xs, gtab, ppr, total, base, tid, lane, poll, dbg_valid, norm_w, inv_rms, normed_out);
+    if (left == 2) ch_stage_batch<MR, MPU, 2, MODE>(x16, xs, gtab, ppr, total, base, tid, lane, poll, dbg_valid, norm_w, inv_rms, normed_out);
+    else if (left == 1) ch_stage_batch<MR, MPU, 1, MODE>(x16, xs, gtab, ppr, total, base, tid, lane, poll, dbg_valid, norm_w, inv_rms, normed_out);
 }
 
 // The row blocks of one linear, stage after stage from the ring; every warp takes two units (wi, wi + 16) of every
@@ -799,6 +821,60 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
         }
         stamp(o, 0);
         if (o + 1 == p.n_ops) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+        if constexpr (GEN) {
+            if (op.ingest) {
+                // cooperative act-order gather: this CTA's slice of x[:, perm] into the ingest mailbox of this run
+                const unsigned short *src = op.ingest_src + (op.ingest_src_mbox ? mb_cur : 0);
+                if (op.ingest_src_mbox) {      // the source is another linear's mailbox: wait for its arrival hint first
+                    if (tid == 0) {
+                        const unsigned long long target = ((unsigned long long)run + 1ull) * (unsigned long long)grid;
+                        unsigned long long seen;
+                        uint32_t spins = 0;
+                        do {
+                            asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(seen) : "l"(op.ingest_src_arrive) : "memory");
+                            if (++spins > GV_SPIN_LIMIT) __trap();
+                        } while (seen < target);
+                    }
+                    ch_bar_consumers();
+                }
+                uint4 *dst = reinterpret_cast<uint4 *>(op.ingest + mb_cur);
+                const int ppr = op.K >> 3, total = op.M * ppr;
+                for (int i = cta + tid * grid; i < total; i += grid * CH_CONS_THREADS) {
+                    const int m = i / ppr, c = i - m * ppr;
+                    const int4 p0 = __ldg(reinterpret_cast<const int4 *>(op.ingest_perm + 8 * c)), p1 = __ldg(reinterpret_cast<const int4 *>(op.ingest_perm + 8 * c) + 1);
+                    const int idx[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+                    const unsigned short *row = src + (size_t)m * op.K;
+                    unsigned short e[8];
+                    uint32_t spins = 0;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) asm volatile("ld.relaxed.gpu.global.u16 %0, [%1];" : "=h"(e[j]) : "l"(row + idx[j]) : "memory");
+                    for (;;) {
+                        bool any = false;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            if (op.ingest_src_mbox && e[j] == 0xFFFFu) {
+                                any = true;
+                                asm volatile("ld.relaxed.gpu.global.u16 %0, [%1];" : "=h"(e[j]) : "l"(row + idx[j]) : "memory");
+                            }
+                        if (!any) break;
+                        if (++spins > GV_SPIN_LIMIT) __trap();
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) if (e[j] == 0xFFFFu) e[j] = 0x7FFFu;       // never store the sentinel as data
+                    uint4 v;
+                    v.x = (uint32_t)e[0] | ((uint32_t)e[1] << 16); v.y = (uint32_t)e[2] | ((uint32_t)e[3] << 16);
+                    v.z = (uint32_t)e[4] | ((uint32_t)e[5] << 16); v.w = (uint32_t)e[6] | ((uint32_t)e[7] << 16);
+                    asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(dst + i), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+                }
+                if (op.ingest_src_mbox) {      // what was read from the shared mailbox becomes the sentinel again in its OTHER parity
+                    uint4 *other = reinterpret_cast<uint4 *>(const_cast<unsigned short *>(op.ingest_src) + mb_nxt);
+                    for (int i = cta + tid * grid; i < total; i += grid * CH_CONS_THREADS)
+                        other[i] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+                }
+                ch_bar_consumers();
+                if (tid == 0) asm volatile("red.relaxed.gpu.global.add.u64 [%0], 1;" ::"l"(op.ingest_arrive) : "memory");
+            }
+        }
         const bool poll = op.mbox_in != nullptr;
         if (poll) {
             if (tid == 0) {
@@ -821,7 +897,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
             uint4 *res = reinterpret_cast<uint4 *>(ch_smem + p.off_res);
             float *red = reinterpret_cast<float *>(ch_smem + p.off_red);
             ch_prologue_pass1<MR>(op, reinterpret_cast<const uint4 *>(xsrc), poll, res, red, tid, lane, warp, cta == 0);
-            ch_stage_x<MR, MPU, true>(reinterpret_cast<const __nv_bfloat16 *>(res), xs, gtab, op.M, op.K, tid, lane, false, nullptr,
+            ch_stage_x<MR, MPU, 1>(reinterpret_cast<const __nv_bfloat16 *>(res), xs, gtab, op.M, op.K, tid, lane, false, nullptr,
                                 reinterpret_cast<const uint4 *>(op.norm_w), red,
                                 cta == 0 ? reinterpret_cast<uint4 *>(op.normed_out) : nullptr);
           }
@@ -879,16 +955,21 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
                 const float b1 = op.bias ? __bfloat162float(op.bias[n0 + 8]) : 0.f;
                 unsigned short *mb = op.mbox_out ? op.mbox_out + mb_cur : nullptr;
                 if (op.swiglu) {   // rows g / g+8 are (gate, up) of output column 8 R + g
-                    const size_t at = (size_t)tok * (op.N >> 1) + (n0 >> 4) * 8 + (n0 & 7);
+                    const int col = (n0 >> 4) * 8 + (n0 & 7);
+                    const size_t row = (size_t)tok * (op.N >> 1);
                     const __nv_bfloat16 r = swiglu_bf16(v.x + b0, v.y + b1);
-                    op.y[at] = r;
-                    if (mb) ch_mbox_store(mb + at, r);
+                    op.y[row + col] = r;
+                    if (mb) ch_mbox_store(mb + row + ch_mbox_col(op.scatter, op.sc_off, op.sc_len, col), r);
                 } else {
                     const size_t at = (size_t)tok * op.N + n0;
                     const __nv_bfloat16 r0 = __float2bfloat16_rn(v.x + b0), r1 = __float2bfloat16_rn(v.y + b1);
                     op.y[at] = r0;
                     op.y[at + 8] = r1;
-                    if (mb) { ch_mbox_store(mb + at, r0); ch_mbox_store(mb + at + 8, r1); }
+                    if (mb) {
+                        const size_t row = (size_t)tok * op.N;
+                        ch_mbox_store(mb + row + ch_mbox_col(op.scatter, op.sc_off, op.sc_len, n0), r0);
+                        ch_mbox_store(mb + row + ch_mbox_col(op.scatter, op.sc_off, op.sc_len, n0 + 8), r1);
+                    }
                 }
             }
         }
@@ -935,7 +1016,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_kernel(const ChainParams 
                     const float bsv = op.bias ? __bfloat162float(op.bias[n]) : 0.f;
                     const __nv_bfloat16 r = __float2bfloat16_rn(acc + bsv);
                     op.y[(size_t)tok * op.N + n] = r;
-                    if (mb) ch_mbox_store(mb + (size_t)tok * op.N + n, r);
+                    if (mb) ch_mbox_store(mb + (size_t)tok * op.N + ch_mbox_col(op.scatter, op.sc_off, op.sc_len, n), r);
                 }
             }
         }
@@ -978,6 +1059,7 @@ struct Chain {
     unsigned long long *d_counter = nullptr;
     unsigned int *d_runs = nullptr;
     unsigned short *d_mbox = nullptr;
+    std::vector<int32_t *> d_scatter;      // inverse act-order permutations handed to the producers of act-order linears
     unsigned long long *d_arrive = nullptr;
     int n_mailboxes = 0, n_barriers = 0;
     unsigned long long *d_dbg = nullptr;
@@ -1040,6 +1122,7 @@ static int chain_launch(const Chain &c, cudaStream_t stream) {
 static void chain_free(Chain *c) {
     if (!c) return;
     cudaFree(c->d_ops); cudaFree(c->d_rb); cudaFree(c->d_counter); cudaFree(c->d_runs); cudaFree(c->d_mbox); cudaFree(c->d_arrive); cudaFree(c->d_dbg);
+    for (int32_t *q : c->d_scatter) cudaFree(q);
     delete c;
 }
 
@@ -1054,10 +1137,11 @@ static int chain_plan(Chain *c) {
     const int grid = ds->sm_count;
     int gs = 0;
     int64_t maxK = 0, max_slots = 1;
+    bool has_perm = false;
     for (Linear *L : c->lin) {
         if (L->d.gs != 32 && L->d.gs != 64 && L->d.gs != 128) { c->why_not = "group size not 32 / 64 / 128"; return 0; }
         if (gs && L->d.gs != gs) { c->why_not = "mixed group sizes"; return 0; }
-        if (L->perm && !L->perm_external) { c->why_not = "act-order linear (activation gather)"; return 0; }
+        if (L->perm && !L->perm_external) c->general_k = has_perm = true;    // the gather lives in the GEN instantiation
         if (L->d.NR * (L->d.K / GV_UNIT_K) >= ((int64_t)1 << 30)) { c->why_not = "linear too large"; return 0; }
         gs = L->d.gs;
         maxK = std::max(maxK, L->d.K);
@@ -1150,9 +1234,22 @@ static int chain_plan(Chain *c) {
             mbox_total += (M * width(dep[i]) + 7) & ~(int64_t)7;
             ++c->n_mailboxes;
         }
+    // act-order linears: the producer scatters when this linear is the only reader of its mailbox; otherwise the grid
+    // gathers once into an ingest mailbox of the linear's own
+    std::vector<int> readers(n, 0), use_scatter(n, 0);
+    std::vector<int64_t> ingest_off(n, -1);
+    for (int i = 0; i < n; ++i)
+        if (dep[i] >= 0) ++readers[dep[i]];
+    for (int i = 0; i < n; ++i) {
+        Linear *L = c->lin[i];
+        if (!(L->perm && !L->perm_external)) continue;
+        if (dep[i] >= 0 && readers[dep[i]] == 1) { use_scatter[i] = 1; continue; }
+        ingest_off[i] = mbox_total;
+        mbox_total += (M * L->d.K + 7) & ~(int64_t)7;
+    }
     if (mbox_total) {
-        W4_CUDA_OK(cudaMalloc(&c->d_arrive, (size_t)n * 16 * sizeof(unsigned long long)));     // one 128-byte line per linear
-        W4_CUDA_OK(cudaMemset(c->d_arrive, 0, (size_t)n * 16 * sizeof(unsigned long long)));
+        W4_CUDA_OK(cudaMalloc(&c->d_arrive, (size_t)2 * n * 16 * sizeof(unsigned long long)));     // one 128-byte line per linear (+ ingest)
+        W4_CUDA_OK(cudaMemset(c->d_arrive, 0, (size_t)2 * n * 16 * sizeof(unsigned long long)));
         W4_CUDA_OK(cudaMalloc(&c->d_mbox, (size_t)mbox_total * 2 * sizeof(unsigned short)));
         W4_CUDA_OK(cudaMemset(c->d_mbox, 0xFF, (size_t)mbox_total * 2 * sizeof(unsigned short)));
     }
@@ -1189,6 +1286,40 @@ static int chain_plan(Chain *c) {
         o.eps = pr.eps;
         o.add_running = pr.norm_weight && !pr.residual_in && pr.add_running_residual;
         o.exchange = 0;
+        o.perm = L->perm && !L->perm_external ? L->perm : nullptr;
+        o.scatter = nullptr; o.sc_off = 0; o.sc_len = 0;
+        o.ingest_perm = nullptr; o.ingest_src = nullptr; o.ingest_src_mbox = 0; o.ingest_src_arrive = nullptr;
+        o.ingest = nullptr; o.ingest_arrive = nullptr;
+        if (ingest_off[i] >= 0) {
+            o.ingest_perm = o.perm;
+            o.perm = nullptr;
+            o.ingest_src_mbox = o.mbox_in != nullptr;
+            o.ingest_src = o.ingest_src_mbox ? o.mbox_in : reinterpret_cast<const unsigned short *>(o.x);
+            o.ingest_src_arrive = o.arrive_in;
+            o.ingest = c->d_mbox + ingest_off[i];
+            o.ingest_arrive = c->d_arrive + (size_t)(n + i) * 16;
+            o.mbox_in = o.ingest;                 // from here on the linear reads its ingest mailbox like any other
+            o.arrive_in = o.ingest_arrive;
+        }
+    }
+    // act-order readers: where a mailbox has exactly one reader and that reader gathers, its producer scatters instead
+    {
+        for (int i = 0; i < n; ++i) {
+            if (!use_scatter[i] || !ops[i].perm) continue;
+            const int64_t K = c->lin[i]->d.K;
+            std::vector<int32_t> perm((size_t)K), inv((size_t)K);
+            W4_CUDA_OK(cudaMemcpy(perm.data(), ops[i].perm, (size_t)K * sizeof(int32_t), cudaMemcpyDeviceToHost));
+            for (int64_t t = 0; t < K; ++t) inv[(size_t)perm[(size_t)t]] = (int32_t)t;      // tiled row t reads column perm[t]
+            int32_t *d = nullptr;
+            W4_CUDA_OK(cudaMalloc(&d, (size_t)K * sizeof(int32_t)));
+            c->d_scatter.push_back(d);
+            W4_CUDA_OK(cudaMemcpy(d, inv.data(), (size_t)K * sizeof(int32_t), cudaMemcpyHostToDevice));
+            ChainOp &prod = ops[dep[i]];
+            prod.scatter = d;
+            prod.sc_off = (int)((lo_x(i) - lo_y(dep[i])) / 2);      // M = 1: any aligned sub-range; M > 1: the whole row (offset 0)
+            prod.sc_len = (int)K;
+            ops[i].perm = nullptr;                                  // the mailbox row arrives gathered
+        }
     }
     W4_CUDA_OK(cudaMemcpy(c->d_rb, rb.data(), rb.size() * sizeof(int), cudaMemcpyHostToDevice));
     W4_CUDA_OK(cudaMalloc(&c->d_ops, ops.size() * sizeof(ChainOp)));
