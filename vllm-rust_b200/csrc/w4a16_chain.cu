@@ -1173,6 +1173,16 @@ static int chain_plan(Chain *c) {
     const int off_ring = (int)off; off += S * stride;
     c->smem = (int)off;
     c->grid = grid;
+    {   // every CTA must be resident at once (the hand-overs wait for all of them): one CTA per SM has to fit
+        int per_sm = 0;
+        cudaFuncSetAttribute(chain_kernel<1, 1, false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CH_SMEM_MAX);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, chain_kernel<1, 1, false, false, false>, CH_THREADS, (size_t)c->smem) != cudaSuccess ||
+            per_sm < 1) {
+            cudaGetLastError();
+            c->why_not = "one CTA of the chain kernel does not fit an SM of this device";
+            return 0;
+        }
+    }
 
     // ---- dependencies between the linears (byte ranges of the caller's buffers) ----
     // RAW: x[i] inside the y of its latest writer j -> mailbox (data-as-flag hand-over, no barrier).  Everything else that
