@@ -98,6 +98,15 @@ __device__ __forceinline__ void ch_imma(int (&c)[4], uint32_t a0, uint32_t a1, u
         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 __device__ __forceinline__ void ch_bar_consumers() { asm volatile("bar.sync 1, %0;" ::"n"(CH_CONS_THREADS) : "memory"); }
+__device__ __forceinline__ uint32_t ch_mbar_test(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok;
+}
 __device__ __forceinline__ void ch_mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
@@ -676,7 +685,7 @@ __device__ __forceinline__ void ch_row_blocks_hoist(const ChainParams &p, int n_
             int nslot = slot + 1;
             uint32_t npar = parity;
             if (nslot == p.S) { nslot = 0; npar ^= 1u; }
-            two = __all_sync(0xffffffffu, gv_mbar_try_wait(bar_full + 8 * nslot, npar) != 0);
+            two = __all_sync(0xffffffffu, ch_mbar_test(bar_full + 8 * nslot, npar) != 0);   // test_wait: never suspends
         }
         if (two) {
             ch_hoist_stages<MR, 2>(p, wi, lane, ring, bar_full, bar_empty, gt_l, bq, part, s, slot, parity);
