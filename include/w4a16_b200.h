@@ -185,6 +185,23 @@ int w4a16_forward_into(w4a16_handle_t h, const void *x_bf16, void *y_bf16, int64
 int w4a16_forward_host(w4a16_handle_t h, const void *x_bf16_host, void *y_bf16_host, int64_t M,
                        w4a16_stream_t stream);
 
+/* No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The decode forward for 1 <= M <= 32 tokens through the register-ring mma.sync kernel, with the
+ * kernel's split-K scratch (fp32 partial fragments + arrival tickets) in a static device array
+ * of the library instead of the handle's workspace: 16 KiB of tickets + 8 MiB of partials, held
+ * by every GPU that loads the library until the process exits.  The call allocates nothing and
+ * synchronises nothing (one cudaMemsetAsync of the tickets + one kernel on `stream`).
+ * x, y, bias and row-shard conventions as w4a16_forward_into.  Fails with a message when M > 32,
+ * when the shape's scratch need -- split x (N / 16) x ceil(M / 8 to 1, 2 or 4) x 512 bytes, the
+ * split chosen as for w4a16_forward_into -- exceeds 8 MiB, when N > 65536, or for an act-order
+ * handle that gathers x itself (that gather buffer is allocated on demand).
+ * Every call on a device shares the one array and it keeps the last call's contents (the tickets
+ * are cleared on entry, partials are rewritten before they are read): calls that may overlap on
+ * the GPU -- different streams, or graph branches -- race; serialise them.                 */
+int w4a16_forward_decode_static(w4a16_handle_t h, const void *x_bf16, void *y_bf16, int64_t M,
+                                w4a16_stream_t stream);
+
 /* RowParallelLinear::forward (parallel_layers.rs:275-313): local GEMM, then
  * all_reduce(Sum) (nccl.rs:1338-1364), then + bias.  `comm` is the caller's
  * ncclComm_t.  tp_size == 1 short-circuits the collective (nccl.rs:1339-1341). */

@@ -51,6 +51,7 @@ SIGNATURES = {
     "w4a16_save_tiled": (_i32, [_vp, ctypes.c_char_p, _u64]),
     "w4a16_load_tiled": (_i32, [_vp, ctypes.c_char_p, _u64, _vp]),
     "w4a16_forward_into": (_i32, [_vp, _vp, _vp, _i64, _vp]),
+    "w4a16_forward_decode_static": (_i32, [_vp, _vp, _vp, _i64, _vp]),
     "w4a16_forward_host": (_i32, [_vp, _vp, _vp, _i64, _vp]),
     "w4a16_forward_row_allreduce": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp]),
     "w4a16_peer_create": (_i32, [ctypes.POINTER(_vp), _i32, _i32, _i64]),

@@ -22,6 +22,7 @@
 // so in a stream of linears the next layer's weights are already in flight while the
 // previous kernel drains; x / y / scratch are only touched after the wait.
 #include <algorithm>
+#include <mutex>
 
 #include "w4a16_internal.cuh"
 #include "w4a16_dequant.cuh"
@@ -394,4 +395,97 @@ int launch_decode(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int
 #undef W4_DISPATCH
 }
 
+// ---- w4a16_forward_decode_static: the same kernel with its split-K scratch in a static device array ----------------
+// (no counterpart in the reference, see include/w4a16_b200.h)
+// One array per GPU that loads the library, held until exit: [0, 16 KiB) the per-column arrival tickets, then 8 MiB of
+// fp32 partial fragments.  Every call on a device shares it.
+constexpr size_t NA_TICKET_BYTES = 16 * 1024;          // 4096 tickets: N <= 65536
+constexpr size_t NA_PART_BYTES = 8u * 1024 * 1024;     // sc * (N / 16) * token tiles * 512 B of partials
+static __device__ __align__(256) unsigned char g_static_scratch[NA_TICKET_BYTES + NA_PART_BYTES];
+
+// In host code g_static_scratch is only a stand-in for the symbol: the device address comes from the runtime, once per
+// device, with that device current.
+static unsigned char *g_static_ptr[64] = {};
+static std::mutex g_static_mu;
+static int static_scratch_ptr(int device, unsigned char **out) {
+    if (device < 0 || device >= 64) return fail("forward_decode_static: device index out of range");
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_ptr[device]) {
+        int cur = -1;
+        W4_CUDA_OK(cudaGetDevice(&cur));
+        if (cur != device) return fail("forward_decode_static: the handle's device is not current");
+        void *ptr = nullptr;
+        W4_CUDA_OK(cudaGetSymbolAddress(&ptr, g_static_scratch));
+        if (!ptr) return fail("forward_decode_static: cudaGetSymbolAddress returned a null address");
+        g_static_ptr[device] = static_cast<unsigned char *>(ptr);
+    }
+    *out = g_static_ptr[device];
+    return 0;
+}
+
+int launch_decode_static(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
+                         cudaStream_t stream) {
+    if (M < 1 || M > 32) return fail("forward_decode_static: M must be in 1..32, got " + std::to_string(M));
+    const int gs = L.d.gs;
+    if (gs != 32 && gs != 64 && gs != 128 && gs != L.d.K) return fail("forward_decode_static: unsupported group size");
+    const DecodeCfg c = pick_cfg(L, L.scratch->sm_count);
+    const int nt = M <= 8 ? 1 : M <= 16 ? 2 : 4;
+    const int WR = DEC_WARPS >> c.wk_shift;
+    const dim3 grid((unsigned)(L.d.NR / WR), (unsigned)c.sc);
+    const size_t part_need = c.sc > 1 ? (size_t)c.sc * L.d.NR * nt * 32 * sizeof(float4) : 0;
+    if (part_need > NA_PART_BYTES)
+        return fail("forward_decode_static: this shape needs " + std::to_string(part_need) + " bytes of split-K scratch, the static array holds " +
+                    std::to_string(NA_PART_BYTES) + " (split " + std::to_string(c.sc) + " x " + std::to_string(L.d.NR) +
+                    " row blocks x " + std::to_string(nt) + " token tiles x 512 B)");
+    if ((size_t)grid.x * sizeof(int32_t) > NA_TICKET_BYTES)
+        return fail("forward_decode_static: out_features " + std::to_string(L.d.N) + " exceeds the static ticket table (65536 columns)");
+    unsigned char *base = nullptr;
+    if (static_scratch_ptr(L.device, &base)) return 1;
+    DecodeParams p;
+    p.qw = reinterpret_cast<const uint4 *>(L.qw);
+    p.meta = L.meta;
+    p.bias = add_bias && L.has_bias ? L.bias : nullptr;
+    p.x = x; p.y = y;
+    p.tickets = reinterpret_cast<int32_t *>(base);
+    p.scratch = reinterpret_cast<float4 *>(base + NA_TICKET_BYTES);
+    p.M = (int)M; p.K = (int)L.d.K; p.N = (int)L.d.N; p.KB = (int)L.d.KB; p.G = (int)L.d.G;
+    p.swiglu = L.epilogue == W4A16_EPILOGUE_SWIGLU;
+    const int mpu = gs == 32 ? 4 : gs == 64 ? 2 : 1;
+    p.meta_unit_stride = gs == L.d.K && gs != 128 ? 0 : mpu * META_BYTES;
+    p.wk_shift = c.wk_shift; p.sc = c.sc; p.ups = c.ups;
+    // The array keeps the last call's contents.  Partials are fully rewritten before they are read; the tickets must
+    // start at zero (they reset themselves, but a launch that died half-way would leave them counting).
+    if (c.sc > 1) W4_CUDA_OK(cudaMemsetAsync(p.tickets, 0, (size_t)grid.x * sizeof(int32_t), stream));
+#define W4_DISPATCH(MPU_)                                                 \
+    do {                                                                  \
+        if (nt == 1) return launch_t<1, MPU_>(p, grid, stream, false);    \
+        if (nt == 2) return launch_t<2, MPU_>(p, grid, stream, false);    \
+        return launch_t<4, MPU_>(p, grid, stream, false);                 \
+    } while (0)
+    if (mpu == 1) W4_DISPATCH(1);
+    if (mpu == 2) W4_DISPATCH(2);
+    W4_DISPATCH(4);
+#undef W4_DISPATCH
+}
+
 }  // namespace w4
+
+extern "C" int w4a16_forward_decode_static(w4a16_handle_t h, const void *x_bf16, void *y_bf16, int64_t M, w4a16_stream_t stream) {
+    using namespace w4;
+    const Linear *L = reinterpret_cast<const Linear *>(h);
+    if (!L) return fail("forward_decode_static: null handle");
+    if (!L->loaded) return fail("forward_decode_static: weights not loaded (call load_weights first)");
+    if (!x_bf16 || !y_bf16) return fail("forward_decode_static: null x or y");
+    if ((reinterpret_cast<uintptr_t>(x_bf16) & 15) || (reinterpret_cast<uintptr_t>(y_bf16) & 15))
+        return fail("forward_decode_static: x and y must be 16-byte aligned");
+    if (L->perm && !L->perm_external)
+        return fail("forward_decode_static: act-order handles gather x into an allocated buffer; use w4a16_forward_into");
+    int prev = -1;
+    W4_CUDA_OK(cudaGetDevice(&prev));
+    if (prev != L->device) W4_CUDA_OK(cudaSetDevice(L->device));
+    const bool add_bias = L->tp_mode != W4A16_TP_ROW || L->tp_size == 1;
+    const int rc = launch_decode_static(*L, reinterpret_cast<const __nv_bfloat16 *>(x_bf16), reinterpret_cast<__nv_bfloat16 *>(y_bf16), M,
+                                        add_bias, reinterpret_cast<cudaStream_t>(stream));
+    if (prev != L->device) cudaSetDevice(prev);
+    return rc;
+}
