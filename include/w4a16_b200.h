@@ -26,7 +26,11 @@
  *     with its workspace tensor (marlin.rs:586-640).  Scratch is grown outside stream
  *     capture only and an outgrown buffer lives as long as its handle, so a captured
  *     graph never sees a freed address; inside a capture a too-small scratch is an
- *     error that names w4a16_reserve.
+ *     error that names w4a16_reserve.  The split-K scratch of the (device, stream)
+ *     pair (mid-M and prefill kernels, 15 <= M <= 256) is the exception: it is
+ *     created by the first un-captured forward on that stream, and a captured forward
+ *     that finds none runs unsplit / on the kernel family that needs none instead
+ *     of failing -- run one forward on the stream before capturing.
  *   - There is no CPU fallback.  If no sm_100 device is present every call that
  *     needs one fails loudly.
  */
@@ -349,7 +353,7 @@ int w4a16_has_bias(w4a16_handle_t h);
 int64_t w4a16_weight_bytes(w4a16_handle_t h);  /* resident bytes of the repacked layout */
 /* Kernels launched by this library in this process so far (bench.py's gpu_launches). */
 uint64_t w4a16_kernel_launches(void);
-/* Name of the kernel the dispatcher picks for M tokens ("decode_nt1", "prefill_umma", ...). */
+/* Name of the kernel the dispatcher picks for M tokens ("gemv_stream_imma2", "decode_mma_nt1", "midm_mma", "prefill_umma", ...). */
 const char *w4a16_kernel_for(w4a16_handle_t h, int64_t M);
 /* Override dispatch for tests: "auto" | "decode" (M <= 32 kernels) | "prefill" (tcgen05 kernel).  Non-zero if unknown. */
 int w4a16_set_dispatch(const char *mode);

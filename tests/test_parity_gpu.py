@@ -162,6 +162,41 @@ def test_forced_dispatch_every_kernel_family(product, dispatch, M):
     assert_close_ref(got, oracle_forward(xb, q, z, sb, g), f"{dispatch} M={M}")
 
 
+@pytest.mark.parametrize("g,K,N,M", [(32, 512, 192, 17), (64, 1024, 320, 32), (-1, 640, 192, 21), (128, 512, 40960, 24),
+                                     (128, 12288, 4096, 15), (128, 4096, 6144, 32), (64, 2560, 19456, 29)])
+def test_midm_kernel_groups_bias_slices_and_many_row_blocks(product, g, K, N, M):
+    """The mid-M kernel (15 <= M <= 32, w4a16_midm.cu): group sizes, per-channel scales, bias, K that does not divide
+    into equal slices (640 = 5 units, 2560 = 20), N % 128 != 0, more row blocks than warps on the chip (N = 40960:
+    several row blocks per warp, the ring runs across them), the Qwen3 shapes; deterministic (slices summed in order)."""
+    lin, (qweight, qzeros, scales, bias) = make_awq_layer(product, K, N, g, seed=11 + M, bias=True)
+    q, z, sb = awq_unpacked(qweight, qzeros, scales)
+    xb = O.make_activations(M, K, seed=5)
+    assert lin.kernel_for(M) == "midm_mma"
+    got = run_forward(lin, xb)
+    again = run_forward(lin, xb)
+    assert_close_ref(got, oracle_forward(xb, q, z, sb, g if g > 0 else K, bias_f32=bias), f"midm g={g} K={K} N={N} M={M}")
+    assert (got == again).all()
+
+
+def test_midm_kernel_inside_a_graph_capture_without_scratch_falls_back(product):
+    """A captured forward on a stream that has no split-K scratch yet must not allocate: it takes the kernels that need
+    none, and the replay matches the un-captured result within the GEMM tolerance."""
+    K, N, M, g = 4096, 4096, 24, 128
+    lin, (qweight, qzeros, scales, _) = make_awq_layer(product, K, N, g, seed=41)
+    q, z, sb = awq_unpacked(qweight, qzeros, scales)
+    xb = O.make_activations(M, K, seed=2)
+    x = t_bf16_from_bits(xb).to(DEV)
+    y = torch.full((M, N), float("nan"), dtype=torch.bfloat16, device=DEV)
+    st = torch.cuda.Stream(DEV)   # a fresh stream: no (device, stream) scratch exists for it
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(st):
+        with torch.cuda.graph(graph, stream=st):
+            lin.forward_into(x, y)
+        graph.replay()
+        st.synchronize()
+    assert_close_ref(bits_of(y), oracle_forward(xb, q, z, sb, g), "midm capture fallback")
+
+
 @pytest.mark.parametrize("g,K,N,M", [(32, 512, 192, 33), (64, 1024, 320, 128), (-1, 512, 192, 37), (128, 512, 40960, 40)])
 def test_prefill_kernel_groups_bias_tail_and_many_tiles(product, g, K, N, M):
     """The tcgen05 kernel at few tokens: group sizes, per-channel scales, bias, a half-full last 128-feature tile

@@ -214,17 +214,19 @@ static int ensure_gather(Linear *L, int64_t M, cudaStream_t stream) {
     return 0;
 }
 
-// Which kernel family takes M tokens.  auto: M <= 16 -> the decode kernels (HBM-bound GEMV / skinny mma.sync GEMM),
-// above -> the prefill kernel (tcgen05; split-K fills the machine at few tokens).  Measured on the Qwen3-8B shapes:
+// Which kernel family takes M tokens.  auto: M <= 14 -> the decode kernels (HBM-bound GEMV / register-ring mma.sync GEMM),
+// 15..32 -> the mid-M kernel (mma.sync, every warp a row block x k slice, w4a16_midm.cu), above -> the prefill kernel
+// (tcgen05; split-K fills the machine at few tokens).  Measured on the Qwen3-8B shapes:
 // at M = 32 the prefill kernel takes 19 / 15 / 47 / 26 us against 23 / 28 / 74 / 48 us for the decode kernel, at
 // M = 16 the decode kernel still wins (13 / 12 / 35 / 23 against 19 / 15 / 46 / 25 us).
-enum { ROUTE_DECODE = 0, ROUTE_PREFILL = 2 };
+enum { ROUTE_DECODE = 0, ROUTE_MIDM = 1, ROUTE_PREFILL = 2 };
 static int env_int_api(const char *name, int dflt) { const char *v = getenv(name); return v ? atoi(v) : dflt; }
 static int pick_route(const Linear &L, int64_t M) {
     if (g_dispatch == "prefill") return ROUTE_PREFILL;
     if (g_dispatch == "decode") return ROUTE_DECODE;
     static const int decode_max = std::min<int>((int)DECODE_MAX_M, exp_env_int("W4A16_DECODE_MAX_M", 16));
-    return M > decode_max ? ROUTE_PREFILL : ROUTE_DECODE;
+    if (M > 4 && midm_usable(L, M)) return ROUTE_MIDM;
+    return M <= decode_max ? ROUTE_DECODE : ROUTE_PREFILL;
 }
 
 static inline int64_t out_width(const Linear &L) { return L.epilogue == W4A16_EPILOGUE_SWIGLU ? L.d.N / 2 : L.d.N; }
@@ -241,7 +243,14 @@ static int forward_local(Linear *L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
         if (launch_gather_x(x, L->perm, L->x_gather, M, L->d.K, stream)) return 1;
         x = L->x_gather;
     }
-    const int route = pick_route(*L, M);
+    int route = pick_route(*L, M);
+    if (route == ROUTE_MIDM) {
+        const int rc = launch_midm(*L, x, y, M, add_bias, stream);
+        if (rc != 2) return rc;
+        // 2: its split-K scratch for this stream would have to be allocated inside a stream capture -> the kernels that
+        // took this M before it existed (a forward on the stream before capturing, or w4a16_reserve, avoids this)
+        route = M <= 16 ? ROUTE_DECODE : ROUTE_PREFILL;
+    }
     if (route == ROUTE_PREFILL) return launch_prefill(*L, x, y, M, add_bias, stream);
     for (int64_t m0 = 0; m0 < M; m0 += DECODE_MAX_M) {
         int64_t mm = std::min<int64_t>(DECODE_MAX_M, M - m0);
@@ -733,6 +742,7 @@ int64_t w4a16_weight_bytes(w4a16_handle_t h) {
 const char *w4a16_kernel_for(w4a16_handle_t h, int64_t M) {
     if (!h) return "none";
     const int route = pick_route(*reinterpret_cast<Linear *>(h), M);
+    if (route == ROUTE_MIDM) return "midm_mma";
     if (route == ROUTE_PREFILL) return "prefill_umma";
     return decode_kernel_name(*reinterpret_cast<Linear *>(h), std::min<int64_t>(M, DECODE_MAX_M));
 }
