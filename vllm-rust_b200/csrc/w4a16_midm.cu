@@ -1,4 +1,4 @@
-// w4a16_midm.cu -- the skinny GEMM for 17 <= M <= 64 tokens: between the GEMV kernels and the tcgen05 prefill kernel.
+// w4a16_midm.cu -- the skinny GEMM for 15 <= M <= 48 tokens: between the GEMV kernels and the tcgen05 prefill kernel.
 //
 // Replaces, for these batch sizes, awq_gemv_int4_kt_mloop_m16 looped over 16-token pieces and the dequant + cuBLAS
 // path above it (marlin_cuda.rs:843-953: M <= 16 -> GEMV, else awq_marlin_dequant_int4_bf16 + matmul), and
@@ -14,13 +14,16 @@
 //                  ahead in registers;
 //   activations  : the CTA's k slice of x for ALL tokens sits in shared memory, put there by TMA as 128B-swizzled
 //                  [64 k][8 NT tokens] tiles (no thread instructions, rows beyond M zero-filled); a lane's B fragment
-//                  is ONE 8-byte LDS (k-slots 4t..4t+3 are contiguous in W4T's k order), conflict-free under the swizzle;
+//                  is ONE 8-byte LDS (k-slots 4t..4t+3 are contiguous in W4T's k order), conflict-free under the swizzle
+//                  once the MMA columns are dealt to the token rows as 0,2,4,6,1,3,5,7 (mm_rho);
 //   math         : mma.sync.m16n8k16 bf16, fp32 accumulators in registers, NT token tiles per A fragment;
 //   split-K      : slices meet in an fp32 scratch in fragment order (one coalesced 512-byte store per token tile); the
 //                  warp that arrives last at a row block's ticket sums the slices in slice order (deterministic) and
 //                  writes y (+ bias / SwiGLU).  No CTA-wide barrier after set-up: warps never wait for each other.
-// Issue slots per chunk at 64 tokens: ~12 shifts + 48 dequant + 32 LDS + 32 MMA + ~10 = ~135 for 65536 MACs; the
-// prefill kernel's dequant alone is more than that per chunk and is redone per tile.
+// Issue slots per chunk at 32 tokens: ~175 (12 shifts + 48 dequant + 16 LDS + 16 MMA + ring / loop bookkeeping) for 32768
+// MACs; the prefill kernel's dequant alone is more than that per chunk, sits on 16 warps of at most 96 SMs at these sizes
+// and is redone per tile.  Above ~48 tokens the x slice no longer leaves room for few slices and the fp32 partials
+// (slices x M x N x 4 bytes, written and re-read) outweigh the weights: the tcgen05 kernel takes over.
 #include <cuda.h>
 
 #include <algorithm>
@@ -78,10 +81,17 @@ __device__ __forceinline__ uint2 mm_lds64(uint32_t addr) {
     return r;
 }
 
-// Fragment -> y.  Lane (g, t) holds rows 16R+g (x, y) and 16R+g+8 (z, w) for tokens 8nt+2t (x, z) and 8nt+2t+1 (y, w).
+// MMA column c of a token tile is token row mm_rho(c) of that tile, not c: with the TMA 128B swizzle the 16-byte piece a
+// lane reads is (2j + t/2) ^ (row & 7), so rows r and r ^ 1 meet in the same pair of pieces -- columns 0..3 (one half-warp of
+// an 8-byte LDS) must sit on rows with distinct r >> 1.  Measured before: 44 % of the shared-memory wavefronts were bank
+// conflicts and the pipe was ~77 % busy.
+__device__ __forceinline__ int mm_rho(int c) { return c < 4 ? 2 * c : 2 * (c - 4) + 1; }
+
+// Fragment -> y.  Lane (g, t) holds rows 16R+g (x, y) and 16R+g+8 (z, w) for MMA columns 2t (x, z) and 2t+1 (y, w).
 template <int NT>
 __device__ __forceinline__ void mm_store(const MidmParams &p, int R, int lane, const float4 (&v)[NT]) {
     const int g = lane >> 2, t = lane & 3;
+    const int r0 = mm_rho(2 * t), r1 = mm_rho(2 * t + 1);
     const int n0 = R * 16 + g;
     const float b0 = p.bias ? __bfloat162float(p.bias[n0]) : 0.f;
     const float b1 = p.bias ? __bfloat162float(p.bias[n0 + 8]) : 0.f;
@@ -89,22 +99,22 @@ __device__ __forceinline__ void mm_store(const MidmParams &p, int R, int lane, c
         const size_t I = (size_t)(p.N >> 1), c = (size_t)R * 8 + g;
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) {
-            const int tok = nt * 8 + 2 * t;
-            if (tok < p.M) p.y[(size_t)tok * I + c] = swiglu_bf16(v[nt].x + b0, v[nt].z + b1);
-            if (tok + 1 < p.M) p.y[(size_t)(tok + 1) * I + c] = swiglu_bf16(v[nt].y + b0, v[nt].w + b1);
+            const int tok0 = nt * 8 + r0, tok1 = nt * 8 + r1;
+            if (tok0 < p.M) p.y[(size_t)tok0 * I + c] = swiglu_bf16(v[nt].x + b0, v[nt].z + b1);
+            if (tok1 < p.M) p.y[(size_t)tok1 * I + c] = swiglu_bf16(v[nt].y + b0, v[nt].w + b1);
         }
         return;
     }
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
-        const int tok = nt * 8 + 2 * t;
-        if (tok < p.M) {
-            p.y[(size_t)tok * p.N + n0] = __float2bfloat16_rn(v[nt].x + b0);
-            p.y[(size_t)tok * p.N + n0 + 8] = __float2bfloat16_rn(v[nt].z + b1);
+        const int tok0 = nt * 8 + r0, tok1 = nt * 8 + r1;
+        if (tok0 < p.M) {
+            p.y[(size_t)tok0 * p.N + n0] = __float2bfloat16_rn(v[nt].x + b0);
+            p.y[(size_t)tok0 * p.N + n0 + 8] = __float2bfloat16_rn(v[nt].z + b1);
         }
-        if (tok + 1 < p.M) {
-            p.y[(size_t)(tok + 1) * p.N + n0] = __float2bfloat16_rn(v[nt].y + b0);
-            p.y[(size_t)(tok + 1) * p.N + n0 + 8] = __float2bfloat16_rn(v[nt].w + b1);
+        if (tok1 < p.M) {
+            p.y[(size_t)tok1 * p.N + n0] = __float2bfloat16_rn(v[nt].y + b0);
+            p.y[(size_t)tok1 * p.N + n0 + 8] = __float2bfloat16_rn(v[nt].w + b1);
         }
     }
 }
@@ -189,10 +199,12 @@ midm_kernel(const __grid_constant__ CUtensorMap x_map, const MidmParams p) {
         }
     }
 
-    // this lane's 8 bytes of a B fragment: token row 8 nt + g, k-slots 16 j + 4 t .. + 3 -> 16-byte piece (2 j + t / 2) ^ g
+    // this lane's 8 bytes of a B fragment: MMA column g = token row 8 nt + rho(g), k-slots 16 j + 4 t .. + 3 -> 16-byte piece
+    // (2 j + t / 2) ^ rho(g) of that row
     uint32_t xl[4];
+    const int xr = mm_rho(g);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) xl[j] = xs + (uint32_t)(g * 128 + (((2 * j + (t >> 1)) ^ g) << 4) + (t & 1) * 8);
+    for (int j = 0; j < 4; ++j) xl[j] = xs + (uint32_t)(xr * 128 + (((2 * j + (t >> 1)) ^ xr) << 4) + (t & 1) * 8);
     const uint32_t my_w = ring + lane * 16, my_s = ring + 512 + 4 * g, my_z = ring + 512 + META_ZERO_OFF + g;
     int slot = 0;
 
@@ -380,7 +392,7 @@ static MmCfg mm_pick(const Linear &L, int64_t M, int sms) {
 bool midm_usable(const Linear &L, int64_t M) {
     static const bool off = exp_env_int("W4A16_NO_MIDM", 0) != 0;
     const int gs = L.d.gs;
-    static const int min_m = exp_env_int("W4A16_MM_MIN_M", 15), max_m = exp_env_int("W4A16_MM_MAX_M", 32);
+    static const int min_m = exp_env_int("W4A16_MM_MIN_M", 15), max_m = exp_env_int("W4A16_MM_MAX_M", 48);
     if (off || M < min_m || M > max_m || M > 64) return false;
     if (gs != 32 && gs != 64 && gs != 128 && gs != L.d.K) return false;
     return L.d.NR <= MM_MAX_TICKETS;
