@@ -197,7 +197,7 @@ def test_midm_kernel_inside_a_graph_capture_without_scratch_falls_back(product):
     assert_close_ref(bits_of(y), oracle_forward(xb, q, z, sb, g), "midm capture fallback")
 
 
-@pytest.mark.parametrize("g,K,N,M", [(32, 512, 192, 33), (64, 1024, 320, 128), (-1, 512, 192, 37), (128, 512, 40960, 40)])
+@pytest.mark.parametrize("g,K,N,M", [(32, 512, 192, 57), (64, 1024, 320, 128), (-1, 512, 192, 61), (128, 512, 40960, 50)])
 def test_prefill_kernel_groups_bias_tail_and_many_tiles(product, g, K, N, M):
     """The tcgen05 kernel at few tokens: group sizes, per-channel scales, bias, a half-full last 128-feature tile
     (N % 128 != 0), and more tiles than SMs (N = 40960: persistent CTAs run several tiles); deterministic."""
