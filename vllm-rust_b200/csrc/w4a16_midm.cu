@@ -413,8 +413,21 @@ static int mm_launch(const CUtensorMap &map, const MidmParams &p, dim3 grid, siz
     }
     if (attr_err[device] != cudaSuccess)
         return fail(std::string("cudaFuncSetAttribute(midm_kernel smem): ") + cudaGetErrorString(attr_err[device]));
-    midm_kernel<NT, GPS><<<grid, MM_THREADS, smem, stream>>>(map, p);
-    W4_CUDA_OK(cudaGetLastError());
+    // Programmatic dependent launch: in a stream of linears the next kernel's CTAs take an SM the moment one frees up, set up
+    // their barriers and start their weight rings (weights are immutable) while this grid drains; x, y and the split-K scratch
+    // are only touched behind griddepcontrol.wait.
+    static const bool pdl = getenv("W4A16_NO_PDL") == nullptr || atoi(getenv("W4A16_NO_PDL")) == 0;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(MM_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    W4_CUDA_OK(cudaLaunchKernelEx(&cfg, midm_kernel<NT, GPS>, map, p));
     count_launch();
     return 0;
 }

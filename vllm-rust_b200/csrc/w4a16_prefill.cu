@@ -128,9 +128,15 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     const uint32_t crank = CL2 ? cluster_ctarank() : 0u;
+    // Programmatic dependent launch (the host sets the attribute for the un-clustered launches): the next kernel of the
+    // stream may take this SM as soon as it is free; of this kernel, only the warps that touch what a previous kernel may
+    // still be using -- x (TMA producer), y / split-K scratch / tickets (epilogue) -- wait for it; the dequant warps start
+    // on the immutable weights at once.  Without the attribute both instructions are no-ops.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     if (warp == 0) {
         // ===== TMA producer: x tiles [TM tokens][64 k] =====
+        asm volatile("griddepcontrol.wait;" ::: "memory");
         int s = 0; uint32_t ph = 0;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const int m_tile = (tile % nm_tiles) / p.n_tiles, kb0 = (tile / nm_tiles) * KBLKS;
@@ -284,6 +290,7 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
         }
     } else if (warp >= 20) {
         // ===== epilogue warps: TMEM -> +bias -> bf16 -> staging -> y =====
+        asm volatile("griddepcontrol.wait;" ::: "memory");
         const int q = warp & 3;
         const int et = threadIdx.x - 20 * 32;   // 0..127
         uint32_t ti = 0;
@@ -521,8 +528,18 @@ static int launch_pf(const CUtensorMap &map, const PrefillParams &p, int grid, i
     if (attr_err[device] != cudaSuccess)
         return fail(std::string("cudaFuncSetAttribute(prefill_kernel smem): ") + cudaGetErrorString(attr_err[device]));
     if (!CL2) {
-        prefill_kernel<TM, GPS, CL2><<<grid, PF_THREADS, C::SMEM_BYTES, stream>>>(map, p);
-        W4_CUDA_OK(cudaGetLastError());
+        static const bool pdl = getenv("W4A16_NO_PDL") == nullptr || atoi(getenv("W4A16_NO_PDL")) == 0;
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3((unsigned)grid);
+        cfg.blockDim = dim3(PF_THREADS);
+        cfg.dynamicSmemBytes = C::SMEM_BYTES;
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = pdl ? 1 : 0;
+        W4_CUDA_OK(cudaLaunchKernelEx(&cfg, prefill_kernel<TM, GPS, CL2>, map, p));
         count_launch();
         return 0;
     }
