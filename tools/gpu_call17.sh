@@ -1,9 +1,7 @@
 #!/bin/bash
 mkdir -p gpurun_out
 {
-for i in 1 2; do
-echo "== pdl $i"; timeout 200 python tools/midm_sweep.py --dispatch auto --m 64 128 --shapes o down gate_up 2>&1 | tail -6
-echo "== no pdl $i"; W4A16_NO_PDL=1 timeout 200 python tools/midm_sweep.py --dispatch auto --m 64 128 --shapes o down gate_up 2>&1 | tail -6
-done
-} > gpurun_out/pf_pdl2.log 2>&1
-cat gpurun_out/pf_pdl2.log
+timeout 900 python -m pytest tests/test_config3_prefill_gpu.py tests/test_parity_gpu.py tests/test_fused_gpu.py -x -q 2>&1 | tail -2
+timeout 300 python tools/midm_sweep.py --check --dispatch auto --m 2048 4096 64 128 256 --shapes gate_up qkv o down 2>&1 | tail -20
+} > gpurun_out/pf_cl2pdl.log 2>&1
+cat gpurun_out/pf_cl2pdl.log

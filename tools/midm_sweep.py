@@ -46,6 +46,7 @@ def main():
             lin.load_weights({"qweight": qweight, "qzeros": qzeros, "scales": scales})
             lins.append(lin)
         W = lins[0].dequantize().float() if args.check else None
+        torch.cuda.synchronize()   # the side stream below must not reuse the freed bf16 temporary while .float() still reads it
         for M in args.m:
             x = torch.randn((M, K), device=dev).to(torch.bfloat16)
             y = torch.empty((M, N), device=dev, dtype=torch.bfloat16)

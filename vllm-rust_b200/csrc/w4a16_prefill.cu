@@ -128,7 +128,7 @@ prefill_kernel(const __grid_constant__ CUtensorMap x_map, const PrefillParams p)
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     const uint32_t crank = CL2 ? cluster_ctarank() : 0u;
-    // Programmatic dependent launch (the host sets the attribute for the un-clustered launches): the next kernel of the
+    // Programmatic dependent launch: the next kernel of the
     // stream may take this SM as soon as it is free; of this kernel, only the warps that touch what a previous kernel may
     // still be using -- x (TMA producer), y / split-K scratch / tickets (epilogue) -- wait for it; the dequant warps start
     // on the immutable weights at once.  Without the attribute both instructions are no-ops.
@@ -549,10 +549,13 @@ static int launch_pf(const CUtensorMap &map, const PrefillParams &p, int grid, i
     cfg.blockDim = dim3(PF_THREADS);
     cfg.dynamicSmemBytes = C::SMEM_BYTES;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    static const bool pdl2 = getenv("W4A16_NO_PDL") == nullptr || atoi(getenv("W4A16_NO_PDL")) == 0;
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl2 ? 2 : 1;
     W4_CUDA_OK(cudaLaunchKernelEx(&cfg, prefill_kernel<TM, GPS, CL2>, map, p));
     count_launch();
     return 0;
@@ -622,13 +625,13 @@ int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, in
         const int kblks = (int)(L.d.K / PF_BLOCK_K), nm = p.n_tiles * p.m_tiles, sms = L.scratch->sm_count;
         // Cost model in units of one 64-k block of one CTA (~0.35 us: the TS-mode MMA chain): waves x (blocks per
         // slice + a fixed per-slice cost: pipeline fill, fp32 partial write, ticket) + the last slice's re-read of all
-        // partials of its tile, which is latency-bound on 128 threads: ~0.06 units per (slice x token row), fitted to
+        // partials of its tile, which is latency-bound on 128 threads: ~0.09 units per (slice x token row), fitted to
         // qkv / o at M = 64 (split wins by 8-11 us), M = 128 (by ~4 us) and M = 256 (split LOSES 9-14 us).
         int ks = 1;
         {
             static const int forced = exp_env_int("W4A16_PF_KSPLIT", 0);
             static const int c_fix = exp_env_int("W4A16_PF_KSPLIT_FIX", 6);
-            static const double c_row = exp_env_double("W4A16_PF_KSPLIT_ROW", 0.06);
+            static const double c_row = exp_env_double("W4A16_PF_KSPLIT_ROW", 0.09);
             const int rows = (int)std::min<int64_t>(M, TM);
             const int cands[6] = {1, 2, 3, 4, 6, 8};
             double best = -1;
