@@ -370,7 +370,7 @@ struct MmCfg { int nt, ns, cps; };
 // in units of one chunk of one warp, passes = row blocks per warp.
 static MmCfg mm_pick(const Linear &L, int64_t M, int sms) {
     MmCfg c;
-    c.nt = M <= 8 ? 1 : M <= 16 ? 2 : M <= 32 ? 4 : M <= 48 ? 6 : 8;
+    c.nt = M <= 48 ? (int)((M + 7) / 8) : 8;   // token tiles of 8: 1 .. 6, or 8
     const int U = (int)(L.d.K / 128), NR = (int)L.d.NR;
     const int max_units = std::min(MM_MAX_KBLKS / 2, MM_SMEM_X_MAX / (c.nt * 2048));
     const int groups = (NR + MM_WARPS - 1) / MM_WARPS;
@@ -468,7 +468,9 @@ int launch_midm(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64
     } while (0)
     if (c.nt == 1) W4_MM(1);
     if (c.nt == 2) W4_MM(2);
+    if (c.nt == 3) W4_MM(3);
     if (c.nt == 4) W4_MM(4);
+    if (c.nt == 5) W4_MM(5);
     if (c.nt == 6) W4_MM(6);
     W4_MM(8);
 #undef W4_MM
