@@ -27,7 +27,7 @@
  *     capture only and an outgrown buffer lives as long as its handle, so a captured
  *     graph never sees a freed address; inside a capture a too-small scratch is an
  *     error that names w4a16_reserve.  The split-K scratch of the (device, stream)
- *     pair (mid-M and prefill kernels, 15 <= M <= 256) is the exception: it is
+ *     pair (mid-M and prefill kernels, 11 <= M <= 256) is the exception: it is
  *     created by the first un-captured forward on that stream, and a captured forward
  *     that finds none runs unsplit / on the kernel family that needs none instead
  *     of failing -- run one forward on the stream before capturing.

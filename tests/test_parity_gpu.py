@@ -163,9 +163,9 @@ def test_forced_dispatch_every_kernel_family(product, dispatch, M):
 
 
 @pytest.mark.parametrize("g,K,N,M", [(32, 512, 192, 17), (64, 1024, 320, 32), (-1, 640, 192, 21), (128, 512, 40960, 24),
-                                     (128, 12288, 4096, 15), (128, 4096, 6144, 32), (64, 2560, 19456, 29), (128, 4096, 4096, 48), (32, 1024, 2368, 41)])
+                                     (128, 12288, 4096, 15), (128, 4096, 6144, 32), (64, 2560, 19456, 29), (128, 4096, 4096, 48), (32, 1024, 2368, 41), (128, 4096, 4096, 11), (64, 2048, 4736, 37)])
 def test_midm_kernel_groups_bias_slices_and_many_row_blocks(product, g, K, N, M):
-    """The mid-M kernel (15 <= M <= 48, w4a16_midm.cu): group sizes, per-channel scales, bias, K that does not divide
+    """The mid-M kernel (11 <= M <= 48, w4a16_midm.cu): group sizes, per-channel scales, bias, K that does not divide
     into equal slices (640 = 5 units, 2560 = 20), N % 128 != 0, more row blocks than warps on the chip (N = 40960:
     several row blocks per warp, the ring runs across them), the Qwen3 shapes; deterministic (slices summed in order)."""
     lin, (qweight, qzeros, scales, bias) = make_awq_layer(product, K, N, g, seed=11 + M, bias=True)

@@ -214,8 +214,8 @@ static int ensure_gather(Linear *L, int64_t M, cudaStream_t stream) {
     return 0;
 }
 
-// Which kernel family takes M tokens.  auto: M <= 14 -> the decode kernels (HBM-bound GEMV / register-ring mma.sync GEMM),
-// 15..48 -> the mid-M kernel (mma.sync, every warp a row block x k slice, w4a16_midm.cu), above -> the prefill kernel
+// Which kernel family takes M tokens.  auto: M <= 10 -> the decode kernels (HBM-bound GEMV / register-ring mma.sync GEMM),
+// 11..48 -> the mid-M kernel (mma.sync, every warp a row block x k slice, w4a16_midm.cu), above -> the prefill kernel
 // (tcgen05; split-K fills the machine at few tokens).  Measured on the Qwen3-8B shapes:
 // at M = 32 the prefill kernel takes 19 / 15 / 47 / 26 us against 23 / 28 / 74 / 48 us for the decode kernel, at
 // M = 16 the decode kernel still wins (13 / 12 / 35 / 23 against 19 / 15 / 46 / 25 us).

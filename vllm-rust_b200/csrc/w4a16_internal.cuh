@@ -159,7 +159,7 @@ int gemv_debug_read(unsigned long long *out, int64_t words, unsigned long long *
 int launch_prefill(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias,
                    cudaStream_t stream);
 bool prefill_available();
-// 15 <= M <= 48: mma.sync skinny GEMM, every warp a row block x k slice (w4a16_midm.cu).  launch_midm returns 2 when it
+// 11 <= M <= 48: mma.sync skinny GEMM, every warp a row block x k slice (w4a16_midm.cu).  launch_midm returns 2 when it
 // cannot run this call (split-K scratch would have to grow under stream capture): the caller uses the prefill kernel.
 bool midm_usable(const Linear &L, int64_t M);
 int launch_midm(const Linear &L, const __nv_bfloat16 *x, __nv_bfloat16 *y, int64_t M, bool add_bias, cudaStream_t stream);

@@ -1,4 +1,4 @@
-// w4a16_midm.cu -- the skinny GEMM for 15 <= M <= 48 tokens: between the GEMV kernels and the tcgen05 prefill kernel.
+// w4a16_midm.cu -- the skinny GEMM for 11 <= M <= 48 tokens: between the GEMV kernels and the tcgen05 prefill kernel.
 //
 // Replaces, for these batch sizes, awq_gemv_int4_kt_mloop_m16 looped over 16-token pieces and the dequant + cuBLAS
 // path above it (marlin_cuda.rs:843-953: M <= 16 -> GEMV, else awq_marlin_dequant_int4_bf16 + matmul), and
@@ -392,7 +392,7 @@ static MmCfg mm_pick(const Linear &L, int64_t M, int sms) {
 bool midm_usable(const Linear &L, int64_t M) {
     static const bool off = exp_env_int("W4A16_NO_MIDM", 0) != 0;
     const int gs = L.d.gs;
-    static const int min_m = exp_env_int("W4A16_MM_MIN_M", 15), max_m = exp_env_int("W4A16_MM_MAX_M", 48);
+    static const int min_m = exp_env_int("W4A16_MM_MIN_M", 11), max_m = exp_env_int("W4A16_MM_MAX_M", 48);
     if (off || M < min_m || M > max_m || M > 64) return false;
     if (gs != 32 && gs != 64 && gs != 128 && gs != L.d.K) return false;
     return L.d.NR <= MM_MAX_TICKETS;
